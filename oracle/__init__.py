@@ -1,0 +1,214 @@
+"""TEST INFRASTRUCTURE ONLY. ctypes access to the two CPU checkers.
+
+* ``ref``  -- oracle/_ref/libpp_ref.so: the reference's own sources compiled unmodified
+              (oracle/Makefile); ``None`` where it was never built.
+* ``port`` -- oracle/liboracle_port.so: the committed C restatement (oracle/port.c).
+
+Only tests/, __graft_entry__.smoke() and bench.py's CPU-baseline / reference arm may import this
+package. The product (path_planner_b200) never does.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+
+u8p = np.ctypeslib.ndpointer(np.uint8, flags="C_CONTIGUOUS")
+i32p = np.ctypeslib.ndpointer(np.int32, flags="C_CONTIGUOUS")
+u32p = np.ctypeslib.ndpointer(np.uint32, flags="C_CONTIGUOUS")
+f32p = np.ctypeslib.ndpointer(np.float32, flags="C_CONTIGUOUS")
+f64p = np.ctypeslib.ndpointer(np.float64, flags="C_CONTIGUOUS")
+
+
+def build(verbose=False):
+    """Compile the port (always) and _ref (only where /root/reference exists)."""
+    r = subprocess.run(["make", "-C", _HERE, "all"], capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError("oracle build failed:\n" + r.stdout + r.stderr)
+    if verbose:
+        print(r.stdout)
+
+
+def _load(path):
+    return C.CDLL(path) if os.path.exists(path) else None
+
+
+def _opt(arr, dtype):
+    return None if arr is None else arr.ctypes.data_as(C.c_void_p)
+
+
+class Port:
+    def __init__(self):
+        path = os.path.join(_HERE, "liboracle_port.so")
+        if not os.path.exists(path):
+            build()
+        self.lib = C.CDLL(path)
+        L = self.lib
+        L.port_footprint_points.argtypes = [C.c_double, f32p, C.c_int, C.c_int, i32p, C.c_int]
+        L.port_se2_volume.argtypes = [u8p, C.c_uint32, C.c_uint32, i32p, C.c_int, C.c_uint32, C.c_float, C.c_float,
+                                      C.c_float, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, u8p, C.c_int, C.c_int]
+        L.port_footprint_cost_batch.argtypes = [u8p, C.c_uint32, C.c_uint32, i32p, C.c_int, f32p, C.c_uint32, f32p,
+                                                u8p, u8p, C.c_int]
+        L.port_heuristic.argtypes = [u8p, C.c_uint32, C.c_uint32, C.c_float, C.c_float, C.c_float, C.c_float,
+                                     C.c_float, C.c_void_p, C.c_uint32, C.c_void_p, f32p]
+        L.port_heuristic_fixed_point.argtypes = [u8p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_float, f32p]
+        L.port_extract_obstacles.argtypes = [u8p, C.c_uint32, C.c_uint32] + [C.c_double] * 8 + [f64p, C.c_uint32]
+        L.port_radius_topk.argtypes = [f64p, C.c_uint32, f64p, C.c_uint32, C.c_double, C.c_uint32, u32p, f64p, u32p,
+                                       u32p]
+
+    def footprint_points(self, resolution, boundary, hole):
+        b = np.ascontiguousarray(boundary, np.float32)
+        out = np.zeros((4096, 2), np.int32)
+        n = self.lib.port_footprint_points(resolution, b, len(b), int(hole), out, 4096)
+        assert n <= 4096
+        return out[:n].copy()
+
+    def se2_volume(self, cost, pts, n_theta, ox=0.5, oy=0.5, ot=0.0, t0=0, t1=None, y0=0, y1=None, nthreads=0,
+                   trig_double=False):
+        H, W = cost.shape
+        t1 = n_theta if t1 is None else t1
+        y1 = H if y1 is None else y1
+        pts = np.ascontiguousarray(pts, np.int32)
+        out = np.empty((t1 - t0, y1 - y0, W), np.uint8)
+        self.lib.port_se2_volume(cost, W, H, pts, len(pts), n_theta, ox, oy, ot, t0, t1, y0, y1, out, nthreads,
+                                 int(trig_double))
+        return out
+
+    def footprint_cost_batch(self, cost, pts, poses, trig_double=False):
+        H, W = cost.shape
+        poses = np.ascontiguousarray(poses, np.float32)
+        pts = np.ascontiguousarray(pts, np.int32)
+        n = len(poses)
+        c = np.empty(n, np.float32)
+        f = np.empty(n, np.uint8)
+        k = np.empty(n, np.uint8)
+        self.lib.port_footprint_cost_batch(cost, W, H, pts, len(pts), poses, n, c, f, k, int(trig_double))
+        return c, f, k
+
+    def heuristic(self, cost, start, goal, cost_penalty, queries=None):
+        H, W = cost.shape
+        table = np.empty((H, W), np.float32)
+        q = None if queries is None else np.ascontiguousarray(queries, np.float32)
+        nq = 0 if q is None else len(q)
+        qo = np.empty(nq, np.float32)
+        ok = self.lib.port_heuristic(cost, W, H, start[0], start[1], goal[0], goal[1], cost_penalty,
+                                     _opt(q, np.float32), nq, qo.ctypes.data_as(C.c_void_p), table)
+        return bool(ok), table, qo
+
+    def heuristic_fixed_point(self, cost, goal_xy, cost_penalty):
+        H, W = cost.shape
+        field = np.empty((H, W), np.float32)
+        self.lib.port_heuristic_fixed_point(cost, W, H, int(goal_xy[0]), int(goal_xy[1]), cost_penalty, field)
+        return field
+
+    def extract_obstacles(self, cost, res, origin, robot_pose, max_follow_range, behind_ignore_range):
+        H, W = cost.shape
+        cap = int((cost >= 253).sum()) + 1
+        out = np.empty((cap, 2), np.float64)
+        n = self.lib.port_extract_obstacles(cost, W, H, res, origin[0], origin[1], robot_pose[0], robot_pose[1],
+                                            robot_pose[2], max_follow_range, behind_ignore_range, out, cap)
+        return out[:n].copy()
+
+    def radius_topk(self, pts, queries, radius_arg, K):
+        pts = np.ascontiguousarray(pts, np.float64)
+        queries = np.ascontiguousarray(queries, np.float64)
+        Q = len(queries)
+        idx = np.zeros((Q, K), np.uint32)
+        d2 = np.zeros((Q, K), np.float64)
+        cnt = np.zeros(Q, np.uint32)
+        found = np.zeros(Q, np.uint32)
+        self.lib.port_radius_topk(pts, len(pts), queries, Q, radius_arg, K, idx, d2, cnt, found)
+        return idx, d2, cnt, found
+
+
+class Ref:
+    """The reference's own code. Footprints are given as the reference takes them: the
+    boundary vector (1, 2 or 4 numbers, metres), the costmap resolution and the hole flag."""
+
+    def __init__(self, double_trig=False):
+        name = "libpp_ref_dtrig.so" if double_trig else "libpp_ref.so"
+        path = os.path.join(_HERE, "_ref", name)
+        if not os.path.exists(path):
+            raise FileNotFoundError(path)
+        self.lib = C.CDLL(path)
+        L = self.lib
+        L.ref_footprint_points.argtypes = [C.c_double, f32p, C.c_int, C.c_int, i32p, C.c_int]
+        L.ref_se2_volume.argtypes = [u8p, C.c_uint32, C.c_uint32, C.c_double, f32p, C.c_int, C.c_int, C.c_uint32,
+                                     C.c_float, C.c_float, C.c_float, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32,
+                                     u8p, C.c_int]
+        L.ref_footprint_cost_batch.argtypes = [u8p, C.c_uint32, C.c_uint32, C.c_double, f32p, C.c_int, C.c_int, f32p,
+                                               C.c_uint32, f32p, u8p, u8p]
+        L.ref_heuristic.argtypes = [u8p, C.c_uint32, C.c_uint32, C.c_double, C.c_float, C.c_float, C.c_float,
+                                    C.c_float, C.c_float, C.c_uint32, C.c_void_p, C.c_uint32, C.c_void_p, f32p,
+                                    C.POINTER(C.c_double)]
+        L.ref_radius_topk.argtypes = [f64p, C.c_uint32, f64p, C.c_uint32, C.c_double, C.c_uint32, u32p, f64p, u32p,
+                                      u32p, C.POINTER(C.c_double), C.POINTER(C.c_double)]
+
+    def footprint_points(self, resolution, boundary, hole):
+        b = np.ascontiguousarray(boundary, np.float32)
+        out = np.zeros((4096, 2), np.int32)
+        n = self.lib.ref_footprint_points(resolution, b, len(b), int(hole), out, 4096)
+        assert n <= 4096
+        return out[:n].copy()
+
+    def se2_volume(self, cost, res, boundary, hole, n_theta, ox=0.5, oy=0.5, ot=0.0, t0=0, t1=None, y0=0, y1=None,
+                   nthreads=0):
+        H, W = cost.shape
+        t1 = n_theta if t1 is None else t1
+        y1 = H if y1 is None else y1
+        b = np.ascontiguousarray(boundary, np.float32)
+        out = np.empty((t1 - t0, y1 - y0, W), np.uint8)
+        self.lib.ref_se2_volume(cost, W, H, res, b, len(b), int(hole), n_theta, ox, oy, ot, t0, t1, y0, y1, out,
+                                nthreads)
+        return out
+
+    def footprint_cost_batch(self, cost, res, boundary, hole, poses):
+        H, W = cost.shape
+        b = np.ascontiguousarray(boundary, np.float32)
+        poses = np.ascontiguousarray(poses, np.float32)
+        n = len(poses)
+        c = np.empty(n, np.float32)
+        f = np.empty(n, np.uint8)
+        k = np.empty(n, np.uint8)
+        self.lib.ref_footprint_cost_batch(cost, W, H, res, b, len(b), int(hole), poses, n, c, f, k)
+        return c, f, k
+
+    def heuristic(self, cost, res, start, goal, cost_penalty, queries=None, n_theta=72):
+        H, W = cost.shape
+        table = np.empty((H, W), np.float32)
+        q = None if queries is None else np.ascontiguousarray(queries, np.float32)
+        nq = 0 if q is None else len(q)
+        qo = np.empty(nq, np.float32)
+        sec = C.c_double(0)
+        ok = self.lib.ref_heuristic(cost, W, H, res, start[0], start[1], goal[0], goal[1], cost_penalty, n_theta,
+                                    _opt(q, np.float32), nq, qo.ctypes.data_as(C.c_void_p), table, C.byref(sec))
+        self.last_seconds = sec.value
+        return bool(ok), table, qo
+
+    def radius_topk(self, pts, queries, radius_arg, K):
+        pts = np.ascontiguousarray(pts, np.float64)
+        queries = np.ascontiguousarray(queries, np.float64)
+        Q = len(queries)
+        idx = np.zeros((Q, K), np.uint32)
+        d2 = np.zeros((Q, K), np.float64)
+        cnt = np.zeros(Q, np.uint32)
+        found = np.zeros(Q, np.uint32)
+        bs, qs = C.c_double(0), C.c_double(0)
+        self.lib.ref_radius_topk(pts, len(pts), queries, Q, radius_arg, K, idx, d2, cnt, found, C.byref(bs),
+                                 C.byref(qs))
+        self.last_build_seconds, self.last_query_seconds = bs.value, qs.value
+        return idx, d2, cnt, found
+
+
+def load_port():
+    return Port()
+
+
+def load_ref(double_trig=False):
+    """Returns None where oracle/_ref was never built (no /root/reference on that machine)."""
+    try:
+        return Ref(double_trig)
+    except FileNotFoundError:
+        return None

@@ -1,0 +1,44 @@
+/* TEST INFRASTRUCTURE ONLY (oracle). CPU restatement of the reference's algorithms for the
+ * costmap-parallel hot path. Only tests/, __graft_entry__.smoke() and bench.py's CPU baseline may
+ * use it; the product library never links or loads it.
+ *
+ * Pinning status: the reference has no tests, golden vectors or fixtures, so this
+ * restatement is pinned against the reference's OWN sources compiled unmodified into
+ * oracle/_ref/libpp_ref.so (oracle/Makefile) -- tests/test_oracle.py compares the two on seeded
+ * inputs and against the fixtures in tests/golden/ that gen_golden.py produced from _ref.
+ */
+#ifndef PP_ORACLE_PORT_H
+#define PP_ORACLE_PORT_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+int port_footprint_points(double resolution, const float *boundary, int nb, int hole, int32_t *out_xy, int max_pts);
+
+int port_se2_volume(const uint8_t *cost, uint32_t W, uint32_t H, const int32_t *pts_xy, int P, uint32_t n_theta,
+                    float ox, float oy, float ot, uint32_t t0, uint32_t t1, uint32_t y0, uint32_t y1, uint8_t *out,
+                    int nthreads, int trig_double);
+
+int port_footprint_cost_batch(const uint8_t *cost, uint32_t W, uint32_t H, const int32_t *pts_xy, int P,
+                              const float *poses_xyt, uint32_t n, float *cost_out, uint8_t *flag_out,
+                              uint8_t *collision_out, int trig_double);
+
+int port_heuristic(const uint8_t *cost, uint32_t W, uint32_t H, float start_x, float start_y, float goal_x,
+                   float goal_y, float cost_penalty, const float *queries_xy, uint32_t n_queries, float *query_out,
+                   float *table_out);
+
+int port_heuristic_fixed_point(const uint8_t *cost, uint32_t W, uint32_t H, uint32_t goal_x, uint32_t goal_y,
+                               float cost_penalty, float *field_out);
+
+int port_extract_obstacles(const uint8_t *cost, uint32_t W, uint32_t H, double res, double origin_x, double origin_y,
+                           double robot_x, double robot_y, double robot_theta, double max_follow_range,
+                           double behind_ignore_range, double *pts_out, uint32_t max_pts);
+
+int port_radius_topk(const double *pts_xy, uint32_t N, const double *q_xy, uint32_t Q, double radius_arg, uint32_t K,
+                     uint32_t *idx_out, double *d2_out, uint32_t *cnt_out, uint32_t *found_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
