@@ -1,0 +1,174 @@
+/* pp_b200.h -- C ABI of libpp_b200.so: the costmap-parallel hot path of liangheming/path_planner,
+ * built from scratch for NVIDIA B200 (sm_100a).
+ *
+ * The reference has no plugin / FFI seam for this path: it is reached through three source-level
+ * C++ surfaces. Each entry point below names the reference interface it replaces,
+ * as file:line relative to the reference repository root.
+ *
+ * Conventions
+ *   - plain C types only; every function returns pp_status (0 = PP_OK) unless stated;
+ *   - pp_last_error(h) gives the text of the last failure on that handle;
+ *   - the caller owns all host buffers; the library owns all device buffers for the lifetime of
+ *     the handle; one handle per (thread, device) -- a handle is not thread-safe;
+ *   - all work is issued on the handle's own CUDA stream; calls that return data in host
+ *     buffers synchronise that stream before returning, the others are asynchronous;
+ *   - there is no CPU fallback: without a CUDA device pp_create fails.
+ */
+#ifndef PP_B200_H
+#define PP_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct pp_ctx *pp_handle;
+typedef int pp_status;
+
+enum
+{
+    PP_OK = 0,
+    PP_ERR_INVALID = 1, /* bad argument */
+    PP_ERR_STATE = 2,   /* call order: e.g. volume build before costmap upload */
+    PP_ERR_CUDA = 3,    /* a CUDA runtime call failed; text in pp_last_error */
+    PP_ERR_RANGE = 4,   /* size beyond a documented limit */
+    PP_ERR_COMM = 5     /* NCCL / peer-access failure */
+};
+
+/* cost values the path depends on (costmap_2d/cost_values.h, used at collision_checker.cpp:138,163,165) */
+#define PP_COST_FREE 0
+#define PP_COST_INSCRIBED 253
+#define PP_COST_LETHAL 254
+#define PP_COST_NO_INFORMATION 255
+
+const char *pp_version(void);
+pp_status pp_create(pp_handle *out, int device);
+pp_status pp_destroy(pp_handle h);
+const char *pp_last_error(pp_handle h);
+/* Block until everything issued on the handle's stream has finished. */
+pp_status pp_sync(pp_handle h);
+
+/* Page-locked host memory for callers that want the asynchronous copies to be true DMA. */
+pp_status pp_host_alloc(void **out, size_t bytes);
+pp_status pp_host_free(void *p);
+
+/* Measurement helpers (no counterpart in the reference):
+ *   pp_timer_start/stop  CUDA-event stopwatch on the handle's stream (what bench.py times with)
+ *   pp_l2_flush          overwrite a scratch buffer of `bytes` (> L2 size) on the handle's stream
+ *                        so that the next kernel starts with a cold L2
+ *   pp_launch_count      number of this library's kernels launched on the handle so far */
+pp_status pp_timer_start(pp_handle h);
+pp_status pp_timer_stop(pp_handle h, float *elapsed_ms); /* synchronises */
+pp_status pp_l2_flush(pp_handle h, size_t bytes);
+pp_status pp_launch_count(pp_handle h, uint64_t *count_out);
+
+/* ---- K0: costmap upload ---------------------------------------------------------------------
+ * Replaces the direct reads of costmap_2d::Costmap2D the reference does at
+ * collision_checker.cpp:129-138,162,208 and teb_follower.cpp:143-155: the grid
+ * (Costmap2D::getCharMap(), row-major my*W+mx) is copied to the device once per update instead.
+ * The reference takes no lock while costmap_2d mutates the grid on its own thread; callers
+ * should copy under costmap->getMutex().
+ *   pp_costmap_upload       whole grid; `host_is_pinned` != 0 skips the staging copy
+ *   pp_costmap_update_rect  rows [y0,y0+h) x cols [x0,x0+w) from `src` (src_pitch bytes per row);
+ *                           the rectangle is merged into the handle's dirty region
+ *   pp_costmap_download     device grid back to the host (tests)
+ */
+pp_status pp_costmap_upload(pp_handle h, const uint8_t *host, uint32_t W, uint32_t H, int host_is_pinned);
+pp_status pp_costmap_update_rect(pp_handle h, uint32_t x0, uint32_t y0, uint32_t w, uint32_t hgt, const uint8_t *src,
+                                 size_t src_pitch);
+pp_status pp_costmap_download(pp_handle h, uint8_t *host_out);
+
+/* ---- footprint ------------------------------------------------------------------------------
+ * Replaces CollisionChecker::initBoundary (collision_checker.cpp:3-81, dispatch :72-81) and
+ * setHole (collision_checker.h:14). `boundary` holds 1 number (circle radius), 2 (width, height)
+ * or 4 (x_min, y_min, x_max, y_max) in metres; offsets are integer cells, produced x-outer /
+ * y-inner exactly as the reference loops do. Unlike the reference, which appends to its point
+ * list on every call, these calls REPLACE the footprint.
+ * pp_footprint_set takes an arbitrary offset list (any rasterised polygon), P <= 4096.
+ */
+pp_status pp_footprint_from_boundary(pp_handle h, double resolution, const float *boundary, int n_boundary, int hole);
+pp_status pp_footprint_set(pp_handle h, const int32_t *offsets_xy, uint32_t P);
+pp_status pp_footprint_get(pp_handle h, int32_t *offsets_xy_out, uint32_t max_points, uint32_t *P_out);
+
+/* ---- K1: SE2 footprint-collision volume -----------------------------------------------------
+ * Replaces per-pose CollisionChecker::checkAndGetFootprintCost (collision_checker.cpp:144-172)
+ * as called from AstarHybrid::getNeighbors (astar_hybrid.cpp:283) and isInputValid (:37,:40).
+ * V[t][iy][ix] = (uint8) cost that function returns at x = fl(ix+ox), y = fl(iy+oy),
+ * theta = fl(fl(t+ot) * bin), bin = 2.0f*(float)M_PI/(float)n_theta (motion_hybrid.cpp:10);
+ * the collision flag it returns equals V >= 253. Layout [t][y][x], x fastest, one byte per cell.
+ * Bit-exact with the reference's float code path (cosf/sinf from the host libm, no FMA).
+ *   pp_se2_volume_build    compute heading bins [t_begin, t_end) of an n_theta-bin volume
+ *   pp_se2_volume_refresh  recompute only the dirty region (grown by the footprint reach) for
+ *                          the bins of the last build, then clear the dirty region
+ *   pp_se2_volume_download copy bins [t_begin, t_end) to `host_out` ((t_end-t_begin)*H*W bytes)
+ *   pp_se2_volume_ptr      device address of bin 0 (for zero-copy consumers and NCCL)
+ */
+pp_status pp_se2_volume_build(pp_handle h, uint32_t n_theta, float ox, float oy, float ot, uint32_t t_begin,
+                              uint32_t t_end);
+pp_status pp_se2_volume_refresh(pp_handle h);
+pp_status pp_se2_volume_download(pp_handle h, uint32_t t_begin, uint32_t t_end, uint8_t *host_out,
+                                 int host_is_pinned);
+pp_status pp_se2_volume_ptr(pp_handle h, const uint8_t **device_ptr_out, uint64_t *bytes_out);
+/* Which kernel variant pp_se2_volume_build uses: 0 = automatic, 1 = force the generic exact
+ * gather everywhere (used by tests to cross-check the tiled fast path against it). */
+pp_status pp_se2_volume_set_mode(pp_handle h, int mode);
+/* Counters of the last build: tiles done by the fast path / by the exact generic path, and the
+ * mean number of shared-memory samples per output of the fast path. */
+pp_status pp_se2_volume_stats(pp_handle h, uint64_t *fast_tiles, uint64_t *generic_tiles, double *samples_per_cell);
+
+/* ---- K1b: batched footprint cost at arbitrary poses ------------------------------------------
+ * Replaces CollisionChecker::checkAndGetFootprintCost (collision_checker.cpp:144-172) and
+ * checkFootPrintCollision (:126-142, called per analytic-expansion sample at
+ * astar_hybrid.cpp:325) for poses that are not bin-aligned. poses_xyt = n x (x, y, theta), x and y
+ * in cell units, theta in radians. cost_out[i] is the float the reference stores (0..255),
+ * flag_out[i] its boolean (also the value checkFootPrintCollision returns).
+ */
+pp_status pp_footprint_cost_batch(pp_handle h, const float *poses_xyt, uint32_t n, float *cost_out,
+                                  uint8_t *flag_out);
+
+/* ---- K2: obstacle-aware 2D heuristic field ---------------------------------------------------
+ * Replaces AstarHybrid::cacheObstacleHeuristic (astar_hybrid.cpp:97-165) and the lazy resume in
+ * getObstacleHeuristic (:184-239): the whole goal-rooted field is built at once, so every later
+ * lookup is the table hit at :182-183. F[y][x] = converged value of the reference recurrence
+ * (h(goal) = 1e-5f, 8-connected, travel cost of :151, border cells and cost >= 253 never
+ * entered); unreachable cells are 0, like the reference's unseen entries.
+ * `field_out` may be NULL (keep the field on the device; see pp_heuristic_ptr).
+ */
+pp_status pp_heuristic_build(pp_handle h, uint32_t goal_x, uint32_t goal_y, float cost_penalty, float *field_out);
+pp_status pp_heuristic_ptr(pp_handle h, const float **device_ptr_out);
+pp_status pp_heuristic_stats(pp_handle h, uint32_t *rounds, uint64_t *tile_visits);
+
+/* ---- K3: TEB obstacle association -----------------------------------------------------------
+ * pp_obstacles_extract replaces TebFollower::addObstacles (teb_follower.cpp:140-169): all cells
+ * with cost >= 253, as world points (cell centres), filtered by the +-1.2*max_follow_range box
+ * and the behind-the-robot rule, in the reference's x-outer / y-inner order. The points stay on
+ * the device for pp_radius_topk; pts_out (max_points x 2 doubles) may be NULL.
+ * pp_radius_topk replaces KDTree2D::buildIndex + radiusSearch + keep-first-K
+ * (teb_optimizer.h:29, teb_optimizer.cpp:294-311; nanoflann.hpp:1747-1758): per query all points
+ * with d2 < radius_arg (strict; radius_arg is compared against SQUARED distances, exactly as the
+ * reference passes it), ascending by d2, first min(K, found) kept, K <= 64. pts_xy == NULL uses
+ * the points of the last pp_obstacles_extract. Equal distances are ordered by point index (the
+ * reference's order among ties is unspecified).
+ */
+pp_status pp_obstacles_extract(pp_handle h, double resolution, double origin_x, double origin_y, double robot_x,
+                               double robot_y, double robot_theta, double max_follow_range,
+                               double behind_ignore_range, double *pts_out, uint32_t max_points, uint32_t *n_out);
+pp_status pp_radius_topk(pp_handle h, const double *pts_xy, uint32_t N, const double *queries_xy, uint32_t Q,
+                         double radius_arg, uint32_t K, uint32_t *idx_out, double *d2_out, uint32_t *cnt_out);
+
+/* ---- multi-GPU: heading-sharded volume --------------------------------------------------------
+ * No counterpart in the reference (single process, single thread). Rank g of `world` builds bins
+ * [g*n_theta/world, (g+1)*n_theta/world) and pp_se2_volume_allgather exchanges the slabs in place
+ * with ncclAllGather so that every rank holds the whole volume.
+ */
+#define PP_COMM_ID_BYTES 128
+pp_status pp_comm_unique_id(void *id_out);
+pp_status pp_comm_init(pp_handle h, const void *id, int rank, int world);
+pp_status pp_se2_volume_allgather(pp_handle h);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PP_B200_H */

@@ -1,0 +1,282 @@
+"""ctypes binding of libpp_b200.so (include/pp_b200.h) for the test-suite and bench.py.
+
+This is harness code: the product is the shared library and the C++ host classes in
+path_planner_b200/host/. There is no fallback of any kind -- if the library is missing, or no
+CUDA device is present, loading or pp_create fails loudly.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libpp_b200.so")
+
+# every symbol include/pp_b200.h declares
+SYMBOLS = [
+    "pp_version", "pp_create", "pp_destroy", "pp_last_error", "pp_sync", "pp_host_alloc", "pp_host_free",
+    "pp_timer_start", "pp_timer_stop", "pp_l2_flush", "pp_launch_count", "pp_costmap_upload", "pp_costmap_update_rect", "pp_costmap_download",
+    "pp_footprint_from_boundary", "pp_footprint_set", "pp_footprint_get", "pp_se2_volume_build",
+    "pp_se2_volume_refresh", "pp_se2_volume_download", "pp_se2_volume_ptr", "pp_se2_volume_set_mode",
+    "pp_se2_volume_stats", "pp_footprint_cost_batch", "pp_heuristic_build", "pp_heuristic_ptr", "pp_heuristic_stats",
+    "pp_obstacles_extract", "pp_radius_topk", "pp_comm_unique_id", "pp_comm_init", "pp_se2_volume_allgather",
+]
+
+_vp = C.c_void_p
+_u32 = C.c_uint32
+_lib = None
+
+
+class PPError(RuntimeError):
+    def __init__(self, status, message):
+        super().__init__(f"pp_b200 status {status}: {message}")
+        self.status = status
+
+
+def load():
+    """Load libpp_b200.so. Raises if it has not been built (python -c 'import __graft_entry__ as g; g.build()')."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(f"{LIB_PATH} is missing: build it first (make -C path_planner_b200/csrc); "
+                          "there is no CPU or PyTorch fallback for this library")
+    L = C.CDLL(LIB_PATH)
+    L.pp_version.restype = C.c_char_p
+    L.pp_last_error.restype = C.c_char_p
+    L.pp_last_error.argtypes = [_vp]
+    L.pp_create.argtypes = [C.POINTER(_vp), C.c_int]
+    L.pp_destroy.argtypes = [_vp]
+    L.pp_sync.argtypes = [_vp]
+    L.pp_host_alloc.argtypes = [C.POINTER(_vp), C.c_size_t]
+    L.pp_host_free.argtypes = [_vp]
+    L.pp_timer_start.argtypes = [_vp]
+    L.pp_timer_stop.argtypes = [_vp, C.POINTER(C.c_float)]
+    L.pp_l2_flush.argtypes = [_vp, C.c_size_t]
+    L.pp_launch_count.argtypes = [_vp, C.POINTER(C.c_uint64)]
+    L.pp_costmap_upload.argtypes = [_vp, _vp, _u32, _u32, C.c_int]
+    L.pp_costmap_update_rect.argtypes = [_vp, _u32, _u32, _u32, _u32, _vp, C.c_size_t]
+    L.pp_costmap_download.argtypes = [_vp, _vp]
+    L.pp_footprint_from_boundary.argtypes = [_vp, C.c_double, _vp, C.c_int, C.c_int]
+    L.pp_footprint_set.argtypes = [_vp, _vp, _u32]
+    L.pp_footprint_get.argtypes = [_vp, _vp, _u32, C.POINTER(_u32)]
+    L.pp_se2_volume_build.argtypes = [_vp, _u32, C.c_float, C.c_float, C.c_float, _u32, _u32]
+    L.pp_se2_volume_refresh.argtypes = [_vp]
+    L.pp_se2_volume_download.argtypes = [_vp, _u32, _u32, _vp, C.c_int]
+    L.pp_se2_volume_ptr.argtypes = [_vp, C.POINTER(_vp), C.POINTER(C.c_uint64)]
+    L.pp_se2_volume_set_mode.argtypes = [_vp, C.c_int]
+    L.pp_se2_volume_stats.argtypes = [_vp, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), C.POINTER(C.c_double)]
+    L.pp_footprint_cost_batch.argtypes = [_vp, _vp, _u32, _vp, _vp]
+    L.pp_heuristic_build.argtypes = [_vp, _u32, _u32, C.c_float, _vp]
+    L.pp_heuristic_ptr.argtypes = [_vp, C.POINTER(_vp)]
+    L.pp_heuristic_stats.argtypes = [_vp, C.POINTER(_u32), C.POINTER(C.c_uint64)]
+    L.pp_obstacles_extract.argtypes = [_vp] + [C.c_double] * 8 + [_vp, _u32, C.POINTER(_u32)]
+    L.pp_radius_topk.argtypes = [_vp, _vp, _u32, _vp, _u32, C.c_double, _u32, _vp, _vp, _vp]
+    L.pp_comm_unique_id.argtypes = [_vp]
+    L.pp_comm_init.argtypes = [_vp, _vp, C.c_int, C.c_int]
+    L.pp_se2_volume_allgather.argtypes = [_vp]
+    _lib = L
+    return L
+
+
+def _ptr(a):
+    return None if a is None else a.ctypes.data_as(_vp)
+
+
+class PinnedBuffer:
+    """numpy view of page-locked memory from pp_host_alloc."""
+
+    def __init__(self, nbytes):
+        L = load()
+        p = _vp()
+        st = L.pp_host_alloc(C.byref(p), nbytes)
+        if st != 0:
+            raise PPError(st, "pp_host_alloc failed")
+        self._p = p
+        self.nbytes = nbytes
+        self.array = np.ctypeslib.as_array((C.c_uint8 * nbytes).from_address(p.value))
+
+    def free(self):
+        if self._p:
+            load().pp_host_free(self._p)
+            self._p = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+
+class Handle:
+    """One pp_handle. Method names follow the C entry points without the pp_ prefix."""
+
+    def __init__(self, device=0):
+        self.L = load()
+        self.h = _vp()
+        st = self.L.pp_create(C.byref(self.h), device)
+        if st != 0:
+            raise PPError(st, "pp_create failed (no CUDA device? this library has no CPU path)")
+        self.W = self.H = 0
+        self.n_theta = 0
+
+    def close(self):
+        if self.h:
+            self.L.pp_destroy(self.h)
+            self.h = _vp()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _ck(self, st):
+        if st != 0:
+            raise PPError(st, self.L.pp_last_error(self.h).decode())
+
+    def sync(self):
+        self._ck(self.L.pp_sync(self.h))
+
+    def timer_start(self):
+        self._ck(self.L.pp_timer_start(self.h))
+
+    def timer_stop(self):
+        ms = C.c_float(0)
+        self._ck(self.L.pp_timer_stop(self.h, C.byref(ms)))
+        return ms.value
+
+    def l2_flush(self, nbytes=256 << 20):
+        self._ck(self.L.pp_l2_flush(self.h, nbytes))
+
+    def launch_count(self):
+        n = C.c_uint64(0)
+        self._ck(self.L.pp_launch_count(self.h, C.byref(n)))
+        return n.value
+
+    # K0
+    def costmap_upload(self, cost, pinned=False):
+        assert cost.dtype == np.uint8 and cost.ndim == 2 and cost.flags.c_contiguous
+        self.H, self.W = cost.shape
+        self._ck(self.L.pp_costmap_upload(self.h, _ptr(cost), self.W, self.H, int(pinned)))
+
+    def costmap_update_rect(self, x0, y0, patch):
+        assert patch.dtype == np.uint8 and patch.ndim == 2
+        patch = np.ascontiguousarray(patch)
+        hgt, w = patch.shape
+        self._ck(self.L.pp_costmap_update_rect(self.h, x0, y0, w, hgt, _ptr(patch), w))
+
+    def costmap_download(self):
+        out = np.empty((self.H, self.W), np.uint8)
+        self._ck(self.L.pp_costmap_download(self.h, _ptr(out)))
+        return out
+
+    # footprint
+    def footprint_from_boundary(self, resolution, boundary, hole):
+        b = np.ascontiguousarray(boundary, np.float32)
+        self._ck(self.L.pp_footprint_from_boundary(self.h, resolution, _ptr(b), len(b), int(hole)))
+
+    def footprint_set(self, offsets):
+        o = np.ascontiguousarray(offsets, np.int32)
+        self._ck(self.L.pp_footprint_set(self.h, _ptr(o), len(o)))
+
+    def footprint_get(self):
+        n = _u32(0)
+        self._ck(self.L.pp_footprint_get(self.h, None, 0, C.byref(n)))
+        out = np.zeros((n.value, 2), np.int32)
+        self._ck(self.L.pp_footprint_get(self.h, _ptr(out), n.value, C.byref(n)))
+        return out
+
+    # K1
+    def se2_volume_build(self, n_theta, ox=0.5, oy=0.5, ot=0.0, t_begin=0, t_end=None):
+        t_end = n_theta if t_end is None else t_end
+        self.n_theta = n_theta
+        self._ck(self.L.pp_se2_volume_build(self.h, n_theta, ox, oy, ot, t_begin, t_end))
+
+    def se2_volume_refresh(self):
+        self._ck(self.L.pp_se2_volume_refresh(self.h))
+
+    def se2_volume_download(self, t_begin=0, t_end=None, out=None, pinned=False):
+        t_end = self.n_theta if t_end is None else t_end
+        if out is None:
+            out = np.empty((t_end - t_begin, self.H, self.W), np.uint8)
+        self._ck(self.L.pp_se2_volume_download(self.h, t_begin, t_end, _ptr(out), int(pinned)))
+        return out
+
+    def se2_volume_ptr(self):
+        p = _vp()
+        n = C.c_uint64(0)
+        self._ck(self.L.pp_se2_volume_ptr(self.h, C.byref(p), C.byref(n)))
+        return p.value, n.value
+
+    def se2_volume_set_mode(self, mode):
+        self._ck(self.L.pp_se2_volume_set_mode(self.h, mode))
+
+    def se2_volume_stats(self):
+        a, b, s = C.c_uint64(0), C.c_uint64(0), C.c_double(0)
+        self._ck(self.L.pp_se2_volume_stats(self.h, C.byref(a), C.byref(b), C.byref(s)))
+        return {"fast_tiles": a.value, "generic_tiles": b.value, "samples_per_cell": s.value}
+
+    # K1b
+    def footprint_cost_batch(self, poses):
+        poses = np.ascontiguousarray(poses, np.float32)
+        n = len(poses)
+        cost = np.zeros(n, np.float32)
+        flag = np.zeros(n, np.uint8)
+        self._ck(self.L.pp_footprint_cost_batch(self.h, _ptr(poses), n, _ptr(cost), _ptr(flag)))
+        return cost, flag
+
+    # K2
+    def heuristic_build(self, goal_x, goal_y, cost_penalty, download=True):
+        out = np.empty((self.H, self.W), np.float32) if download else None
+        self._ck(self.L.pp_heuristic_build(self.h, goal_x, goal_y, cost_penalty, _ptr(out)))
+        return out
+
+    def heuristic_stats(self):
+        r, v = _u32(0), C.c_uint64(0)
+        self._ck(self.L.pp_heuristic_stats(self.h, C.byref(r), C.byref(v)))
+        return {"rounds": r.value, "tile_visits": v.value}
+
+    # K3
+    def obstacles_extract(self, resolution, origin, robot_pose, max_follow_range, behind_ignore_range, download=True):
+        n = _u32(0)
+        self._ck(self.L.pp_obstacles_extract(self.h, resolution, origin[0], origin[1], robot_pose[0], robot_pose[1],
+                                             robot_pose[2], max_follow_range, behind_ignore_range, None, 0, C.byref(n)))
+        if not download:
+            return n.value
+        out = np.empty((n.value, 2), np.float64)
+        if n.value:
+            self._ck(self.L.pp_obstacles_extract(self.h, resolution, origin[0], origin[1], robot_pose[0], robot_pose[1],
+                                                 robot_pose[2], max_follow_range, behind_ignore_range, _ptr(out),
+                                                 n.value, C.byref(n)))
+        return out
+
+    def radius_topk(self, pts, queries, radius_arg, K):
+        queries = np.ascontiguousarray(queries, np.float64)
+        Q = len(queries)
+        N = 0
+        if pts is not None:
+            pts = np.ascontiguousarray(pts, np.float64)
+            N = len(pts)
+        idx = np.zeros((Q, K), np.uint32)
+        d2 = np.zeros((Q, K), np.float64)
+        cnt = np.zeros(Q, np.uint32)
+        self._ck(self.L.pp_radius_topk(self.h, _ptr(pts), N, _ptr(queries), Q, radius_arg, K, _ptr(idx), _ptr(d2),
+                                       _ptr(cnt)))
+        return idx, d2, cnt
+
+    # multi-GPU
+    def comm_init(self, uid_bytes, rank, world):
+        buf = C.create_string_buffer(bytes(uid_bytes), 128)
+        self._ck(self.L.pp_comm_init(self.h, buf, rank, world))
+
+    def se2_volume_allgather(self):
+        self._ck(self.L.pp_se2_volume_allgather(self.h))
+
+
+def comm_unique_id():
+    buf = C.create_string_buffer(128)
+    st = load().pp_comm_unique_id(buf)
+    if st != 0:
+        raise PPError(st, "pp_comm_unique_id failed")
+    return buf.raw

@@ -1,0 +1,261 @@
+// K2: obstacle-aware 2D heuristic field (see include/pp_b200.h).
+//
+// The reference grows the field lazily with a heap (astar_hybrid.cpp:97-241). Its recurrence is
+//   d[goal] = 1e-5f                                                       (:117, sign-encoded)
+//   d[v]    = min over 8 neighbours u of  fl( d[u] + travel(u->v) )        (:151-158)
+//   travel  = (straight ? 1.0f : sqrtf(2.0f)) * (1.0f + (cost_penalty * cost[v] / 252.0f))
+// where v must be an interior cell (:141) with cost[v] < 253 (:143-145). Float addition is
+// monotone, so this system has one least fixed point, independent of relaxation order; here it is
+// reached by tiled chaotic relaxation: each active 32x32 tile is staged in shared memory with a
+// one-cell halo, relaxed in place until nothing in it changes (per-tile convergence flag via
+// __syncthreads_or), written back, and the tiles across any border that changed are flagged for
+// the next round. min_u fl(d[u] + w) == fl(min_u d[u] + w), so the 4 straight and the 4 diagonal
+// neighbours are min-reduced first and each class costs one rounded addition. The travel weights
+// come from a 2x256 table evaluated on the host with the reference's exact float expression.
+#include "pp_internal.h"
+
+#include <cmath>
+#include <limits>
+#include <vector>
+
+namespace
+{
+constexpr int HT = 32;            // tile edge
+constexpr int HT_THREADS = 256;   // 4 cells per thread
+constexpr int HT_PITCH = HT + 2 + 1;
+constexpr int ROUNDS_PER_CHECK = 8;
+
+__global__ void heur_init_kernel(float *field, size_t n, uint32_t *flags, size_t n_flags, uint32_t goal_index,
+                                 uint32_t goal_tile)
+{
+    const size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x;
+    const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+    for (size_t k = i; k < n; k += stride)
+        field[k] = (k == goal_index) ? 0.00001f : __int_as_float(0x7f800000);
+    for (size_t k = i; k < n_flags; k += stride)
+        flags[k] = 0;
+    if (i == 0)
+    {
+        flags[goal_tile] = 1;  // generation 0
+    }
+}
+
+// flags layout: [0, nT) generation 0, [nT, 2nT) generation 1, then 4 round counters
+__global__ void __launch_bounds__(HT_THREADS) heur_round_kernel(float *__restrict__ field, const uint8_t *__restrict__ cost,
+                                                                const float *__restrict__ travel, uint32_t W, uint32_t H,
+                                                                uint32_t tiles_x, uint32_t tiles_y, uint32_t *flags,
+                                                                uint32_t round)
+{
+    const uint32_t nT = tiles_x * tiles_y;
+    uint32_t *cur = flags + (round & 1) * nT;
+    uint32_t *nxt = flags + ((round + 1) & 1) * nT;
+    uint32_t *counters = flags + 2 * nT;
+    const uint32_t tile = blockIdx.x;
+    if (tile == 0 && threadIdx.x == 0)
+        counters[(round + 2) & 3] = 0;  // will count the tiles flagged during round+1
+    if (cur[tile] == 0)
+        return;
+    __shared__ float F[HT + 2][HT_PITCH];
+    __shared__ float WS[HT][HT];
+    __shared__ float WD[HT][HT];
+    __shared__ uint32_t edge_changed[8];
+
+    const uint32_t tx = tile % tiles_x, ty = tile / tiles_x;
+    const int x0 = static_cast<int>(tx * HT), y0 = static_cast<int>(ty * HT);
+    const int tid = threadIdx.x;
+    const float INF = __int_as_float(0x7f800000);
+    if (tid < 8)
+        edge_changed[tid] = 0;
+    for (int i = tid; i < (HT + 2) * (HT + 2); i += HT_THREADS)
+    {
+        const int r = i / (HT + 2), c = i - r * (HT + 2);
+        const int gy = y0 + r - 1, gx = x0 + c - 1;
+        float v = INF;
+        if (gy >= 0 && gy < static_cast<int>(H) && gx >= 0 && gx < static_cast<int>(W))
+            v = field[static_cast<size_t>(gy) * W + gx];
+        F[r][c] = v;
+    }
+    for (int i = tid; i < HT * HT; i += HT_THREADS)
+    {
+        const int r = i / HT, c = i - r * HT;
+        const int gy = y0 + r, gx = x0 + c;
+        float ws = INF, wd = INF;
+        // border cells are never entered (astar_hybrid.cpp:141), nor cells with cost >= 253 (:143)
+        if (gy > 0 && gy < static_cast<int>(H) - 1 && gx > 0 && gx < static_cast<int>(W) - 1)
+        {
+            const uint32_t cst = cost[static_cast<size_t>(gy) * W + gx];
+            ws = travel[cst];
+            wd = travel[256 + cst];
+        }
+        WS[r][c] = ws;
+        WD[r][c] = wd;
+    }
+    __syncthreads();
+
+    // thread owns cells (row, col0 + 8*k): consecutive lanes -> consecutive columns
+    const int col0 = tid & 7, rowq = tid >> 3;  // 8 columns phase x 32 rows
+    float init[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+        init[k] = F[rowq + 1][col0 + 8 * k + 1];
+
+    int changed;
+    do
+    {
+        int local = 0;
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+        {
+            const int r = rowq + 1, c = col0 + 8 * k + 1;
+            const float ms = fminf(fminf(F[r - 1][c], F[r + 1][c]), fminf(F[r][c - 1], F[r][c + 1]));
+            const float md = fminf(fminf(F[r - 1][c - 1], F[r + 1][c + 1]), fminf(F[r - 1][c + 1], F[r + 1][c - 1]));
+            const float cand = fminf(__fadd_rn(ms, WS[r - 1][c - 1]), __fadd_rn(md, WD[r - 1][c - 1]));
+            if (cand < F[r][c])
+            {
+                F[r][c] = cand;
+                local = 1;
+            }
+        }
+        changed = __syncthreads_or(local);
+    } while (changed);
+
+    // write back what changed and note which borders moved
+    cur[tile] = 0;  // benign if several threads do it; cleared for reuse two rounds later
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+    {
+        const int r = rowq, c = col0 + 8 * k;
+        const float v = F[r + 1][c + 1];
+        if (v < init[k])
+        {
+            const int gy = y0 + r, gx = x0 + c;
+            if (gy < static_cast<int>(H) && gx < static_cast<int>(W))
+                field[static_cast<size_t>(gy) * W + gx] = v;
+            if (r == 0) edge_changed[0] = 1;                       // N
+            if (r == HT - 1) edge_changed[1] = 1;                  // S
+            if (c == 0) edge_changed[2] = 1;                       // W
+            if (c == HT - 1) edge_changed[3] = 1;                  // E
+            if (r == 0 && c == 0) edge_changed[4] = 1;             // NW
+            if (r == 0 && c == HT - 1) edge_changed[5] = 1;        // NE
+            if (r == HT - 1 && c == 0) edge_changed[6] = 1;        // SW
+            if (r == HT - 1 && c == HT - 1) edge_changed[7] = 1;   // SE
+        }
+    }
+    __syncthreads();
+    if (tid < 8 && edge_changed[tid])
+    {
+        const int dxs[8] = {0, 0, -1, 1, -1, 1, -1, 1};
+        const int dys[8] = {-1, 1, 0, 0, -1, -1, 1, 1};
+        const int ntx = static_cast<int>(tx) + dxs[tid], nty = static_cast<int>(ty) + dys[tid];
+        if (ntx >= 0 && ntx < static_cast<int>(tiles_x) && nty >= 0 && nty < static_cast<int>(tiles_y))
+        {
+            const uint32_t nt = nty * tiles_x + ntx;
+            if (atomicExch(&nxt[nt], 1u) == 0u)
+                atomicAdd(&counters[(round + 1) & 3], 1u);
+        }
+    }
+}
+
+__global__ void heur_finalize_kernel(float *field, size_t n)
+{
+    const size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x;
+    const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+    for (size_t k = i; k < n; k += stride)
+        if (field[k] == __int_as_float(0x7f800000))
+            field[k] = 0.0f;  // unreachable: the reference leaves 0 (unseen) there
+}
+}  // namespace
+
+extern "C" {
+
+pp_status pp_heuristic_build(pp_handle h, uint32_t goal_x, uint32_t goal_y, float cost_penalty, float *field_out)
+{
+    if (!h)
+        return PP_ERR_INVALID;
+    PP_REQUIRE(h, h->d_cost, PP_ERR_STATE, "pp_heuristic_build: upload a costmap first");
+    PP_REQUIRE(h, goal_x < h->W && goal_y < h->H, PP_ERR_INVALID, "goal (%u,%u) outside %ux%u", goal_x, goal_y, h->W, h->H);
+    PP_CUDA(h, cudaSetDevice(h->device));
+    const uint32_t W = h->W, H = h->H;
+    const size_t n = static_cast<size_t>(W) * H;
+    const uint32_t tiles_x = (W + HT - 1) / HT, tiles_y = (H + HT - 1) / HT, nT = tiles_x * tiles_y;
+    const size_t n_flags = 2 * static_cast<size_t>(nT) + 4;
+    PP_CUDA(h, pp_reserve(h->d_field, h->field_cap, n));
+    PP_CUDA(h, pp_reserve(h->d_tile_flags, h->tile_flags_cap, n_flags));
+    size_t travel_cap = h->d_travel ? 512 : 0;
+    PP_CUDA(h, pp_reserve(h->d_travel, travel_cap, static_cast<size_t>(512)));
+
+    // travel-cost table with the reference's float expression and evaluation order (:151)
+    float travel[512];
+    const float sqrt_2 = sqrtf(2.0f);
+    for (int c = 0; c < 256; ++c)
+    {
+        const float cost = static_cast<float>(c);
+        const float scale = 1.0f + (cost_penalty * cost / 252.0f);
+        travel[c] = c >= PP_COST_INSCRIBED ? std::numeric_limits<float>::infinity() : 1.0f * scale;
+        travel[256 + c] = c >= PP_COST_INSCRIBED ? std::numeric_limits<float>::infinity() : sqrt_2 * scale;
+    }
+    PP_CUDA(h, cudaMemcpyAsync(h->d_travel, travel, sizeof(travel), cudaMemcpyHostToDevice, h->stream));
+    PP_CUDA(h, cudaStreamSynchronize(h->stream));  // `travel` lives on this stack frame
+
+    const uint32_t goal_index = goal_y * W + goal_x;
+    const uint32_t goal_tile = (goal_y / HT) * tiles_x + goal_x / HT;
+    heur_init_kernel<<<148 * 8, 256, 0, h->stream>>>(h->d_field, n, h->d_tile_flags, n_flags, goal_index, goal_tile);
+    h->launches++;
+    PP_CUDA(h, cudaGetLastError());
+
+    h->heur_rounds = 0;
+    h->heur_tile_visits = 0;
+    // every round moves information across at least one tile border, and a shortest path visits a
+    // cell at most once, so W*H rounds is a (very loose) hard bound
+    const uint64_t max_rounds = static_cast<uint64_t>(n) + 8;
+    uint32_t round = 0;
+    bool done = false;
+    while (!done)
+    {
+        for (int k = 0; k < ROUNDS_PER_CHECK; ++k, ++round)
+        {
+            heur_round_kernel<<<nT, HT_THREADS, 0, h->stream>>>(h->d_field, h->d_cost, h->d_travel, W, H, tiles_x, tiles_y,
+                                                                h->d_tile_flags, round);
+            h->launches++;
+        }
+        PP_CUDA(h, cudaGetLastError());
+        // counters[(round) & 3] holds the number of tiles flagged for the round that would run next
+        PP_CUDA(h, cudaMemcpyAsync(h->h_counter, h->d_tile_flags + 2 * static_cast<size_t>(nT), 4 * sizeof(uint32_t),
+                                   cudaMemcpyDeviceToHost, h->stream));
+        PP_CUDA(h, cudaStreamSynchronize(h->stream));
+        done = h->h_counter[round & 3] == 0;
+        PP_REQUIRE(h, round < max_rounds, PP_ERR_STATE, "pp_heuristic_build: relaxation did not converge");
+    }
+    h->heur_rounds = round;
+    heur_finalize_kernel<<<148 * 8, 256, 0, h->stream>>>(h->d_field, n);
+    h->launches++;
+    PP_CUDA(h, cudaGetLastError());
+    if (field_out)
+    {
+        PP_CUDA(h, cudaMemcpyAsync(field_out, h->d_field, n * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
+        PP_CUDA(h, cudaStreamSynchronize(h->stream));
+    }
+    return PP_OK;
+}
+
+pp_status pp_heuristic_ptr(pp_handle h, const float **device_ptr_out)
+{
+    if (!h || !device_ptr_out)
+        return PP_ERR_INVALID;
+    PP_REQUIRE(h, h->d_field, PP_ERR_STATE, "pp_heuristic_ptr: no field built");
+    *device_ptr_out = h->d_field;
+    return PP_OK;
+}
+
+pp_status pp_heuristic_stats(pp_handle h, uint32_t *rounds, uint64_t *tile_visits)
+{
+    if (!h)
+        return PP_ERR_INVALID;
+    if (rounds)
+        *rounds = h->heur_rounds;
+    if (tile_visits)
+        *tile_visits = h->heur_tile_visits;
+    return PP_OK;
+}
+
+}  // extern "C"

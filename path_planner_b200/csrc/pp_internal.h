@@ -1,0 +1,120 @@
+// Internal state of a pp_handle. Not part of the ABI.
+#pragma once
+#include "../../include/pp_b200.h"
+
+#include <cuda_runtime.h>
+#include <cstdio>
+#include <string>
+#include <vector>
+
+struct Se2Plan;  // se2_plan.h
+
+struct pp_ctx
+{
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev_start = nullptr, ev_stop = nullptr;
+    std::string err;
+    uint64_t launches = 0;  // kernels launched by this library on this handle
+    uint8_t *d_flush = nullptr;
+    size_t flush_cap = 0;
+
+    // K0 costmap
+    uint8_t *d_cost = nullptr;
+    size_t cost_cap = 0;
+    uint32_t W = 0, H = 0;
+    uint8_t *h_stage = nullptr;  // pinned staging
+    size_t stage_cap = 0;
+    bool dirty = false;
+    uint32_t dirty_x0 = 0, dirty_y0 = 0, dirty_x1 = 0, dirty_y1 = 0;  // half-open
+
+    // footprint
+    std::vector<int32_t> fp;  // x0,y0,x1,y1,...
+    int32_t *d_fp = nullptr;
+    size_t fp_cap = 0;
+    int reach = 0;  // ceil(max |p|) in cells
+
+    // K1 volume
+    uint8_t *d_vol = nullptr;
+    size_t vol_cap = 0;
+    uint32_t n_theta = 0, t_begin = 0, t_end = 0;
+    float ox = 0.5f, oy = 0.5f, ot = 0.0f;
+    bool vol_valid = false;
+    float2 *d_trig = nullptr;  // (cos, sin) per heading bin, from the host libm
+    size_t trig_cap = 0;
+    std::vector<float2> host_trig;
+    int vol_mode = 0;
+    uint64_t stat_fast_tiles = 0, stat_generic_tiles = 0;
+    double stat_samples_per_cell = 0.0;
+    Se2Plan *plan = nullptr;
+
+    // K2 heuristic
+    float *d_field = nullptr;
+    size_t field_cap = 0;
+    uint32_t *d_tile_flags = nullptr;  // two generations of per-tile activity flags + counters
+    size_t tile_flags_cap = 0;
+    float *d_travel = nullptr;  // 2 x 256 travel-cost table (straight, diagonal)
+    uint32_t *h_counter = nullptr;  // pinned
+    uint32_t heur_rounds = 0;
+    uint64_t heur_tile_visits = 0;
+
+    // K3 TEB
+    double *d_pts = nullptr;
+    size_t pts_cap = 0;
+    uint32_t n_pts = 0;
+    uint32_t *d_col_counts = nullptr;
+    size_t col_cap = 0;
+    double *d_queries = nullptr;
+    size_t q_cap = 0;
+    uint32_t *d_topk_idx = nullptr;
+    double *d_topk_d2 = nullptr;
+    uint32_t *d_topk_cnt = nullptr;
+    size_t topk_cap = 0, topk_q_cap = 0;
+
+    // multi-GPU
+    void *comm = nullptr;  // ncclComm_t
+    int rank = 0, world = 1;
+};
+
+pp_status pp_fail(pp_handle h, pp_status code, const char *fmt, ...);
+
+#define PP_CUDA(h, call)                                                                             \
+    do                                                                                               \
+    {                                                                                                \
+        cudaError_t _e = (call);                                                                     \
+        if (_e != cudaSuccess)                                                                       \
+            return pp_fail((h), PP_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(_e), \
+                           __FILE__, __LINE__);                                                      \
+    } while (0)
+
+#define PP_REQUIRE(h, cond, code, ...)            \
+    do                                            \
+    {                                             \
+        if (!(cond))                              \
+            return pp_fail((h), (code), __VA_ARGS__); \
+    } while (0)
+
+// grow-only device buffer helper
+template <class T>
+inline cudaError_t pp_reserve(T *&ptr, size_t &cap, size_t need)
+{
+    if (need <= cap && ptr)
+        return cudaSuccess;
+    if (ptr)
+    {
+        cudaError_t e = cudaFree(ptr);
+        if (e != cudaSuccess)
+            return e;
+        ptr = nullptr;
+        cap = 0;
+    }
+    cudaError_t e = cudaMalloc(reinterpret_cast<void **>(&ptr), need * sizeof(T));
+    if (e == cudaSuccess)
+        cap = need;
+    return e;
+}
+
+// implemented per kernel file
+pp_status pp_se2_launch(pp_handle h, uint32_t x0, uint32_t y0, uint32_t x1, uint32_t y1);
+void pp_se2_plan_free(pp_handle h);
+void pp_comm_destroy(pp_handle h);

@@ -1,0 +1,10 @@
+// Internal: interface between the volume driver (se2_volume.cu) and the tiled fast path
+// (se2_fast.cu). Not part of the ABI.
+#pragma once
+#include "pp_internal.h"
+
+// returned by pp_se2_launch_fast when it leaves the whole region to the generic kernel
+constexpr pp_status PP_INTERNAL_DECLINED = 1002;
+
+pp_status pp_se2_launch_fast(pp_handle h, uint32_t x0, uint32_t y0, uint32_t x1, uint32_t y1);
+pp_status pp_se2_generic_worklist(pp_handle h, const uint32_t *d_worklist, uint32_t n_work);

@@ -1,0 +1,350 @@
+// K1: SE2 footprint-collision volume (see include/pp_b200.h).
+//
+// se2_generic_kernel is the exact table-free path: it evaluates the reference expression
+//   x_new = (x + px*cos) - py*sin ,  y_new = (y + px*sin) + py*cos ,  idx = floor(.)
+// (collision_checker.cpp:155-158) per footprint point and per tile column / tile row with
+// separately rounded IEEE operations (__fmul_rn/__fadd_rn/__fsub_rn: no FMA contraction, like the
+// reference build) and cos/sin supplied by the host libm, so indices are bit-identical to the
+// reference for every cell, including the cells where float rounding makes the integer offset
+// depend on the position. Because x_new depends only on (column, point, bin)
+// and y_new only on (row, point, bin), the offsets are tabulated once per tile in shared memory.
+// Out-of-map samples are ignored by the reference (:160); here the tile is staged with zeros
+// outside the map, which is the identity of max over uint8.
+#include "pp_internal.h"
+#include "se2_plan.h"
+
+#include <cmath>
+#include <algorithm>
+
+namespace
+{
+constexpr int GT_W = 64;        // tile width  (outputs)
+constexpr int GT_H = 32;        // tile height (outputs)
+constexpr int GT_THREADS = 256;
+constexpr int GT_ROWS_PER_THREAD = GT_H / (GT_THREADS / GT_W);  // 8
+constexpr int GT_PCHUNK = 256;  // footprint points tabulated per pass
+
+struct GenericArgs
+{
+    const uint8_t *cost;
+    uint8_t *vol;
+    const float2 *trig;
+    const int32_t *fp;
+    uint32_t W, H, P;
+    int R;
+    float ox, oy;
+    uint32_t t_begin, t_end, t_per_cta;
+    uint32_t x0, y0, x1, y1;
+    const uint32_t *worklist;  // optional: pairs (tile_x | tile_y << 16, t)
+};
+
+__global__ void __launch_bounds__(GT_THREADS) se2_generic_kernel(GenericArgs a)
+{
+    extern __shared__ __align__(16) uint8_t smem[];
+    const int R = a.R;
+    const int pitch = (GT_W + 2 * R + 3) & ~3;
+    const int rows = GT_H + 2 * R;
+    uint8_t *tile = smem;
+    int8_t *xo = reinterpret_cast<int8_t *>(smem + ((pitch * rows + 15) & ~15));
+    int8_t *yo = xo + GT_PCHUNK * GT_W;
+
+    uint32_t tile_x, tile_y, t_lo, t_hi;
+    if (a.worklist)
+    {
+        const uint32_t w = a.worklist[2 * blockIdx.x];
+        tile_x = w & 0xFFFFu;
+        tile_y = w >> 16;
+        t_lo = a.worklist[2 * blockIdx.x + 1];
+        t_hi = t_lo + 1;
+    }
+    else
+    {
+        tile_x = blockIdx.x;
+        tile_y = blockIdx.y;
+        t_lo = a.t_begin + blockIdx.z * a.t_per_cta;
+        t_hi = min(t_lo + a.t_per_cta, a.t_end);
+    }
+    const int tx0 = static_cast<int>(a.x0 + tile_x * GT_W);
+    const int ty0 = static_cast<int>(a.y0 + tile_y * GT_H);
+    const int tid = threadIdx.x;
+
+    // stage the tile with its halo; zeros outside the map
+    for (int i = tid; i < rows * pitch; i += GT_THREADS)
+    {
+        const int r = i / pitch, c = i - r * pitch;
+        const int gy = ty0 - R + r, gx = tx0 - R + c;
+        uint8_t v = 0;
+        if (gy >= 0 && gy < static_cast<int>(a.H) && gx >= 0 && gx < static_cast<int>(a.W))
+            v = a.cost[static_cast<size_t>(gy) * a.W + gx];
+        tile[i] = v;
+    }
+
+    const int xl = tid % GT_W;
+    const int yg = tid / GT_W;  // 0..3; rows yg, yg+4, ...
+    const size_t plane = static_cast<size_t>(a.W) * a.H;
+
+    for (uint32_t t = t_lo; t < t_hi; ++t)
+    {
+        const float2 cs = a.trig[t];
+        unsigned acc[GT_ROWS_PER_THREAD];
+#pragma unroll
+        for (int k = 0; k < GT_ROWS_PER_THREAD; ++k)
+            acc[k] = 0;
+
+        for (uint32_t p0 = 0; p0 < a.P; p0 += GT_PCHUNK)
+        {
+            const int pc = static_cast<int>(min(static_cast<uint32_t>(GT_PCHUNK), a.P - p0));
+            __syncthreads();  // tile staged / previous chunk consumed
+            for (int i = tid; i < pc * GT_W; i += GT_THREADS)
+            {
+                const int p = i / GT_W, l = i - p * GT_W;
+                const float px = static_cast<float>(a.fp[2 * (p0 + p)]), py = static_cast<float>(a.fp[2 * (p0 + p) + 1]);
+                const int gx = tx0 + l;
+                const float x = __fadd_rn(static_cast<float>(gx), a.ox);
+                const float xn = __fsub_rn(__fadd_rn(x, __fmul_rn(px, cs.x)), __fmul_rn(py, cs.y));
+                int off = __float2int_rd(xn) - gx;
+                off = max(-R, min(R, off));
+                xo[i] = static_cast<int8_t>(off);
+            }
+            for (int i = tid; i < pc * GT_H; i += GT_THREADS)
+            {
+                const int p = i / GT_H, l = i - p * GT_H;
+                const float px = static_cast<float>(a.fp[2 * (p0 + p)]), py = static_cast<float>(a.fp[2 * (p0 + p) + 1]);
+                const int gy = ty0 + l;
+                const float y = __fadd_rn(static_cast<float>(gy), a.oy);
+                const float yn = __fadd_rn(__fadd_rn(y, __fmul_rn(px, cs.y)), __fmul_rn(py, cs.x));
+                int off = __float2int_rd(yn) - gy;
+                off = max(-R, min(R, off));
+                yo[i] = static_cast<int8_t>(off);
+            }
+            __syncthreads();
+            for (int p = 0; p < pc; ++p)
+            {
+                const uint8_t *col = tile + (R + xl + xo[p * GT_W + xl]);
+#pragma unroll
+                for (int k = 0; k < GT_ROWS_PER_THREAD; ++k)
+                {
+                    const int row = yg + k * (GT_THREADS / GT_W);
+                    const int sr = R + row + yo[p * GT_H + row];
+                    acc[k] = max(acc[k], static_cast<unsigned>(col[sr * pitch]));
+                }
+            }
+        }
+        const int gx = tx0 + xl;
+        if (gx < static_cast<int>(a.x1))
+        {
+#pragma unroll
+            for (int k = 0; k < GT_ROWS_PER_THREAD; ++k)
+            {
+                const int gy = ty0 + yg + k * (GT_THREADS / GT_W);
+                if (gy < static_cast<int>(a.y1))
+                    a.vol[plane * t + static_cast<size_t>(gy) * a.W + gx] = static_cast<uint8_t>(acc[k]);
+            }
+        }
+    }
+}
+
+size_t generic_smem_bytes(int R)
+{
+    const int pitch = (GT_W + 2 * R + 3) & ~3;
+    const int rows = GT_H + 2 * R;
+    return static_cast<size_t>((pitch * rows + 15) & ~15) + static_cast<size_t>(GT_PCHUNK) * (GT_W + GT_H);
+}
+}  // namespace
+
+// Launch the generic kernel over region [x0,x1) x [y0,y1) for the handle's bins.
+static pp_status launch_generic(pp_handle h, uint32_t x0, uint32_t y0, uint32_t x1, uint32_t y1, const uint32_t *d_worklist,
+                                uint32_t n_work)
+{
+    GenericArgs a;
+    a.cost = h->d_cost;
+    a.vol = h->d_vol;
+    a.trig = h->d_trig;
+    a.fp = h->d_fp;
+    a.W = h->W;
+    a.H = h->H;
+    a.P = static_cast<uint32_t>(h->fp.size() / 2);
+    a.R = h->reach + 2;
+    a.ox = h->ox;
+    a.oy = h->oy;
+    a.t_begin = h->t_begin;
+    a.t_end = h->t_end;
+    a.x0 = x0;
+    a.y0 = y0;
+    a.x1 = x1;
+    a.y1 = y1;
+    a.worklist = d_worklist;
+    const size_t smem = generic_smem_bytes(a.R);
+    PP_REQUIRE(h, smem <= 227 * 1024, PP_ERR_RANGE, "footprint reach %d needs %zu bytes of shared memory", h->reach, smem);
+    PP_CUDA(h, cudaFuncSetAttribute(se2_generic_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+    dim3 grid;
+    if (d_worklist)
+    {
+        a.t_per_cta = 1;
+        grid = dim3(n_work, 1, 1);
+    }
+    else
+    {
+        const uint32_t tiles_x = (x1 - x0 + GT_W - 1) / GT_W, tiles_y = (y1 - y0 + GT_H - 1) / GT_H;
+        const uint32_t n_t = h->t_end - h->t_begin;
+        // enough CTAs to fill 148 SMs several times over, but as many bins per CTA as that allows
+        // so that the staged tile is reused
+        const uint64_t tiles = static_cast<uint64_t>(tiles_x) * tiles_y;
+        uint32_t chunks = static_cast<uint32_t>(std::min<uint64_t>(n_t, (148ull * 16 + tiles - 1) / tiles));
+        chunks = std::max(1u, chunks);
+        a.t_per_cta = (n_t + chunks - 1) / chunks;
+        chunks = (n_t + a.t_per_cta - 1) / a.t_per_cta;
+        PP_REQUIRE(h, tiles_y <= 65535 && chunks <= 65535, PP_ERR_RANGE, "grid too large");
+        grid = dim3(tiles_x, tiles_y, chunks);
+        h->stat_generic_tiles += tiles * n_t;
+    }
+    se2_generic_kernel<<<grid, GT_THREADS, smem, h->stream>>>(a);
+    h->launches++;
+    PP_CUDA(h, cudaGetLastError());
+    return PP_OK;
+}
+
+pp_status pp_se2_launch(pp_handle h, uint32_t x0, uint32_t y0, uint32_t x1, uint32_t y1)
+{
+    h->stat_fast_tiles = 0;
+    h->stat_generic_tiles = 0;
+    h->stat_samples_per_cell = 0.0;
+    if (x1 <= x0 || y1 <= y0 || h->t_end <= h->t_begin)
+        return PP_OK;
+    if (h->vol_mode == 0)
+    {
+        pp_status s = pp_se2_launch_fast(h, x0, y0, x1, y1);
+        if (s != PP_INTERNAL_DECLINED)
+            return s;
+    }
+    return launch_generic(h, x0, y0, x1, y1, nullptr, 0);
+}
+
+pp_status pp_se2_generic_worklist(pp_handle h, const uint32_t *d_worklist, uint32_t n_work)
+{
+    if (n_work == 0)
+        return PP_OK;
+    h->stat_generic_tiles += n_work;
+    return launch_generic(h, 0, 0, h->W, h->H, d_worklist, n_work);
+}
+
+extern "C" {
+
+pp_status pp_se2_volume_set_mode(pp_handle h, int mode)
+{
+    if (!h)
+        return PP_ERR_INVALID;
+    PP_REQUIRE(h, mode == 0 || mode == 1, PP_ERR_INVALID, "pp_se2_volume_set_mode: mode must be 0 or 1");
+    h->vol_mode = mode;
+    return PP_OK;
+}
+
+pp_status pp_se2_volume_stats(pp_handle h, uint64_t *fast_tiles, uint64_t *generic_tiles, double *samples_per_cell)
+{
+    if (!h)
+        return PP_ERR_INVALID;
+    if (fast_tiles)
+        *fast_tiles = h->stat_fast_tiles;
+    if (generic_tiles)
+        *generic_tiles = h->stat_generic_tiles;
+    if (samples_per_cell)
+        *samples_per_cell = h->stat_samples_per_cell;
+    return PP_OK;
+}
+
+pp_status pp_se2_volume_build(pp_handle h, uint32_t n_theta, float ox, float oy, float ot, uint32_t t_begin,
+                              uint32_t t_end)
+{
+    if (!h)
+        return PP_ERR_INVALID;
+    PP_REQUIRE(h, h->d_cost, PP_ERR_STATE, "pp_se2_volume_build: upload a costmap first");
+    PP_REQUIRE(h, !h->fp.empty(), PP_ERR_STATE, "pp_se2_volume_build: set a footprint first");
+    PP_REQUIRE(h, n_theta > 0 && n_theta <= 4096, PP_ERR_RANGE, "n_theta %u outside 1..4096", n_theta);
+    PP_REQUIRE(h, t_begin <= t_end && t_end <= n_theta, PP_ERR_INVALID, "bins [%u,%u) outside [0,%u)", t_begin, t_end, n_theta);
+    PP_REQUIRE(h, ox >= -1.0f && ox <= 1.0f && oy >= -1.0f && oy <= 1.0f, PP_ERR_INVALID,
+               "sample offsets must lie in [-1,1] (got %g, %g)", ox, oy);
+    PP_CUDA(h, cudaSetDevice(h->device));
+    const size_t plane = static_cast<size_t>(h->W) * h->H;
+    PP_CUDA(h, pp_reserve(h->d_vol, h->vol_cap, plane * n_theta));
+    if (n_theta != h->n_theta || ox != h->ox || oy != h->oy || ot != h->ot)
+        pp_se2_plan_free(h);
+    h->n_theta = n_theta;
+    h->ox = ox;
+    h->oy = oy;
+    h->ot = ot;
+    h->t_begin = t_begin;
+    h->t_end = t_end;
+
+    // heading -> (cos, sin) with the host libm, formed exactly like the reference does:
+    // theta = motion.theta * bin_size (astar_hybrid.cpp:283), bin_size = 2.0f*(float)M_PI/size_theta
+    // (motion_hybrid.cpp:10); float cos/sin as in collision_checker.cpp:155-156.
+    std::vector<float2> trig(n_theta);
+    const float bin = 2.0f * static_cast<float>(M_PI) / static_cast<float>(n_theta);
+    for (uint32_t t = 0; t < n_theta; ++t)
+    {
+        const float tf = static_cast<float>(t) + ot;
+        const float theta = tf * bin;
+        trig[t].x = cosf(theta);
+        trig[t].y = sinf(theta);
+    }
+    PP_CUDA(h, pp_reserve(h->d_trig, h->trig_cap, static_cast<size_t>(n_theta)));
+    PP_CUDA(h, cudaMemcpyAsync(h->d_trig, trig.data(), sizeof(float2) * n_theta, cudaMemcpyHostToDevice, h->stream));
+    PP_CUDA(h, cudaStreamSynchronize(h->stream));  // `trig` is pageable and about to go out of scope
+    h->host_trig.swap(trig);
+
+    pp_status s = pp_se2_launch(h, 0, 0, h->W, h->H);
+    if (s != PP_OK)
+        return s;
+    h->vol_valid = true;
+    h->dirty = false;
+    return PP_OK;
+}
+
+pp_status pp_se2_volume_refresh(pp_handle h)
+{
+    if (!h)
+        return PP_ERR_INVALID;
+    PP_REQUIRE(h, h->vol_valid, PP_ERR_STATE, "pp_se2_volume_refresh: no volume built for the current costmap/footprint");
+    if (!h->dirty)
+        return PP_OK;
+    PP_CUDA(h, cudaSetDevice(h->device));
+    // an output cell reads inputs within reach+1 cells (rotation keeps |p|, floor and the sample
+    // offset add at most one more), so those are the outputs a changed input can affect
+    const uint32_t grow = static_cast<uint32_t>(h->reach + 2);
+    const uint32_t x0 = h->dirty_x0 > grow ? h->dirty_x0 - grow : 0;
+    const uint32_t y0 = h->dirty_y0 > grow ? h->dirty_y0 - grow : 0;
+    const uint32_t x1 = std::min(h->W, h->dirty_x1 + grow);
+    const uint32_t y1 = std::min(h->H, h->dirty_y1 + grow);
+    pp_status s = pp_se2_launch(h, x0, y0, x1, y1);
+    if (s != PP_OK)
+        return s;
+    h->dirty = false;
+    return PP_OK;
+}
+
+pp_status pp_se2_volume_download(pp_handle h, uint32_t t_begin, uint32_t t_end, uint8_t *host_out, int host_is_pinned)
+{
+    if (!h)
+        return PP_ERR_INVALID;
+    (void)host_is_pinned;  // cudaMemcpyAsync handles both; pinned memory makes it a true async DMA
+    PP_REQUIRE(h, h->d_vol && host_out, PP_ERR_STATE, "pp_se2_volume_download: no volume or null output");
+    PP_REQUIRE(h, t_begin <= t_end && t_end <= h->n_theta, PP_ERR_INVALID, "bins [%u,%u) outside [0,%u)", t_begin, t_end, h->n_theta);
+    PP_CUDA(h, cudaSetDevice(h->device));
+    const size_t plane = static_cast<size_t>(h->W) * h->H;
+    PP_CUDA(h, cudaMemcpyAsync(host_out, h->d_vol + plane * t_begin, plane * (t_end - t_begin), cudaMemcpyDeviceToHost, h->stream));
+    PP_CUDA(h, cudaStreamSynchronize(h->stream));
+    return PP_OK;
+}
+
+pp_status pp_se2_volume_ptr(pp_handle h, const uint8_t **device_ptr_out, uint64_t *bytes_out)
+{
+    if (!h || !device_ptr_out)
+        return PP_ERR_INVALID;
+    PP_REQUIRE(h, h->d_vol, PP_ERR_STATE, "pp_se2_volume_ptr: no volume");
+    *device_ptr_out = h->d_vol;
+    if (bytes_out)
+        *bytes_out = static_cast<uint64_t>(h->W) * h->H * h->n_theta;
+    return PP_OK;
+}
+
+}  // extern "C"

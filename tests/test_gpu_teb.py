@@ -1,0 +1,85 @@
+"""GPU parity: K3 TEB candidate extraction and radius / top-K association."""
+import numpy as np
+import pytest
+
+from path_planner_b200.synth import make_costmap, make_teb_scene
+
+pytestmark = pytest.mark.gpu
+
+
+def assert_topk_equal(got, want):
+    idx, d2, cnt = got
+    widx, wd2, wcnt = want[0], want[1], want[2]
+    assert np.array_equal(cnt, wcnt)
+    assert np.array_equal(d2, wd2)  # doubles, bit-exact
+    diff = idx != widx
+    for q, j in zip(*np.nonzero(diff)):  # only permutations among equal distances are tolerated
+        assert j < cnt[q] and (wd2[q, :cnt[q]] == d2[q, j]).sum() > 1, (q, j)
+
+
+def test_radius_topk_matches_golden(handle, golden):
+    got = handle.radius_topk(golden["teb_pts"], golden["teb_queries"], 0.9574, 10)
+    assert_topk_equal(got, (golden["teb_idx"], golden["teb_d2"], golden["teb_cnt"]))
+
+
+@pytest.mark.parametrize("N,Q,K,r", [(10000, 100, 10, 0.9574), (10000, 100, 5, 0.9574), (500, 7, 64, 0.5),
+                                     (10000, 3, 10, 1e9), (1, 1, 1, 1e9), (5000, 64, 10, 1e-9)])
+def test_radius_topk_vs_oracle(handle, port, N, Q, K, r):
+    pts, poses = make_teb_scene(N, Q, seed=N + Q)
+    got = handle.radius_topk(pts, poses, r, K)
+    assert_topk_equal(got, port.radius_topk(pts, poses, r, K))
+
+
+def test_radius_topk_ties_and_strictness(handle, port):
+    # points on a lattice: many exactly equal distances, and points exactly at d2 == radius_arg
+    g = np.arange(-5, 6, dtype=np.float64)
+    pts = np.stack(np.meshgrid(g, g), -1).reshape(-1, 2)
+    q = np.array([[0.0, 0.0], [0.5, 0.5], [5.0, 5.0]])
+    for r in (1.0, 2.0, 4.0, 0.5):  # d2 == r must be excluded (strict <)
+        got = handle.radius_topk(pts, q, r, 8)
+        want = port.radius_topk(pts, q, r, 8)
+        assert_topk_equal(got, want)
+        assert (got[1][got[1] > 0] < r).all()
+
+
+def test_three_rounds_with_moving_poses(handle, port):
+    """One replan = 1 extraction + 3 query rounds with the poses moved in between (teb_optimizer.cpp:90-108)."""
+    pts, poses = make_teb_scene(10000, 100, seed=1)
+    rng = np.random.default_rng(2)
+    handle.radius_topk(pts, poses, 0.9574, 10)
+    for _ in range(3):
+        poses = poses + rng.uniform(-0.02, 0.02, poses.shape)
+        got = handle.radius_topk(None, poses, 0.9574, 10)  # points stay resident on the device
+        assert_topk_equal(got, port.radius_topk(pts, poses, 0.9574, 10))
+
+
+@pytest.mark.parametrize("shape,pose", [((200, 200), (5.0, 5.0, 0.7)), ((200, 200), (2.0, 8.0, -2.5)), ((77, 130), (1.0, 3.0, 3.1)),
+                                        ((1, 1), (0.0, 0.0, 0.0)), ((640, 480), (16.0, 12.0, 1.3))])
+def test_extract_matches_oracle(handle, port, shape, pose):
+    W, H = shape
+    cost = make_costmap(W, H, seed=W + H, coverage=0.1) if W > 8 else np.full((H, W), 254, np.uint8)
+    handle.costmap_upload(cost)
+    for (mfr, behind) in [(4.5, 1.5), (1.0, 0.3), (100.0, 0.0)]:
+        got = handle.obstacles_extract(0.05, (0.0, 0.0), pose, mfr, behind)
+        want = port.extract_obstacles(cost, 0.05, (0.0, 0.0), pose, mfr, behind)
+        assert got.shape == want.shape
+        assert np.array_equal(got, want)
+
+
+def test_extract_then_query_on_device(handle, port):
+    cost = make_costmap(200, 200, seed=10, coverage=0.08)
+    pose = (5.0, 5.0, 0.3)
+    handle.costmap_upload(cost)
+    pts = handle.obstacles_extract(0.05, (0.0, 0.0), pose, 4.5, 1.5)
+    s = np.linspace(0, 3, 33)
+    poses = np.stack([5.0 + s * np.cos(0.3), 5.0 + s * np.sin(0.3)], 1)
+    got = handle.radius_topk(None, poses, 0.9574, 10)
+    assert_topk_equal(got, port.radius_topk(pts, poses, 0.9574, 10))
+
+
+def test_empty_extraction(handle):
+    handle.costmap_upload(np.zeros((50, 50), np.uint8))
+    pts = handle.obstacles_extract(0.05, (0.0, 0.0), (1.0, 1.0, 0.0), 4.5, 1.5)
+    assert pts.shape == (0, 2)
+    idx, d2, cnt = handle.radius_topk(None, np.zeros((4, 2)), 0.9574, 10)
+    assert (cnt == 0).all()

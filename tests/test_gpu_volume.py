@@ -1,0 +1,151 @@
+"""GPU parity: K1 SE2 footprint-collision volume through the C ABI, bit-exact against the golden
+vectors (reference's own code) and the oracle on seeded inputs."""
+import numpy as np
+import pytest
+
+from conftest import FOOTPRINTS, OFFSETS, RES
+from path_planner_b200.synth import make_costmap
+
+pytestmark = pytest.mark.gpu
+
+
+def build(handle, cost, fname, n_theta=72, off=(0.5, 0.5, 0.0), t0=0, t1=None, mode=0):
+    b, hole = FOOTPRINTS[fname]
+    handle.costmap_upload(cost)
+    handle.footprint_from_boundary(RES, b, hole)
+    handle.se2_volume_set_mode(mode)
+    handle.se2_volume_build(n_theta, *off, t_begin=t0, t_end=t1)
+    return handle.se2_volume_download(t0, t1)
+
+
+@pytest.mark.parametrize("mode", [0, 1])
+@pytest.mark.parametrize("fname,oname", [(f, o) for f in FOOTPRINTS for o in OFFSETS if f == "rect_hole" or o == "centre"])
+def test_volume_matches_golden(handle, golden, fname, oname, mode):
+    v = build(handle, golden["cost"], fname, 72, OFFSETS[oname], mode=mode)
+    assert np.array_equal(v, golden[f"vol_{fname}_{oname}_72"])
+
+
+def test_volume_144_bins_matches_golden(handle, golden):
+    v = build(handle, golden["cost"], "rect_hole", 144)
+    bins = golden["vol_rect_hole_centre_144_bins"]
+    assert np.array_equal(v[bins], golden["vol_rect_hole_centre_144"])
+
+
+def test_footprint_points_match_reference(handle, golden):
+    for fname, (b, hole) in FOOTPRINTS.items():
+        handle.footprint_from_boundary(RES, b, hole)
+        assert np.array_equal(handle.footprint_get(), golden[f"fp_{fname}"])
+
+
+@pytest.mark.parametrize("shape", [(1, 1), (3, 2), (31, 33), (131, 77), (200, 150), (257, 64)])
+@pytest.mark.parametrize("mode", [0, 1])
+def test_volume_ragged_sizes_vs_oracle(handle, port, shape, mode):
+    W, H = shape
+    cost = make_costmap(W, H, seed=W * 1000 + H, coverage=0.1) if W > 8 else np.full((H, W), 254, np.uint8)
+    for fname in ("rect_hole", "box_hole"):
+        for off in OFFSETS.values():
+            v = build(handle, cost, fname, 72, off, mode=mode)
+            b, hole = FOOTPRINTS[fname]
+            o = port.se2_volume(cost, port.footprint_points(RES, b, hole), 72, *off)
+            assert np.array_equal(v, o), (shape, fname, off)
+
+
+@pytest.mark.parametrize("fill", [0, 1, 252, 253, 254, 255])
+def test_volume_constant_maps(handle, port, fill):
+    cost = np.full((70, 90), fill, np.uint8)
+    v = build(handle, cost, "rect_hole")
+    o = port.se2_volume(cost, port.footprint_points(RES, *FOOTPRINTS["rect_hole"]), 72)
+    assert np.array_equal(v, o)
+    # every pose has at least one in-map sample on a 90x70 map, so the volume is constant too
+    assert (v == fill).all()
+
+
+def test_volume_partial_bins_and_arbitrary_offsets(handle, port):
+    cost = make_costmap(150, 90, seed=5)
+    offs = np.array([[0, 0], [3, -2], [-7, 1], [0, 9], [4, 4], [4, 4], [-1, -1]], np.int32)  # with a duplicate
+    handle.costmap_upload(cost)
+    handle.footprint_set(offs)
+    handle.se2_volume_build(72, 0.5, 0.5, 0.0, 18, 27)
+    v = handle.se2_volume_download(18, 27)
+    o = port.se2_volume(cost, offs, 72, 0.5, 0.5, 0.0, t0=18, t1=27)
+    assert np.array_equal(v, o)
+
+
+def test_dirty_region_refresh_equals_rebuild(handle, port):
+    cost = make_costmap(300, 200, seed=6)
+    pts = port.footprint_points(RES, *FOOTPRINTS["rect_hole"])
+    v0 = build(handle, cost, "rect_hole")
+    assert np.array_equal(v0, port.se2_volume(cost, pts, 72))
+    rng = np.random.default_rng(0)
+    new = cost.copy()
+    for (x0, y0, w, h) in [(40, 50, 30, 20), (250, 170, 50, 30), (0, 0, 10, 10)]:
+        patch = rng.choice(np.array([0, 0, 0, 100, 253, 254, 255], np.uint8), size=(h, w))
+        new[y0:y0 + h, x0:x0 + w] = patch
+        handle.costmap_update_rect(x0, y0, patch)
+    handle.se2_volume_refresh()
+    v1 = handle.se2_volume_download()
+    assert np.array_equal(handle.costmap_download(), new)
+    assert np.array_equal(v1, port.se2_volume(new, pts, 72))
+    handle.se2_volume_refresh()  # nothing dirty: a no-op
+    assert np.array_equal(handle.se2_volume_download(), v1)
+
+
+def test_fast_and_generic_paths_agree_on_large_map(handle):
+    cost = make_costmap(1100, 700, seed=9)
+    a = build(handle, cost, "rect_hole", mode=0)
+    st = handle.se2_volume_stats()
+    b = build(handle, cost, "rect_hole", mode=1)
+    assert np.array_equal(a, b), st
+
+
+def test_full_size_volume_sampled_against_oracle(handle, port):
+    """BASELINE config 3 (4096x4096x72): too big for the CPU oracle as a whole, so check (a) a seeded
+    sample of cells against the oracle's per-pose evaluation, (b) two full row bands, (c) that
+    rebuilding is deterministic, (d) that collision flags never appear on an all-free map."""
+    W = H = 4096
+    cost = make_costmap(W, H, seed=1)
+    b, hole = FOOTPRINTS["rect_hole"]
+    pts = port.footprint_points(RES, b, hole)
+    handle.costmap_upload(cost)
+    handle.footprint_from_boundary(RES, b, hole)
+    handle.se2_volume_build(72)
+    rng = np.random.default_rng(3)
+    bin_sz = np.float32(2.0) * np.float32(np.pi) / np.float32(72)
+    for t in (0, 1, 17, 18, 35, 36, 54, 71):
+        plane = handle.se2_volume_download(t, t + 1)[0]
+        xs = rng.integers(0, W, 3000)
+        ys = rng.integers(0, H, 3000)
+        # include the map corners and power-of-two columns/rows where float spacing changes
+        xs[:8] = [0, 1, W - 1, W - 2, 2047, 2048, 1023, 1024]
+        ys[:8] = [0, W - 1, 0, H - 1, 2048, 2047, 1024, 1023]
+        theta = np.float32(np.float32(t) * bin_sz)
+        poses = np.stack([xs.astype(np.float32) + np.float32(0.5), ys.astype(np.float32) + np.float32(0.5),
+                          np.full(3000, theta, np.float32)], 1)
+        c, _, _ = port.footprint_cost_batch(cost, pts, poses)
+        assert np.array_equal(plane[ys, xs], c.astype(np.uint8)), t
+        if t in (17, 54):
+            for y0 in (0, 2040):
+                band = port.se2_volume(cost, pts, 72, t0=t, t1=t + 1, y0=y0, y1=y0 + 16)
+                assert np.array_equal(plane[y0:y0 + 16], band[0]), (t, y0)
+    first = handle.se2_volume_download(10, 12).copy()
+    handle.se2_volume_build(72)
+    assert np.array_equal(handle.se2_volume_download(10, 12), first)
+    handle.costmap_upload(np.zeros((H, W), np.uint8))
+    handle.se2_volume_build(72, t_begin=0, t_end=2)
+    assert not handle.se2_volume_download(0, 2).any()
+
+
+def test_error_paths(handle):
+    from path_planner_b200.capi import PPError
+    with pytest.raises(PPError):
+        handle.se2_volume_build(72)  # no costmap
+    handle.costmap_upload(np.zeros((8, 8), np.uint8))
+    with pytest.raises(PPError):
+        handle.se2_volume_build(72)  # no footprint
+    handle.footprint_from_boundary(RES, [0.64, 0.46], True)
+    with pytest.raises(PPError):
+        handle.se2_volume_build(72, t_begin=5, t_end=80)
+    with pytest.raises(PPError):
+        handle.footprint_from_boundary(RES, [1.0, 2.0, 3.0], True)  # 3 numbers: the reference asserts
+    with pytest.raises(PPError):
+        handle.se2_volume_refresh()  # nothing built yet
