@@ -1,0 +1,368 @@
+#!/usr/bin/env python
+"""bench.py -- the reference's headline workload on B200: SE2 collision volume (+ heuristic field,
+TEB queries) at 4096x4096x72 (BASELINE.json configs[2]).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+
+One process per GPU (torchrun for N > 1). A step is one build of the whole SE2 volume from a costmap
+already resident in HBM; with N > 1 the 72 heading bins are split evenly across ranks (strong
+scaling, no data-path collective in `value`; the NCCL all-gather of the slabs is timed
+separately and reported under "gathered"). Rank 0 prints ONE JSON line.
+
+`--impl reference` times the reference's own CPU code (oracle/_ref, compiled unmodified from the
+reference sources; falls back to the oracle port where that is absent) with all host threads on
+a bounded row band of the same workload.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+W = H = 4096
+N_THETA = 72
+RES = 0.05
+BOUNDARY, HOLE = [0.64, 0.46], True  # shipped default footprint, path_planner/config/params.yaml:29-30
+COST_PENALTY = 2.0
+GOAL = (3000, 1000)
+METRIC = "se2_collision_cells_per_sec"
+UNIT = "cells/s"
+WORKLOAD = "se2_volume_4096x4096x72_rect0.64x0.46_hole"
+
+
+def measured_peak_gbs():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
+    FIELDS = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+              "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.tmp = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        self.proc = None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(gpu_index), "--query-gpu=" + self.FIELDS,
+                                          "--format=csv,noheader,nounits", "-lms", "200"], stdout=self.tmp,
+                                         stderr=subprocess.DEVNULL)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
+        if self.proc is None:
+            return out
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        self.tmp.flush()
+        self.tmp.seek(0)
+        sm, mx, reasons = [], [], set()
+        for line in self.tmp.read().splitlines():
+            p = [x.strip() for x in line.split(",")]
+            if len(p) < 9:
+                continue
+            try:
+                sm.append(float(p[1]))
+                mx.append(float(p[2]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), p[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        try:
+            os.unlink(self.tmp.name)
+        except OSError:
+            pass
+        if sm:
+            out["sm_mhz"] = float(np.median(sm))
+            out["sm_max_mhz"] = float(max(mx))
+        out["reasons"] = sorted(reasons)
+        out["samples"] = len(sm)
+        return out
+
+
+def make_inputs():
+    from path_planner_b200.synth import make_costmap
+    return make_costmap(W, H, seed=1, pockets=[(GOAL[0], GOAL[1], 6)])
+
+
+def cpu_volume_sample(cost, target_seconds, threads):
+    """Reference CPU volume on a row band sized for ~target_seconds; returns (cells/s, kind, sample)."""
+    import oracle
+    ref = oracle.load_ref()
+    y0 = 1024
+    if ref is not None:
+        kind = "reference"
+        run = lambda rows: ref.se2_volume(cost, RES, BOUNDARY, HOLE, N_THETA, y0=y0, y1=y0 + rows, nthreads=threads)
+    else:
+        kind = "port"
+        port = oracle.load_port()
+        pts = port.footprint_points(RES, BOUNDARY, HOLE)
+        run = lambda rows: port.se2_volume(cost, pts, N_THETA, y0=y0, y1=y0 + rows, nthreads=threads)
+    t = time.perf_counter()
+    run(4)
+    probe = time.perf_counter() - t
+    rows = int(max(4, min(1024, 4 * target_seconds / max(probe, 1e-3))))
+    t = time.perf_counter()
+    run(rows)
+    dt = time.perf_counter() - t
+    cells = rows * W * N_THETA
+    return cells / dt, kind, f"rows [{y0},{y0 + rows}) of {H} x all {W} columns x all {N_THETA} bins ({cells} cells, {dt:.1f} s)"
+
+
+def run_reference(args, rank):
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    cost = make_inputs()
+    per_step = max(2.0, min(20.0, 120.0 / max(1, args.steps + args.warmup)))
+    vals = []
+    kind = sample = None
+    for i in range(args.warmup + args.steps):
+        v, kind, sample = cpu_volume_sample(cost, per_step, cores)
+        if i >= args.warmup:
+            vals.append(v)
+    value = float(np.mean(vals))
+    total_cells = W * H * N_THETA
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * total_cells / value, "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "note": "CPU; each step is a row band, ms_per_step extrapolated to the full volume"},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--mode", type=int, default=0, help="0 auto, 1 force the generic kernel")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.impl == "reference":
+        run_reference(args, rank)
+        return
+    if world != args.gpus:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torchrun --nproc-per-node {args.gpus}")
+    if N_THETA % world:
+        raise SystemExit(f"{N_THETA} heading bins do not split evenly over {world} ranks")
+
+    import torch
+    import torch.distributed as dist
+    from path_planner_b200 import capi
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (no CPU fallback)")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if world == 1:
+            return float(x)
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    cost = make_inputs()
+    per = N_THETA // world
+    t0, t1 = rank * per, (rank + 1) * per
+    h = capi.Handle(local_rank)
+    pinned_cost = capi.PinnedBuffer(W * H)
+    pinned_cost.array.reshape(H, W)[:] = cost
+    cost_pinned = pinned_cost.array.reshape(H, W)
+    h.costmap_upload(cost_pinned, pinned=True)
+    h.footprint_from_boundary(RES, BOUNDARY, HOLE)
+    h.se2_volume_set_mode(args.mode)
+    h.sync()
+    if world > 1:
+        obj = [capi.comm_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(obj, src=0)
+        h.comm_init(obj[0], rank, world)
+
+    def step():
+        h.se2_volume_build(N_THETA, 0.5, 0.5, 0.0, t0, t1)
+
+    # ---- device-resident throughput (`value`) -------------------------------------------------
+    for _ in range(args.warmup):
+        h.l2_flush()
+        step()
+    h.sync()
+    stats = h.se2_volume_stats()
+    barrier()
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    launches0 = h.launch_count()
+    total_ms = 0.0
+    wall0 = time.perf_counter()
+    for _ in range(args.steps):
+        h.l2_flush()          # cold L2 for every step; the flush is outside the event pair
+        h.timer_start()
+        step()
+        total_ms += h.timer_stop()
+    barrier()
+    wall = time.perf_counter() - wall0
+    launches = h.launch_count() - launches0
+    clocks = sampler.stop() if sampler else None
+    ms_per_step = max_over_ranks(total_ms / args.steps)
+    total_cells = W * H * N_THETA
+    value = total_cells / (ms_per_step * 1e-3)
+
+    # ---- compute + NCCL all-gather of the slabs (N > 1) ----------------------------------------
+    gathered = None
+    if world > 1:
+        for _ in range(2):
+            step()
+            h.se2_volume_allgather()
+        h.sync()
+        barrier()
+        g_ms = 0.0
+        for _ in range(args.steps):
+            h.l2_flush()
+            h.timer_start()
+            step()
+            h.se2_volume_allgather()
+            g_ms += h.timer_stop()
+        barrier()
+        g_ms = max_over_ranks(g_ms / args.steps)
+        gathered = {"value": total_cells / (g_ms * 1e-3), "unit": UNIT, "ms_per_step": g_ms,
+                    "collective": "ncclAllGather of heading slabs, in place",
+                    "bytes_received_per_gpu": int(W * H * (N_THETA - per))}
+
+    # ---- end to end through the C ABI with host buffers (`e2e`) ----------------------------------
+    out_pinned = capi.PinnedBuffer(W * H * per)
+    out_view = out_pinned.array.reshape(per, H, W)
+    e2e_steps = max(3, min(args.steps, 5))
+
+    def e2e_step():
+        h.costmap_upload(cost_pinned, pinned=True)
+        step()
+        h.se2_volume_download(t0, t1, out=out_view, pinned=True)
+
+    e2e_step()
+    barrier()
+    e0 = time.perf_counter()
+    h.timer_start()
+    for _ in range(e2e_steps):
+        e2e_step()
+    e_ms = h.timer_stop()
+    barrier()
+    e_wall = (time.perf_counter() - e0) * 1e3
+    e_ms = max_over_ranks(max(e_ms, 0.0) / e2e_steps)
+    e2e = {"value": total_cells / (e_ms * 1e-3), "unit": UNIT, "ms_per_step": e_ms, "wall_ms_per_step": e_wall / e2e_steps,
+           "h2d_bytes_per_step": int(W * H * world), "d2h_bytes_per_step": int(W * H * N_THETA),
+           "path": "pp_costmap_upload(pinned host) + pp_se2_volume_build + pp_se2_volume_download(pinned host)"}
+
+    # ---- roofline of the dominant kernel ---------------------------------------------------------
+    peak, peak_src = measured_peak_gbs()
+    alg_bytes = W * H * (1 + per)            # read the costmap once, write every output byte once
+    my_ms = total_ms / args.steps
+    achieved = alg_bytes / (my_ms * 1e-3) / 1e9
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "se2_traffic.json")
+    if os.path.exists(tpath):
+        try:
+            traffic = json.load(open(tpath)).get("dram_bytes_per_launch")
+        except Exception:
+            traffic = None
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                "traffic": traffic, "peak_source": peak_src, "kernel": "se2 volume build (all launches of one pp_se2_volume_build)",
+                "algorithmic_bytes_per_launch": alg_bytes, "ms_per_launch": my_ms,
+                "frac_of_nominal_8TBs": achieved / 8000.0}
+
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "u8",
+        "data": "synthetic",
+        "config": {"workload": WORKLOAD, "W": W, "H": H, "n_theta": N_THETA, "bins_per_gpu": per,
+                   "footprint_points": int(len(h.footprint_get())), "sample_offset": [0.5, 0.5, 0.0],
+                   "sharding": f"theta x{world}", "l2": "flushed between steps (256 MiB memset, outside the timed events)",
+                   "kernel_mode": "auto" if args.mode == 0 else "generic", "fast_tiles": stats["fast_tiles"],
+                   "generic_tiles": stats["generic_tiles"], "samples_per_cell": stats["samples_per_cell"]},
+        "roofline": roofline, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
+        "wall_s_timed_region": wall,
+    }
+    if gathered:
+        line["gathered"] = gathered
+
+    if rank == 0:
+        # heuristic field and TEB queries stay on one GPU
+        for _ in range(2):
+            h.heuristic_build(GOAL[0], GOAL[1], COST_PENALTY, download=False)
+        h.sync()
+        reps = 5
+        h.timer_start()
+        for _ in range(reps):
+            h.heuristic_build(GOAL[0], GOAL[1], COST_PENALTY, download=False)
+        hms = h.timer_stop() / reps
+        hs = h.heuristic_stats()
+        line["heuristic"] = {"build_ms": hms, "rounds": hs["rounds"], "map": f"{W}x{H}", "unit": "ms"}
+        from path_planner_b200.synth import make_teb_scene
+        pts, poses = make_teb_scene(10000, 100, seed=0)
+        h.radius_topk(pts, poses, 0.9574, 10)
+        t = time.perf_counter()
+        rounds = 30
+        for _ in range(rounds):
+            h.radius_topk(None, poses, 0.9574, 10)
+        line["teb"] = {"us_per_round_e2e": 1e6 * (time.perf_counter() - t) / rounds,
+                       "workload": "100 poses x 10000 points, K=10, host buffers in and out"}
+
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        cores = os.cpu_count() or 1
+        v, kind, sample = cpu_volume_sample(cost, 15.0, cores)
+        line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample}
+        try:
+            import oracle
+            ref = oracle.load_ref()
+            if ref is not None:
+                ref.heuristic(cost, RES, (0.0, 0.0), (GOAL[0] + 0.5, GOAL[1] + 0.5), COST_PENALTY)
+                line["cpu_baseline"]["heuristic_ms"] = 1e3 * ref.last_seconds
+                from path_planner_b200.synth import make_teb_scene
+                pts, poses = make_teb_scene(10000, 100, seed=0)
+                ref.radius_topk(pts, poses, 0.9574, 10)
+                line["cpu_baseline"]["teb_us_per_round"] = 1e6 * (ref.last_build_seconds + ref.last_query_seconds)
+        except Exception as e:  # the baseline is a report, never a reason to lose the GPU line
+            line["cpu_baseline"]["note"] = f"heuristic/teb baseline failed: {e}"
+
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    out_pinned.free()
+    pinned_cost.free()
+    h.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -33,11 +33,7 @@ __global__ void heur_init_kernel(float *field, size_t n, uint32_t *flags, size_t
     for (size_t k = i; k < n; k += stride)
         field[k] = (k == goal_index) ? 0.00001f : __int_as_float(0x7f800000);
     for (size_t k = i; k < n_flags; k += stride)
-        flags[k] = 0;
-    if (i == 0)
-    {
-        flags[goal_tile] = 1;  // generation 0
-    }
+        flags[k] = (k == goal_tile) ? 1u : 0u;  // the goal's tile is the only active one in generation 0
 }
 
 // flags layout: [0, nT) generation 0, [nT, 2nT) generation 1, then 4 round counters

@@ -65,6 +65,18 @@ def test_unreachable_and_degenerate_goals(handle, port):
     assert field[20, 63] == np.float32(0.00001)
 
 
+def test_repeated_builds_with_goals_in_many_tiles(handle, port):
+    """Every build must restart from a clean activity state, whichever tile holds the goal."""
+    cost = make_costmap(520, 390, seed=13, coverage=0.06)
+    handle.costmap_upload(cost)
+    rng = np.random.default_rng(4)
+    for _ in range(12):
+        gx, gy = int(rng.integers(1, 519)), int(rng.integers(1, 389))
+        field = handle.heuristic_build(gx, gy, 2.0)
+        assert np.array_equal(field, port.heuristic_fixed_point(cost, (gx, gy), 2.0)), (gx, gy)
+        assert handle.heuristic_stats()["rounds"] >= 8
+
+
 def test_tiny_maps(handle, port):
     for shape in [(1, 1), (2, 5), (3, 3)]:
         cost = np.zeros(shape[::-1], np.uint8)
