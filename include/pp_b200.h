@@ -140,6 +140,25 @@ pp_status pp_heuristic_build(pp_handle h, uint32_t goal_x, uint32_t goal_y, floa
 pp_status pp_heuristic_ptr(pp_handle h, const float **device_ptr_out);
 pp_status pp_heuristic_stats(pp_handle h, uint32_t *rounds, uint64_t *tile_visits);
 
+/* pp_heuristic_build_noalloc -- no counterpart in the reference. The same field as
+ * pp_heuristic_build for callers that are not allowed to allocate device memory (hard real-time
+ * planner threads, plugins inside a process that has given all device memory to its own pool,
+ * processes that forbid allocation after start-up): it needs no handle and calls no cudaMalloc,
+ * cudaFree or other allocating routine. The caller passes the costmap and the output field as
+ * DEVICE pointers (W*H bytes in, W*H floats out) and the stream to run on (a cudaStream_t, or
+ * NULL for the default stream); the kernel's scratch (per-tile activity flags, travel-cost table)
+ * lives in a fixed ~130 KB array inside the library image, held by every GPU that loads the
+ * library until the process exits.
+ *   limit    ceil(W/32) * ceil(H/32) <= 16384 tiles (e.g. 4096 x 4096); larger maps are refused
+ *            with PP_ERR_RANGE and a message on stderr
+ *   device   the CUDA device that is current in the calling thread
+ *   set-up   the first call on each device looks up the array's device address; make that call
+ *            before any stream capture on that device
+ *   sharing  one array per device, cleared at the start of every call; calls whose GPU work
+ *            overlaps race on it, so serialise them. Returns after the field is complete. */
+pp_status pp_heuristic_build_noalloc(const uint8_t *d_cost, uint32_t W, uint32_t H, uint32_t goal_x, uint32_t goal_y,
+                                     float cost_penalty, float *d_field_out, void *cuda_stream);
+
 /* ---- K3: TEB obstacle association -----------------------------------------------------------
  * pp_obstacles_extract replaces TebFollower::addObstacles (teb_follower.cpp:140-169): all cells
  * with cost >= 253, as world points (cell centres), filtered by the +-1.2*max_follow_range box

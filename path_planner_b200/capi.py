@@ -18,7 +18,7 @@ SYMBOLS = [
     "pp_timer_start", "pp_timer_stop", "pp_l2_flush", "pp_launch_count", "pp_costmap_upload", "pp_costmap_update_rect", "pp_costmap_download",
     "pp_footprint_from_boundary", "pp_footprint_set", "pp_footprint_get", "pp_se2_volume_build",
     "pp_se2_volume_refresh", "pp_se2_volume_download", "pp_se2_volume_ptr", "pp_se2_volume_set_mode",
-    "pp_se2_volume_stats", "pp_footprint_cost_batch", "pp_heuristic_build", "pp_heuristic_ptr", "pp_heuristic_stats",
+    "pp_se2_volume_stats", "pp_footprint_cost_batch", "pp_heuristic_build", "pp_heuristic_ptr", "pp_heuristic_stats", "pp_heuristic_build_noalloc",
     "pp_obstacles_extract", "pp_radius_topk", "pp_comm_unique_id", "pp_comm_init", "pp_se2_volume_allgather",
 ]
 
@@ -68,6 +68,7 @@ def load():
     L.pp_se2_volume_stats.argtypes = [_vp, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), C.POINTER(C.c_double)]
     L.pp_footprint_cost_batch.argtypes = [_vp, _vp, _u32, _vp, _vp]
     L.pp_heuristic_build.argtypes = [_vp, _u32, _u32, C.c_float, _vp]
+    L.pp_heuristic_build_noalloc.argtypes = [_vp, _u32, _u32, _u32, _u32, C.c_float, _vp, _vp]
     L.pp_heuristic_ptr.argtypes = [_vp, C.POINTER(_vp)]
     L.pp_heuristic_stats.argtypes = [_vp, C.POINTER(_u32), C.POINTER(C.c_uint64)]
     L.pp_obstacles_extract.argtypes = [_vp] + [C.c_double] * 8 + [_vp, _u32, C.POINTER(_u32)]
@@ -272,6 +273,13 @@ class Handle:
 
     def se2_volume_allgather(self):
         self._ck(self.L.pp_se2_volume_allgather(self.h))
+
+
+def heuristic_build_noalloc(d_cost_ptr, W, H, goal_x, goal_y, cost_penalty, d_field_ptr, stream=None):
+    """pp_heuristic_build_noalloc: device pointers in and out (integers), no handle, no allocation."""
+    st = load().pp_heuristic_build_noalloc(d_cost_ptr, W, H, goal_x, goal_y, cost_penalty, d_field_ptr, stream)
+    if st != 0:
+        raise PPError(st, "pp_heuristic_build_noalloc failed (message on stderr)")
 
 
 def comm_unique_id():

@@ -255,3 +255,127 @@ pp_status pp_heuristic_stats(pp_handle h, uint32_t *rounds, uint64_t *tile_visit
 }
 
 }  // extern "C"
+
+// ------------------------------------------------------------------------------------------------
+// pp_heuristic_build_noalloc: the same field, for callers that must not allocate.
+//
+// Who needs it: a planner thread that runs inside a hard real-time control loop (cudaMalloc and
+// cudaFree may take the device-wide allocator lock, synchronise the device and take an
+// unbounded time), a plugin loaded into a host process that has already handed all device memory
+// to its own pool, and code that runs after start-up in a process whose policy forbids new device
+// allocations. Such a caller owns its buffers; what it cannot supply is this kernel's scratch
+// memory: the two generations of per-tile activity flags with their round counters, and the
+// travel-cost table. Here that scratch lives in a fixed array in device global memory that is part
+// of the library image, so every GPU that loads the library carries these ~130 KB until the
+// process exits.
+//
+// Limit: at most 16384 tiles of 32x32 cells, i.e. ceil(W/32)*ceil(H/32) <= 16384 (4096 x 4096 fits);
+// anything larger is refused with PP_ERR_RANGE.
+//
+// Set-up: the array's name means something only to device code; in host code it is a stand-in,
+// not an address a kernel can use. So the first call on each device asks the runtime for the real
+// device address (cudaGetSymbolAddress) with that device current and remembers it. That first call
+// therefore does slightly more work than later ones and should be made before any stream capture
+// begins on that device.
+//
+// Sharing: there is ONE array per device. Each call clears the flags and counters and rewrites the
+// travel table before use, so nothing leaks from one call into the next, but two calls whose GPU
+// work overlaps (different streams, or different threads) would trample each other's flags:
+// serialise them.
+namespace
+{
+constexpr uint32_t NOALLOC_MAX_TILES = (4096 / HT) * (4096 / HT);
+constexpr size_t NOALLOC_FLAG_WORDS = 2 * static_cast<size_t>(NOALLOC_MAX_TILES) + 4;
+constexpr size_t NOALLOC_WORDS = NOALLOC_FLAG_WORDS + 512;  // flags + counters, then the 2x256 travel table
+constexpr int NOALLOC_MAX_DEVICES = 64;
+
+static __device__ __align__(256) uint32_t g_noalloc_scratch[NOALLOC_WORDS];
+
+uint32_t *g_noalloc_addr[NOALLOC_MAX_DEVICES] = {};  // device address of the array, per device ordinal
+}  // namespace
+
+extern "C" pp_status pp_heuristic_build_noalloc(const uint8_t *d_cost, uint32_t W, uint32_t H, uint32_t goal_x,
+                                                uint32_t goal_y, float cost_penalty, float *d_field_out,
+                                                void *cuda_stream)
+{
+    if (!d_cost || !d_field_out || W == 0 || H == 0)
+        return pp_fail(nullptr, PP_ERR_INVALID, "pp_heuristic_build_noalloc: null buffer or empty map");
+    if (goal_x >= W || goal_y >= H)
+        return pp_fail(nullptr, PP_ERR_INVALID, "pp_heuristic_build_noalloc: goal (%u,%u) outside %ux%u", goal_x, goal_y, W, H);
+    const uint32_t tiles_x = (W + HT - 1) / HT, tiles_y = (H + HT - 1) / HT;
+    const uint64_t nT64 = static_cast<uint64_t>(tiles_x) * tiles_y;
+    if (nT64 > NOALLOC_MAX_TILES)
+        return pp_fail(nullptr, PP_ERR_RANGE,
+                       "pp_heuristic_build_noalloc: a %ux%u map needs %llu tiles of %dx%d cells; the built-in scratch "
+                       "holds %u (e.g. 4096x4096). Use pp_heuristic_build for larger maps.",
+                       W, H, static_cast<unsigned long long>(nT64), HT, HT, NOALLOC_MAX_TILES);
+    const uint32_t nT = static_cast<uint32_t>(nT64);
+    cudaStream_t stream = static_cast<cudaStream_t>(cuda_stream);
+
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess)
+        return pp_fail(nullptr, PP_ERR_CUDA, "pp_heuristic_build_noalloc: cudaGetDevice: %s", cudaGetErrorString(e));
+    if (dev < 0 || dev >= NOALLOC_MAX_DEVICES)
+        return pp_fail(nullptr, PP_ERR_RANGE, "pp_heuristic_build_noalloc: device ordinal %d not supported", dev);
+    if (!g_noalloc_addr[dev])
+    {
+        // once per device, with that device current: turn the host-side stand-in into the address
+        // the kernels can dereference
+        uint32_t *p = nullptr;
+        e = cudaGetSymbolAddress(reinterpret_cast<void **>(&p), g_noalloc_scratch);
+        if (e != cudaSuccess || !p)
+            return pp_fail(nullptr, PP_ERR_CUDA, "pp_heuristic_build_noalloc: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+        g_noalloc_addr[dev] = p;
+    }
+    uint32_t *flags = g_noalloc_addr[dev];
+    float *travel_dev = reinterpret_cast<float *>(flags + NOALLOC_FLAG_WORDS);
+
+    float travel[512];
+    const float sqrt_2 = sqrtf(2.0f);
+    for (int c = 0; c < 256; ++c)
+    {
+        const float cost = static_cast<float>(c);
+        const float scale = 1.0f + (cost_penalty * cost / 252.0f);
+        travel[c] = c >= PP_COST_INSCRIBED ? std::numeric_limits<float>::infinity() : 1.0f * scale;
+        travel[256 + c] = c >= PP_COST_INSCRIBED ? std::numeric_limits<float>::infinity() : sqrt_2 * scale;
+    }
+    e = cudaMemcpyAsync(travel_dev, travel, sizeof(travel), cudaMemcpyHostToDevice, stream);
+    if (e == cudaSuccess)
+        e = cudaStreamSynchronize(stream);  // `travel` is on this stack frame
+    if (e != cudaSuccess)
+        return pp_fail(nullptr, PP_ERR_CUDA, "pp_heuristic_build_noalloc: travel table upload: %s", cudaGetErrorString(e));
+
+    const size_t n = static_cast<size_t>(W) * H;
+    const size_t n_flags = 2 * static_cast<size_t>(nT) + 4;
+    const uint32_t goal_index = goal_y * W + goal_x;
+    const uint32_t goal_tile = (goal_y / HT) * tiles_x + goal_x / HT;
+    // the init kernel clears every flag and counter this call will touch, and seeds the goal
+    heur_init_kernel<<<148 * 8, 256, 0, stream>>>(d_field_out, n, flags, n_flags, goal_index, goal_tile);
+    uint32_t round = 0;
+    uint32_t counters[4];
+    const uint64_t max_rounds = static_cast<uint64_t>(n) + 8;
+    for (;;)
+    {
+        for (int k = 0; k < ROUNDS_PER_CHECK; ++k, ++round)
+            heur_round_kernel<<<nT, HT_THREADS, 0, stream>>>(d_field_out, d_cost, travel_dev, W, H, tiles_x, tiles_y, flags, round);
+        e = cudaGetLastError();
+        if (e == cudaSuccess)
+            e = cudaMemcpyAsync(counters, flags + 2 * static_cast<size_t>(nT), sizeof(counters), cudaMemcpyDeviceToHost, stream);
+        if (e == cudaSuccess)
+            e = cudaStreamSynchronize(stream);
+        if (e != cudaSuccess)
+            return pp_fail(nullptr, PP_ERR_CUDA, "pp_heuristic_build_noalloc: relaxation round %u: %s", round, cudaGetErrorString(e));
+        if (counters[round & 3] == 0)
+            break;
+        if (round >= max_rounds)
+            return pp_fail(nullptr, PP_ERR_STATE, "pp_heuristic_build_noalloc: relaxation did not converge");
+    }
+    heur_finalize_kernel<<<148 * 8, 256, 0, stream>>>(d_field_out, n);
+    e = cudaGetLastError();
+    if (e == cudaSuccess)
+        e = cudaStreamSynchronize(stream);
+    if (e != cudaSuccess)
+        return pp_fail(nullptr, PP_ERR_CUDA, "pp_heuristic_build_noalloc: %s", cudaGetErrorString(e));
+    return PP_OK;
+}
