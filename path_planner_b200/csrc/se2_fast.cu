@@ -1,16 +1,696 @@
-// K1 fast path (tiled, shared-memory brick tables). Placeholder: declines everything so that the
-// exact generic kernel runs; filled in once the generic path is parity-green.
+// K1 fast path: tiled SE2 volume with shared-memory "brick" tables.
+//
+// For one heading bin the reference's footprint test is, away from the few places where float
+// rounding makes the integer sample offsets position-dependent, a grey-scale dilation of the
+// costmap by a fixed set S_t of integer offsets (collision_checker.cpp:155-166).
+// max over uint8 is exact, idempotent and order-free, so S_t may be covered by translated copies
+// of small "bricks" B (S_t = U_i (B_i + o_i), overlaps allowed, no point outside S_t), and
+//   V[t][y][x] = max_i T_{B_i}[y + o_i.y][x + o_i.x],   T_B = dilation of the costmap tile by B.
+// The brick tables are heading-independent: a CTA stages one 64x32 tile (+ halo) of the costmap in
+// shared memory, derives up to 11 brick tables from it by doubling (each table is the max of two
+// shifted earlier tables), and then serves ALL heading bins of the launch from them, turning the
+// P = 48 gathers per cell of the reference into ~17 aligned 32-bit shared-memory loads per four
+// cells. Every table is stored in four byte-shifted copies so that the word for any x offset is an
+// aligned LDS.32.
+//
+// sm_100a has no native per-byte max (__vmaxu4 is emulated with ~7 instructions). It does have the
+// 3-input VIMNMX3.U16x2. A u16 max is decided by the high byte, so on a raw word (b0,b1,b2,b3) it
+// yields the correct maxima of b1 and b3, and on the word shifted left by 8 bits those of b0 and
+// b2; the low bytes are don't-cares. Two accumulators per thread, two samples per instruction;
+// the shift is an IMAD on the otherwise idle FMA pipe.
+//
+// Exactness: the host planner evaluates the reference expression for every column, row, point
+// and bin with the same float operations (and the host libm's cosf/sinf), finds the ranges of
+// columns / rows over which all offsets are constant, and lets the fast kernel handle only tiles
+// that lie inside such ranges (up to 2 ranges per axis and bin). All other (tile, bin) pairs go
+// to the exact generic kernel through a work list.
 #include "se2_plan.h"
+
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <map>
+#include <vector>
+
+namespace
+{
+constexpr int FT_W = 64, FT_H = 32, FT_THREADS = 512;
+constexpr int MAX_TABLES = 12;
+constexpr int MAX_T_PER_LAUNCH = 160;
+constexpr int MAX_LIST_WORDS = 6400;
+constexpr int MAX_R = 15;
+constexpr size_t SMEM_LIMIT = 227 * 1024;
+
+struct FastArgs
+{
+    const uint8_t *cost;
+    uint8_t *vol;
+    const uint8_t *xclass;  // [n_theta][tiles_x]: 0/1 = column range class, 255 = not uniform
+    const uint8_t *yclass;  // [n_theta][tiles_y]
+    uint32_t W, H, tiles_x, tiles_y, tile_x0, tile_y0;
+    int32_t R, PW, rows, copy_words, n_tables;
+    uint32_t t_first, n_t;
+    uint8_t rec_a[MAX_TABLES], rec_b[MAX_TABLES];
+    int8_t rec_du[MAX_TABLES], rec_dv[MAX_TABLES];
+    uint16_t list_off[MAX_T_PER_LAUNCH][4];
+    uint16_t list_len[MAX_T_PER_LAUNCH][4];
+    uint32_t lists[MAX_LIST_WORDS];  // byte offsets into shared memory, relative to the thread's base
+};
+static_assert(sizeof(FastArgs) < 32764, "kernel parameter block too large");
+
+__device__ __forceinline__ uint32_t bytemax4(uint32_t a, uint32_t b)
+{
+    const uint32_t odd = __vmaxu2(a, b);                 // high byte of each half = max(b1), max(b3)
+    const uint32_t even = __vmaxu2(a << 8, b << 8);      // high byte of each half = max(b0), max(b2)
+    return __byte_perm(even, odd, 0x7351);
+}
+
+__device__ __forceinline__ uint32_t lds32(uint32_t addr)
+{
+    uint32_t v;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr));
+    return v;
+}
+
+__global__ void __launch_bounds__(FT_THREADS, 1) se2_fast_kernel(const __grid_constant__ FastArgs a)
+{
+    extern __shared__ __align__(16) uint32_t sm[];
+    __shared__ uint8_t s_cls[MAX_T_PER_LAUNCH];
+    __shared__ int s_any;
+    const int tid = threadIdx.x;
+    const uint32_t tile_x = a.tile_x0 + blockIdx.x, tile_y = a.tile_y0 + blockIdx.y;
+    if (tid == 0)
+        s_any = 0;
+    __syncthreads();
+    for (uint32_t t = tid; t < a.n_t; t += FT_THREADS)
+    {
+        const uint32_t cx = a.xclass[static_cast<size_t>(a.t_first + t) * a.tiles_x + tile_x];
+        const uint32_t cy = a.yclass[static_cast<size_t>(a.t_first + t) * a.tiles_y + tile_y];
+        const uint32_t cls = (cx > 1 || cy > 1) ? 255u : cx * 2 + cy;
+        s_cls[t] = static_cast<uint8_t>(cls);
+        if (cls != 255u)
+            s_any = 1;
+    }
+    __syncthreads();
+    if (!s_any)
+        return;  // every bin of this tile belongs to the generic work list
+
+    const int R = a.R, PW = a.PW, rows = a.rows, CW = a.copy_words;
+    const int tx0 = static_cast<int>(tile_x) * FT_W, ty0 = static_cast<int>(tile_y) * FT_H;
+    const int W = static_cast<int>(a.W), H = static_cast<int>(a.H);
+
+    // costmap tile with halo, copy 0: word w of row r holds columns tx0-R+4w .. +3; zeros outside the map
+    for (int i = tid; i < CW; i += FT_THREADS)
+    {
+        const int r = i / PW, w = i - r * PW;
+        const int gy = ty0 - R + r, ax = tx0 - R + 4 * w;
+        uint32_t v = 0;
+        if (gy >= 0 && gy < H)
+        {
+            const int ga = ax & ~3, sh = ax & 3;
+            const uint8_t *rowp = a.cost + static_cast<size_t>(gy) * a.W;
+            const uint32_t lo = (ga >= 0 && ga < W) ? *reinterpret_cast<const uint32_t *>(rowp + ga) : 0u;
+            const uint32_t hi = (sh && ga + 4 >= 0 && ga + 4 < W) ? *reinterpret_cast<const uint32_t *>(rowp + ga + 4) : 0u;
+            v = __funnelshift_r(lo, hi, 8 * sh);
+        }
+        sm[i] = v;
+    }
+    __syncthreads();
+    // byte-shifted copies 1..3 of the costmap tile
+    for (int i = tid; i < CW; i += FT_THREADS)
+    {
+        const int w = i % PW;
+        const uint32_t lo = sm[i], hi = (w + 1 < PW) ? sm[i + 1] : 0u;
+        sm[CW + i] = __funnelshift_r(lo, hi, 8);
+        sm[2 * CW + i] = __funnelshift_r(lo, hi, 16);
+        sm[3 * CW + i] = __funnelshift_r(lo, hi, 24);
+    }
+    __syncthreads();
+    // derived brick tables: T_k = max(T_a, T_b shifted by (du, dv)), all four copies
+    for (int k = 1; k < a.n_tables; ++k)
+    {
+        const uint32_t *A = sm + a.rec_a[k] * 4 * CW;
+        const uint32_t *B = sm + a.rec_b[k] * 4 * CW;
+        uint32_t *D = sm + k * 4 * CW;
+        const int du = a.rec_du[k], dv = a.rec_dv[k];
+        for (int i = tid; i < 4 * CW; i += FT_THREADS)
+        {
+            const int s = i / CW, j = i - s * CW;
+            const int r = j / PW, w = j - r * PW;
+            const int r2 = r + dv, sd = s + du;
+            const int s2 = sd & 3, w2 = w + (sd >> 2);
+            uint32_t vb = 0;
+            if (r2 >= 0 && r2 < rows && w2 >= 0 && w2 < PW)
+                vb = B[s2 * CW + r2 * PW + w2];
+            D[i] = bytemax4(A[i], vb);
+        }
+        __syncthreads();
+    }
+
+    // output phase: one quad (4 cells along x) per thread and bin
+    const int warp = tid >> 5, lane = tid & 31;
+    const int q = lane & 15;
+    const int row = (warp >> 3) * 16 + (warp & 7) + 8 * (lane >> 4);  // half-warps 8 rows apart: bank-conflict free for PW = 2 mod 4
+    const uint32_t sbase = static_cast<uint32_t>(__cvta_generic_to_shared(sm)) + static_cast<uint32_t>((row * PW + q) * 4);
+    const int gx = tx0 + 4 * q, gy = ty0 + row;
+    const bool inside = gx < W && gy < H;
+    const size_t plane = static_cast<size_t>(a.W) * a.H;
+    uint8_t *out = a.vol + plane * a.t_first + static_cast<size_t>(gy) * a.W + gx;
+
+    for (uint32_t t = 0; t < a.n_t; ++t, out += plane)
+    {
+        const uint32_t cls = s_cls[t];
+        if (cls == 255u)
+            continue;
+        const uint32_t off = a.list_off[t][cls], len = a.list_len[t][cls];
+        uint32_t acc_odd = 0, acc_even = 0;
+#pragma unroll 4
+        for (uint32_t i = 0; i < len; i += 2)
+        {
+            const uint32_t w1 = lds32(sbase + a.lists[off + i]);
+            const uint32_t w2 = lds32(sbase + a.lists[off + i + 1]);
+            acc_odd = __vimax3_u16x2(acc_odd, w1, w2);
+            acc_even = __vimax3_u16x2(acc_even, w1 * 256u, w2 * 256u);
+        }
+        if (inside)
+            *reinterpret_cast<uint32_t *>(out) = __byte_perm(acc_even, acc_odd, 0x7351);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// host planner
+// ---------------------------------------------------------------------------------------------
+struct Recipe
+{
+    int a, b, du, dv;
+};
+using Library = std::vector<Recipe>;
+
+// index 0 is always the costmap itself (the one-point brick)
+const Library LIB_STAIRS = {{0, 0, 0, 0}, {0, 0, 1, 0}, {0, 0, 0, 1}, {0, 0, 1, 1}, {0, 0, 1, -1}, {1, 1, 2, 0},
+                            {2, 2, 0, 2}, {1, 1, 2, 1}, {1, 1, 2, -1}, {2, 2, 1, 2}, {2, 2, -1, 2}, {5, 5, 4, 0}};
+const Library LIB_RUNS3 = {{0, 0, 0, 0}, {0, 0, 1, 0}, {0, 0, 0, 1}, {0, 0, 1, 1}, {0, 0, 1, -1}, {1, 0, 2, 0},
+                           {2, 0, 0, 2}, {3, 0, 2, 2}, {4, 0, 2, -2}, {5, 5, 3, 0}, {6, 6, 0, 3}, {3, 3, 2, 2}};
+const Library LIB_BLOCKS = {{0, 0, 0, 0}, {0, 0, 1, 0}, {0, 0, 0, 1}, {1, 1, 0, 1}, {1, 1, 2, 0}, {2, 2, 0, 2},
+                            {3, 3, 2, 0}, {6, 6, 0, 2}, {4, 4, 4, 0}, {5, 5, 0, 4}, {7, 7, 4, 0}, {10, 10, 0, 4}};
+const Library LIB_RUNS = {{0, 0, 0, 0}, {0, 0, 1, 0}, {0, 0, 0, 1}, {0, 0, 1, 1}, {0, 0, 1, -1}, {1, 1, 2, 0},
+                          {2, 2, 0, 2}, {3, 3, 2, 2}, {4, 4, 2, -2}, {5, 5, 4, 0}, {6, 6, 0, 4}};
+
+using Offsets = std::vector<std::pair<int, int>>;  // sorted, unique (dx, dy)
+
+struct Placement
+{
+    int brick, ox, oy;
+};
+
+struct Bits
+{
+    uint64_t w[16];
+    void clear() { std::memset(w, 0, sizeof(w)); }
+    void set(int i) { w[i >> 6] |= 1ull << (i & 63); }
+    bool get(int i) const { return (w[i >> 6] >> (i & 63)) & 1ull; }
+};
+
+std::vector<Offsets> brick_points(const Library &lib, int n)
+{
+    std::vector<Offsets> pts(n);
+    pts[0] = {{0, 0}};
+    for (int k = 1; k < n; ++k)
+    {
+        Offsets p = pts[lib[k].a];
+        for (auto &q : pts[lib[k].b])
+            p.emplace_back(q.first + lib[k].du, q.second + lib[k].dv);
+        std::sort(p.begin(), p.end());
+        p.erase(std::unique(p.begin(), p.end()), p.end());
+        pts[k] = p;
+    }
+    return pts;
+}
+
+// Greedy exact cover of S by brick placements that lie entirely inside S, then reverse deletion
+// of placements made redundant by later ones.
+std::vector<Placement> cover_set(const Offsets &S, const std::vector<Offsets> &bricks, int R)
+{
+    const int side = 2 * R + 1;
+    auto idx = [&](int x, int y) { return (y + R) * side + (x + R); };
+    Bits in;
+    in.clear();
+    for (auto &p : S)
+        in.set(idx(p.first, p.second));
+    struct Cand
+    {
+        Placement pl;
+        Bits mask;
+        int npts;
+    };
+    std::vector<Cand> cands;
+    // every valid placement has its first (smallest) brick point on a cell of S, so anchoring that
+    // point on each cell of S enumerates each placement exactly once
+    for (int k = static_cast<int>(bricks.size()) - 1; k >= 0; --k)
+        for (auto &anchor : S)
+        {
+            const int ox = anchor.first - bricks[k][0].first, oy = anchor.second - bricks[k][0].second;
+            bool ok = true;
+            Cand c;
+            c.mask.clear();
+            for (auto &q : bricks[k])
+            {
+                const int x = ox + q.first, y = oy + q.second;
+                if (x < -R || x > R || y < -R || y > R || !in.get(idx(x, y)))
+                {
+                    ok = false;
+                    break;
+                }
+                c.mask.set(idx(x, y));
+            }
+            if (!ok)
+                continue;
+            c.pl = {k, ox, oy};
+            c.npts = static_cast<int>(bricks[k].size());
+            cands.push_back(c);
+        }
+    Bits unc = in;
+    std::vector<int> chosen;
+    size_t remaining = S.size();
+    while (remaining > 0)
+    {
+        int best = -1, best_gain = 0;
+        for (size_t c = 0; c < cands.size(); ++c)
+        {
+            int g = 0;
+            for (int i = 0; i < 16; ++i)
+                g += __builtin_popcountll(cands[c].mask.w[i] & unc.w[i]);
+            if (g > best_gain || (g == best_gain && g > 0 && best >= 0 && cands[c].npts < cands[best].npts))
+            {
+                best = static_cast<int>(c);
+                best_gain = g;
+            }
+        }
+        chosen.push_back(best);
+        for (int i = 0; i < 16; ++i)
+            unc.w[i] &= ~cands[best].mask.w[i];
+        remaining -= best_gain;
+    }
+    // reverse deletion
+    std::vector<char> keep(chosen.size(), 1);
+    for (size_t c = 0; c < chosen.size(); ++c)
+    {
+        Bits others;
+        others.clear();
+        for (size_t d = 0; d < chosen.size(); ++d)
+            if (d != c && keep[d])
+                for (int i = 0; i < 16; ++i)
+                    others.w[i] |= cands[chosen[d]].mask.w[i];
+        bool redundant = true;
+        for (int i = 0; i < 16; ++i)
+            if (cands[chosen[c]].mask.w[i] & ~others.w[i])
+            {
+                redundant = false;
+                break;
+            }
+        if (redundant)
+            keep[c] = 0;
+    }
+    std::vector<Placement> out;
+    for (size_t c = 0; c < chosen.size(); ++c)
+        if (keep[c])
+            out.push_back(cands[chosen[c]].pl);
+    return out;
+}
+
+// One axis of one bin: integer offsets floor(f(pos)) - pos for every position and point, the
+// maximal ranges of positions over which all of them are constant, and the two longest ranges.
+struct AxisClasses
+{
+    int n_classes = 0;
+    int lo[2], hi[2];               // position ranges [lo, hi)
+    std::vector<int> offs[2];       // per point
+};
+
+}  // namespace
 
 struct Se2Plan
 {
-    int unused;
+    // key
+    uint32_t W = 0, H = 0, n_theta = 0;
+    float ox = 0, oy = 0, ot = 0;
+    std::vector<int32_t> fp;
+    // geometry
+    bool usable = false;
+    int R = 0, PW = 0, rows = 0, copy_words = 0, n_tables = 0;
+    size_t smem_bytes = 0;
+    Library lib;
+    uint32_t tiles_x = 0, tiles_y = 0;
+    uint8_t *d_xclass = nullptr, *d_yclass = nullptr;
+    std::vector<uint8_t> h_xclass, h_yclass;
+    // per bin: up to 4 sample lists (class = cx*2 + cy)
+    std::vector<uint32_t> lists;
+    std::vector<uint32_t> list_off;  // [n_theta*4]
+    std::vector<uint16_t> list_len;  // [n_theta*4]
+    // generic work list, sorted by bin
+    std::vector<uint32_t> h_work;
+    std::vector<uint32_t> work_off;  // [n_theta+1] entry index
+    uint32_t *d_work = nullptr;
+    ~Se2Plan()
+    {
+        cudaFree(d_xclass);
+        cudaFree(d_yclass);
+        cudaFree(d_work);
+    }
 };
 
 void pp_se2_plan_free(pp_handle h)
 {
-    delete h->plan;
+    if (h->plan)
+    {
+        cudaSetDevice(h->device);
+        cudaStreamSynchronize(h->stream);
+        delete h->plan;
+    }
     h->plan = nullptr;
 }
 
-pp_status pp_se2_launch_fast(pp_handle, uint32_t, uint32_t, uint32_t, uint32_t) { return PP_INTERNAL_DECLINED; }
+namespace
+{
+// the reference expressions, one float operation at a time (no contraction on the host either)
+inline int ref_x_index(float x, float px, float py, float c, float s)
+{
+    const float a = px * c;
+    const float b = py * s;
+    const float t = x + a;
+    const float xn = t - b;
+    return static_cast<int>(floorf(xn));
+}
+inline int ref_y_index(float y, float px, float py, float c, float s)
+{
+    const float a = px * s;
+    const float b = py * c;
+    const float t = y + a;
+    const float yn = t + b;
+    return static_cast<int>(floorf(yn));
+}
+
+AxisClasses classify_axis(bool is_x, uint32_t n, float sample_off, const std::vector<int32_t> &fp, float c, float s,
+                          std::vector<int8_t> &scratch)
+{
+    const size_t P = fp.size() / 2;
+    scratch.resize(P * n);
+    for (size_t p = 0; p < P; ++p)
+    {
+        const float px = static_cast<float>(fp[2 * p]), py = static_cast<float>(fp[2 * p + 1]);
+        int8_t *dst = scratch.data() + p * n;
+        for (uint32_t i = 0; i < n; ++i)
+        {
+            const float pos = static_cast<float>(i) + sample_off;
+            const int idx = is_x ? ref_x_index(pos, px, py, c, s) : ref_y_index(pos, px, py, c, s);
+            int d = idx - static_cast<int>(i);
+            d = std::max(-127, std::min(127, d));
+            dst[i] = static_cast<int8_t>(d);
+        }
+    }
+    // boundaries of constant ranges
+    std::vector<uint32_t> starts{0};
+    for (uint32_t i = 1; i < n; ++i)
+    {
+        bool same = true;
+        for (size_t p = 0; p < P && same; ++p)
+            same = scratch[p * n + i] == scratch[p * n + i - 1];
+        if (!same)
+            starts.push_back(i);
+    }
+    starts.push_back(n);
+    // two longest ranges
+    std::vector<std::pair<uint32_t, uint32_t>> ranges;
+    for (size_t k = 0; k + 1 < starts.size(); ++k)
+        ranges.emplace_back(starts[k + 1] - starts[k], starts[k]);
+    std::sort(ranges.begin(), ranges.end(), [](auto &l, auto &r) { return l.first > r.first; });
+    AxisClasses out;
+    out.n_classes = static_cast<int>(std::min<size_t>(2, ranges.size()));
+    for (int k = 0; k < out.n_classes; ++k)
+    {
+        out.lo[k] = static_cast<int>(ranges[k].second);
+        out.hi[k] = static_cast<int>(ranges[k].second + ranges[k].first);
+        out.offs[k].resize(P);
+        for (size_t p = 0; p < P; ++p)
+            out.offs[k][p] = scratch[p * n + out.lo[k]];
+    }
+    return out;
+}
+
+bool plan_matches(const Se2Plan *p, pp_handle h)
+{
+    return p && p->W == h->W && p->H == h->H && p->n_theta == h->n_theta && p->ox == h->ox && p->oy == h->oy &&
+           p->ot == h->ot && p->fp == h->fp;
+}
+
+pp_status build_plan(pp_handle h)
+{
+    Se2Plan *pl = new Se2Plan();
+    h->plan = pl;
+    pl->W = h->W;
+    pl->H = h->H;
+    pl->n_theta = h->n_theta;
+    pl->ox = h->ox;
+    pl->oy = h->oy;
+    pl->ot = h->ot;
+    pl->fp = h->fp;
+    pl->usable = false;
+    if (h->W % 4 != 0)
+        return PP_OK;  // rows would not be 4-byte aligned: leave everything to the generic kernel
+    const uint32_t nt = h->n_theta;
+    pl->tiles_x = (h->W + FT_W - 1) / FT_W;
+    pl->tiles_y = (h->H + FT_H - 1) / FT_H;
+
+    // 1. exact offsets and uniform ranges for every bin
+    std::vector<AxisClasses> xc(nt), yc(nt);
+    std::vector<int8_t> scratch;
+    int R = 0;
+    for (uint32_t t = 0; t < nt; ++t)
+    {
+        const float c = h->host_trig[t].x, s = h->host_trig[t].y;
+        xc[t] = classify_axis(true, h->W, h->ox, h->fp, c, s, scratch);
+        yc[t] = classify_axis(false, h->H, h->oy, h->fp, c, s, scratch);
+        for (int k = 0; k < xc[t].n_classes; ++k)
+            for (int d : xc[t].offs[k])
+                R = std::max(R, std::abs(d));
+        for (int k = 0; k < yc[t].n_classes; ++k)
+            for (int d : yc[t].offs[k])
+                R = std::max(R, std::abs(d));
+    }
+    if (R > MAX_R)
+        return PP_OK;
+    // 2. geometry
+    pl->R = R;
+    pl->rows = FT_H + 2 * R;
+    int pw = (FT_W + 2 * R + 3) / 4;
+    while (pw % 4 != 2)
+        ++pw;
+    pl->PW = pw;
+    pl->copy_words = pl->rows * pl->PW;
+    const size_t table_bytes = static_cast<size_t>(4) * pl->copy_words * 4;
+    const int slots = static_cast<int>(std::min<size_t>(MAX_TABLES, (SMEM_LIMIT - 1024) / table_bytes));
+    if (slots < 3)
+        return PP_OK;
+
+    // 3. distinct offset sets per (bin, class)
+    auto make_set = [&](uint32_t t, int cx, int cy) {
+        Offsets S;
+        const size_t P = h->fp.size() / 2;
+        for (size_t p = 0; p < P; ++p)
+            S.emplace_back(xc[t].offs[cx][p], yc[t].offs[cy][p]);
+        std::sort(S.begin(), S.end());
+        S.erase(std::unique(S.begin(), S.end()), S.end());
+        return S;
+    };
+    // 4. choose the library on a sample of bins
+    const Library *candidates[] = {&LIB_STAIRS, &LIB_RUNS3, &LIB_BLOCKS, &LIB_RUNS};
+    const Library *best_lib = nullptr;
+    size_t best_total = ~static_cast<size_t>(0);
+    const uint32_t step = std::max(1u, nt / 18);
+    for (const Library *cand : candidates)
+    {
+        const int n = std::min<int>(slots, static_cast<int>(cand->size()));
+        auto bricks = brick_points(*cand, n);
+        size_t total = 0;
+        for (uint32_t t = 0; t < nt; t += step)
+            total += cover_set(make_set(t, 0, 0), bricks, R).size();
+        if (total < best_total)
+        {
+            best_total = total;
+            best_lib = cand;
+        }
+    }
+    pl->n_tables = std::min<int>(slots, static_cast<int>(best_lib->size()));
+    pl->lib.assign(best_lib->begin(), best_lib->begin() + pl->n_tables);
+    pl->smem_bytes = table_bytes * pl->n_tables;
+    auto bricks = brick_points(pl->lib, pl->n_tables);
+
+    // 5. covers -> sample lists (byte offsets relative to the thread's base address)
+    pl->list_off.assign(static_cast<size_t>(nt) * 4, 0);
+    pl->list_len.assign(static_cast<size_t>(nt) * 4, 0);
+    std::map<Offsets, std::vector<uint32_t>> memo;
+    for (uint32_t t = 0; t < nt; ++t)
+        for (int cx = 0; cx < xc[t].n_classes; ++cx)
+            for (int cy = 0; cy < yc[t].n_classes; ++cy)
+            {
+                Offsets S = make_set(t, cx, cy);
+                auto it = memo.find(S);
+                if (it == memo.end())
+                {
+                    std::vector<uint32_t> words;
+                    for (const Placement &p : cover_set(S, bricks, R))
+                    {
+                        const int ax = R + p.ox, ay = R + p.oy;  // >= 0
+                        const uint32_t word = static_cast<uint32_t>((p.brick * 4 + (ax & 3)) * pl->copy_words + ay * pl->PW + (ax >> 2));
+                        words.push_back(word * 4);
+                    }
+                    if (words.size() & 1)
+                        words.push_back(words.back());  // samples are consumed in pairs
+                    it = memo.emplace(S, words).first;
+                }
+                pl->list_off[t * 4 + cx * 2 + cy] = static_cast<uint32_t>(pl->lists.size());
+                pl->list_len[t * 4 + cx * 2 + cy] = static_cast<uint16_t>(it->second.size());
+                pl->lists.insert(pl->lists.end(), it->second.begin(), it->second.end());
+            }
+
+    // 6. tile classes and the generic work list
+    pl->h_xclass.assign(static_cast<size_t>(nt) * pl->tiles_x, 255);
+    pl->h_yclass.assign(static_cast<size_t>(nt) * pl->tiles_y, 255);
+    pl->work_off.assign(nt + 1, 0);
+    for (uint32_t t = 0; t < nt; ++t)
+    {
+        for (uint32_t tx = 0; tx < pl->tiles_x; ++tx)
+        {
+            const int lo = static_cast<int>(tx * FT_W), hi = static_cast<int>(std::min(h->W, (tx + 1) * FT_W));
+            for (int k = 0; k < xc[t].n_classes; ++k)
+                if (lo >= xc[t].lo[k] && hi <= xc[t].hi[k])
+                    pl->h_xclass[static_cast<size_t>(t) * pl->tiles_x + tx] = static_cast<uint8_t>(k);
+        }
+        for (uint32_t ty = 0; ty < pl->tiles_y; ++ty)
+        {
+            const int lo = static_cast<int>(ty * FT_H), hi = static_cast<int>(std::min(h->H, (ty + 1) * FT_H));
+            for (int k = 0; k < yc[t].n_classes; ++k)
+                if (lo >= yc[t].lo[k] && hi <= yc[t].hi[k])
+                    pl->h_yclass[static_cast<size_t>(t) * pl->tiles_y + ty] = static_cast<uint8_t>(k);
+        }
+        pl->work_off[t] = static_cast<uint32_t>(pl->h_work.size() / 2);
+        for (uint32_t ty = 0; ty < pl->tiles_y; ++ty)
+            for (uint32_t tx = 0; tx < pl->tiles_x; ++tx)
+                if (pl->h_xclass[static_cast<size_t>(t) * pl->tiles_x + tx] == 255 ||
+                    pl->h_yclass[static_cast<size_t>(t) * pl->tiles_y + ty] == 255)
+                {
+                    pl->h_work.push_back(tx | (ty << 16));
+                    pl->h_work.push_back(t);
+                }
+    }
+    pl->work_off[nt] = static_cast<uint32_t>(pl->h_work.size() / 2);
+
+    PP_CUDA(h, cudaMalloc(reinterpret_cast<void **>(&pl->d_xclass), pl->h_xclass.size()));
+    PP_CUDA(h, cudaMalloc(reinterpret_cast<void **>(&pl->d_yclass), pl->h_yclass.size()));
+    PP_CUDA(h, cudaMemcpyAsync(pl->d_xclass, pl->h_xclass.data(), pl->h_xclass.size(), cudaMemcpyHostToDevice, h->stream));
+    PP_CUDA(h, cudaMemcpyAsync(pl->d_yclass, pl->h_yclass.data(), pl->h_yclass.size(), cudaMemcpyHostToDevice, h->stream));
+    if (!pl->h_work.empty())
+    {
+        PP_CUDA(h, cudaMalloc(reinterpret_cast<void **>(&pl->d_work), pl->h_work.size() * sizeof(uint32_t)));
+        PP_CUDA(h, cudaMemcpyAsync(pl->d_work, pl->h_work.data(), pl->h_work.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, h->stream));
+    }
+    PP_CUDA(h, cudaStreamSynchronize(h->stream));
+    PP_CUDA(h, cudaFuncSetAttribute(se2_fast_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(pl->smem_bytes)));
+    pl->usable = true;
+    return PP_OK;
+}
+}  // namespace
+
+pp_status pp_se2_launch_fast(pp_handle h, uint32_t x0, uint32_t y0, uint32_t x1, uint32_t y1)
+{
+    if (!plan_matches(h->plan, h))
+    {
+        pp_se2_plan_free(h);
+        pp_status s = build_plan(h);
+        if (s != PP_OK)
+            return s;
+    }
+    Se2Plan *pl = h->plan;
+    if (!pl->usable)
+        return PP_INTERNAL_DECLINED;
+
+    const uint32_t tx_lo = x0 / FT_W, tx_hi = (x1 + FT_W - 1) / FT_W;
+    const uint32_t ty_lo = y0 / FT_H, ty_hi = (y1 + FT_H - 1) / FT_H;
+    static thread_local FastArgs args;  // ~28 KB: keep it off the stack
+    args.cost = h->d_cost;
+    args.vol = h->d_vol;
+    args.xclass = pl->d_xclass;
+    args.yclass = pl->d_yclass;
+    args.W = h->W;
+    args.H = h->H;
+    args.tiles_x = pl->tiles_x;
+    args.tiles_y = pl->tiles_y;
+    args.tile_x0 = tx_lo;
+    args.tile_y0 = ty_lo;
+    args.R = pl->R;
+    args.PW = pl->PW;
+    args.rows = pl->rows;
+    args.copy_words = pl->copy_words;
+    args.n_tables = pl->n_tables;
+    for (int k = 0; k < pl->n_tables; ++k)
+    {
+        args.rec_a[k] = static_cast<uint8_t>(pl->lib[k].a);
+        args.rec_b[k] = static_cast<uint8_t>(pl->lib[k].b);
+        args.rec_du[k] = static_cast<int8_t>(pl->lib[k].du);
+        args.rec_dv[k] = static_cast<int8_t>(pl->lib[k].dv);
+    }
+    const dim3 grid(tx_hi - tx_lo, ty_hi - ty_lo, 1);
+    const uint64_t n_tiles = static_cast<uint64_t>(grid.x) * grid.y;
+    double sample_sum = 0.0;
+    uint64_t fast_pairs = 0, generic_pairs = 0;
+
+    uint32_t t = h->t_begin;
+    while (t < h->t_end)
+    {
+        // as many bins as fit in the parameter block
+        uint32_t n = 0, words = 0;
+        while (t + n < h->t_end && n < MAX_T_PER_LAUNCH)
+        {
+            uint32_t need = 0;
+            for (int c = 0; c < 4; ++c)
+                need += pl->list_len[(t + n) * 4 + c];
+            if (words + need > MAX_LIST_WORDS)
+                break;
+            for (int c = 0; c < 4; ++c)
+            {
+                const uint32_t len = pl->list_len[(t + n) * 4 + c];
+                args.list_off[n][c] = static_cast<uint16_t>(words);
+                args.list_len[n][c] = static_cast<uint16_t>(len);
+                std::memcpy(args.lists + words, pl->lists.data() + pl->list_off[(t + n) * 4 + c], len * sizeof(uint32_t));
+                words += len;
+            }
+            ++n;
+        }
+        PP_REQUIRE(h, n > 0, PP_ERR_RANGE, "a single heading bin needs more than %d sample words", MAX_LIST_WORDS);
+        args.t_first = t;
+        args.n_t = n;
+        se2_fast_kernel<<<grid, FT_THREADS, pl->smem_bytes, h->stream>>>(args);
+        h->launches++;
+        PP_CUDA(h, cudaGetLastError());
+        // bookkeeping + the exact path for the (tile, bin) pairs outside uniform ranges
+        for (uint32_t k = 0; k < n; ++k)
+        {
+            const uint32_t nw = pl->work_off[t + k + 1] - pl->work_off[t + k];
+            generic_pairs += nw;
+            fast_pairs += static_cast<uint64_t>(pl->tiles_x) * pl->tiles_y - nw;
+            sample_sum += pl->list_len[(t + k) * 4];
+        }
+        const uint32_t w0 = pl->work_off[t], w1 = pl->work_off[t + n];
+        if (w1 > w0)
+        {
+            pp_status s = pp_se2_generic_worklist(h, pl->d_work + 2 * static_cast<size_t>(w0), w1 - w0);
+            if (s != PP_OK)
+                return s;
+        }
+        t += n;
+    }
+    (void)n_tiles;
+    h->stat_fast_tiles = fast_pairs;
+    h->stat_samples_per_cell = sample_sum / std::max(1u, h->t_end - h->t_begin);
+    return PP_OK;
+}
