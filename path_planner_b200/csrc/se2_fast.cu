@@ -54,8 +54,9 @@ struct FastArgs
     int8_t rec_du[MAX_TABLES], rec_dv[MAX_TABLES];
     uint16_t list_off[MAX_T_PER_LAUNCH][4];
     uint16_t list_len[MAX_T_PER_LAUNCH][4];
-    uint32_t lists[MAX_LIST_WORDS];  // byte offsets into shared memory, relative to the thread's base
+    alignas(16) uint32_t lists[MAX_LIST_WORDS];  // byte offsets into shared memory, relative to the thread's base
 };
+static_assert(FT_THREADS == 512, "run_group dispatches 4 groups of 4 warps");
 static_assert(sizeof(FastArgs) < 32764, "kernel parameter block too large");
 
 __device__ __forceinline__ uint32_t bytemax4(uint32_t a, uint32_t b)
@@ -72,12 +73,84 @@ __device__ __forceinline__ uint32_t lds32(uint32_t addr)
     return v;
 }
 
+
+constexpr int NGROUPS = FT_THREADS / 128;
+
+template <int T_START>
+__device__ __forceinline__ void run_bins(const FastArgs &a, const uint32_t *sm, const uint8_t *s_cls, int gw, int lane,
+                                         int tx0, int ty0)
+{
+    // T_START is a literal in each instantiation, so the bin index and with it every list offset
+    // stays warp-uniform: descriptors travel through the uniform datapath and LDS takes [R + UR].
+    const int PW = a.PW;
+    const int q = lane & 15;
+    const int row0 = gw + 8 * (lane >> 4);
+    const uint32_t b0 = static_cast<uint32_t>(__cvta_generic_to_shared(sm)) + static_cast<uint32_t>((row0 * PW + q) * 4);
+    const uint32_t b1 = b0 + 4 * PW * 4, b2 = b0 + 16 * PW * 4, b3 = b0 + 20 * PW * 4;
+    const int W = static_cast<int>(a.W), H = static_cast<int>(a.H);
+    const int gx = tx0 + 4 * q, gy = ty0 + row0;
+    const bool in_x = gx < W;
+    const size_t plane = static_cast<size_t>(a.W) * a.H;
+    const size_t rs = a.W;
+    uint8_t *out = a.vol + plane * (a.t_first + T_START) + static_cast<size_t>(gy) * a.W + gx;
+    for (uint32_t t = T_START; t < a.n_t; t += NGROUPS, out += NGROUPS * plane)
+    {
+        const uint32_t cls = s_cls[t];
+        if (cls == 255u)
+            continue;
+        const uint32_t off = a.list_off[t][cls], len = a.list_len[t][cls];  // len is even
+        uint32_t o0 = 0, e0 = 0, o1 = 0, e1 = 0, o2 = 0, e2 = 0, o3 = 0, e3 = 0;
+#pragma unroll 4
+        for (uint32_t i = 0; i < len; i += 2)
+        {
+            const uint32_t d1 = a.lists[off + i], d2 = a.lists[off + i + 1];
+            const uint32_t u0 = lds32(b0 + d1), v0 = lds32(b0 + d2);
+            const uint32_t u1 = lds32(b1 + d1), v1 = lds32(b1 + d2);
+            const uint32_t u2 = lds32(b2 + d1), v2 = lds32(b2 + d2);
+            const uint32_t u3 = lds32(b3 + d1), v3 = lds32(b3 + d2);
+            o0 = __vimax3_u16x2(o0, u0, v0);
+            e0 = __vimax3_u16x2(e0, u0 * 256u, v0 * 256u);
+            o1 = __vimax3_u16x2(o1, u1, v1);
+            e1 = __vimax3_u16x2(e1, u1 * 256u, v1 * 256u);
+            o2 = __vimax3_u16x2(o2, u2, v2);
+            e2 = __vimax3_u16x2(e2, u2 * 256u, v2 * 256u);
+            o3 = __vimax3_u16x2(o3, u3, v3);
+            e3 = __vimax3_u16x2(e3, u3 * 256u, v3 * 256u);
+        }
+        if (in_x)
+        {
+            if (gy < H)
+                *reinterpret_cast<uint32_t *>(out) = __byte_perm(e0, o0, 0x7351);
+            if (gy + 4 < H)
+                *reinterpret_cast<uint32_t *>(out + 4 * rs) = __byte_perm(e1, o1, 0x7351);
+            if (gy + 16 < H)
+                *reinterpret_cast<uint32_t *>(out + 16 * rs) = __byte_perm(e2, o2, 0x7351);
+            if (gy + 20 < H)
+                *reinterpret_cast<uint32_t *>(out + 20 * rs) = __byte_perm(e3, o3, 0x7351);
+        }
+    }
+}
+
+__device__ __forceinline__ void run_group(const FastArgs &a, const uint32_t *sm, const uint8_t *s_cls, int group, int gw,
+                                          int lane, int tx0, int ty0)
+{
+    switch (group)
+    {
+    case 0: run_bins<0>(a, sm, s_cls, gw, lane, tx0, ty0); break;
+    case 1: run_bins<1>(a, sm, s_cls, gw, lane, tx0, ty0); break;
+    case 2: run_bins<2>(a, sm, s_cls, gw, lane, tx0, ty0); break;
+    default: run_bins<3>(a, sm, s_cls, gw, lane, tx0, ty0); break;
+    }
+}
+
 __global__ void __launch_bounds__(FT_THREADS, 1) se2_fast_kernel(const __grid_constant__ FastArgs a)
 {
     extern __shared__ __align__(16) uint32_t sm[];
     __shared__ uint8_t s_cls[MAX_T_PER_LAUNCH];
     __shared__ int s_any;
     const int tid = threadIdx.x;
+    const int warp = tid >> 5, lane = tid & 31;
+    constexpr int NWARPS = FT_THREADS / 32;
     const uint32_t tile_x = a.tile_x0 + blockIdx.x, tile_y = a.tile_y0 + blockIdx.y;
     if (tid == 0)
         s_any = 0;
@@ -98,83 +171,82 @@ __global__ void __launch_bounds__(FT_THREADS, 1) se2_fast_kernel(const __grid_co
     const int R = a.R, PW = a.PW, rows = a.rows, CW = a.copy_words;
     const int tx0 = static_cast<int>(tile_x) * FT_W, ty0 = static_cast<int>(tile_y) * FT_H;
     const int W = static_cast<int>(a.W), H = static_cast<int>(a.H);
+    const bool wlane = lane < PW;  // one warp per table row, one lane per word (PW <= 30)
 
-    // costmap tile with halo, copy 0: word w of row r holds columns tx0-R+4w .. +3; zeros outside the map
-    for (int i = tid; i < CW; i += FT_THREADS)
+    // costmap tile with halo: word w of row r holds columns tx0-R+4w .. +3, zeros outside the map;
+    // the three byte-shifted copies are funnel shifts of neighbouring words (warp shuffle)
     {
-        const int r = i / PW, w = i - r * PW;
-        const int gy = ty0 - R + r, ax = tx0 - R + 4 * w;
-        uint32_t v = 0;
-        if (gy >= 0 && gy < H)
+        const int ax = tx0 - R + 4 * lane;
+        const int ga = ax & ~3, sh = ax & 3;
+        for (int r = warp; r < rows; r += NWARPS)
         {
-            const int ga = ax & ~3, sh = ax & 3;
-            const uint8_t *rowp = a.cost + static_cast<size_t>(gy) * a.W;
-            const uint32_t lo = (ga >= 0 && ga < W) ? *reinterpret_cast<const uint32_t *>(rowp + ga) : 0u;
-            const uint32_t hi = (sh && ga + 4 >= 0 && ga + 4 < W) ? *reinterpret_cast<const uint32_t *>(rowp + ga + 4) : 0u;
-            v = __funnelshift_r(lo, hi, 8 * sh);
+            const int gy = ty0 - R + r;
+            uint32_t v = 0;
+            if (wlane && gy >= 0 && gy < H)
+            {
+                const uint8_t *rowp = a.cost + static_cast<size_t>(gy) * a.W;
+                const uint32_t lo = (ga >= 0 && ga < W) ? __ldg(reinterpret_cast<const uint32_t *>(rowp + ga)) : 0u;
+                const uint32_t hi = (sh && ga + 4 >= 0 && ga + 4 < W) ? __ldg(reinterpret_cast<const uint32_t *>(rowp + ga + 4)) : 0u;
+                v = __funnelshift_r(lo, hi, 8 * sh);
+            }
+            uint32_t nx = __shfl_down_sync(0xffffffffu, v, 1);
+            if (lane + 1 >= PW)
+                nx = 0;
+            if (wlane)
+            {
+                uint32_t *d = sm + r * PW + lane;
+                d[0] = v;
+                d[CW] = __funnelshift_r(v, nx, 8);
+                d[2 * CW] = __funnelshift_r(v, nx, 16);
+                d[3 * CW] = __funnelshift_r(v, nx, 24);
+            }
         }
-        sm[i] = v;
     }
     __syncthreads();
-    // byte-shifted copies 1..3 of the costmap tile
-    for (int i = tid; i < CW; i += FT_THREADS)
-    {
-        const int w = i % PW;
-        const uint32_t lo = sm[i], hi = (w + 1 < PW) ? sm[i + 1] : 0u;
-        sm[CW + i] = __funnelshift_r(lo, hi, 8);
-        sm[2 * CW + i] = __funnelshift_r(lo, hi, 16);
-        sm[3 * CW + i] = __funnelshift_r(lo, hi, 24);
-    }
-    __syncthreads();
-    // derived brick tables: T_k = max(T_a, T_b shifted by (du, dv)), all four copies
+    // derived brick tables: T_k = max(T_a, T_b shifted by (du, dv)); copy 0 by that formula, copies
+    // 1..3 as funnel shifts of it
     for (int k = 1; k < a.n_tables; ++k)
     {
         const uint32_t *A = sm + a.rec_a[k] * 4 * CW;
-        const uint32_t *B = sm + a.rec_b[k] * 4 * CW;
-        uint32_t *D = sm + k * 4 * CW;
         const int du = a.rec_du[k], dv = a.rec_dv[k];
-        for (int i = tid; i < 4 * CW; i += FT_THREADS)
+        const uint32_t *B0 = sm + a.rec_b[k] * 4 * CW;
+        const uint32_t *B = B0 + (du & 3) * CW;
+        const int w2 = lane + (du >> 2);
+        const bool w2ok = wlane && w2 >= 0 && w2 < PW;
+        uint32_t *D = sm + k * 4 * CW;
+        for (int r = warp; r < rows; r += NWARPS)
         {
-            const int s = i / CW, j = i - s * CW;
-            const int r = j / PW, w = j - r * PW;
-            const int r2 = r + dv, sd = s + du;
-            const int s2 = sd & 3, w2 = w + (sd >> 2);
-            uint32_t vb = 0;
-            if (r2 >= 0 && r2 < rows && w2 >= 0 && w2 < PW)
-                vb = B[s2 * CW + r2 * PW + w2];
-            D[i] = bytemax4(A[i], vb);
+            const int r2 = r + dv;
+            const uint32_t va = wlane ? A[r * PW + lane] : 0u;
+            uint32_t vb = 0u;
+            if (r2 >= 0 && r2 < rows)
+            {
+                if (w2ok)
+                    vb = B[r2 * PW + w2];
+                else if (wlane && w2 == -1 && (du & 3) != 0)  // du < 0: columns -(4-s)..s-1, of which only the last s exist
+                    vb = B0[r2 * PW] << (8 * (4 - (du & 3)));
+            }
+            const uint32_t v = bytemax4(va, vb);
+            uint32_t nx = __shfl_down_sync(0xffffffffu, v, 1);
+            if (lane + 1 >= PW)
+                nx = 0;
+            if (wlane)
+            {
+                uint32_t *d = D + r * PW + lane;
+                d[0] = v;
+                d[CW] = __funnelshift_r(v, nx, 8);
+                d[2 * CW] = __funnelshift_r(v, nx, 16);
+                d[3 * CW] = __funnelshift_r(v, nx, 24);
+            }
         }
         __syncthreads();
     }
 
-    // output phase: one quad (4 cells along x) per thread and bin
-    const int warp = tid >> 5, lane = tid & 31;
-    const int q = lane & 15;
-    const int row = (warp >> 3) * 16 + (warp & 7) + 8 * (lane >> 4);  // half-warps 8 rows apart: bank-conflict free for PW = 2 mod 4
-    const uint32_t sbase = static_cast<uint32_t>(__cvta_generic_to_shared(sm)) + static_cast<uint32_t>((row * PW + q) * 4);
-    const int gx = tx0 + 4 * q, gy = ty0 + row;
-    const bool inside = gx < W && gy < H;
-    const size_t plane = static_cast<size_t>(a.W) * a.H;
-    uint8_t *out = a.vol + plane * a.t_first + static_cast<size_t>(gy) * a.W + gx;
-
-    for (uint32_t t = 0; t < a.n_t; ++t, out += plane)
-    {
-        const uint32_t cls = s_cls[t];
-        if (cls == 255u)
-            continue;
-        const uint32_t off = a.list_off[t][cls], len = a.list_len[t][cls];
-        uint32_t acc_odd = 0, acc_even = 0;
-#pragma unroll 4
-        for (uint32_t i = 0; i < len; i += 2)
-        {
-            const uint32_t w1 = lds32(sbase + a.lists[off + i]);
-            const uint32_t w2 = lds32(sbase + a.lists[off + i + 1]);
-            acc_odd = __vimax3_u16x2(acc_odd, w1, w2);
-            acc_even = __vimax3_u16x2(acc_even, w1 * 256u, w2 * 256u);
-        }
-        if (inside)
-            *reinterpret_cast<uint32_t *>(out) = __byte_perm(acc_even, acc_odd, 0x7351);
-    }
+    // output phase. A group of 4 warps serves one bin: lane -> quad column (lane & 15) and row parity
+    // block (lane >> 4), 4 quads per thread at rows base, base+4, base+16, base+20 with
+    // base = (warp & 3) + 8*(lane >> 4). Half-warps sit 8 rows apart, which is bank-conflict free for
+    // PW = 2 (mod 4). The FT_THREADS/128 groups take bins t = group, group + NGROUPS, ...
+    run_group(a, sm, s_cls, warp >> 2, warp & 3, lane, tx0, ty0);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -653,7 +725,7 @@ pp_status pp_se2_launch_fast(pp_handle h, uint32_t x0, uint32_t y0, uint32_t x1,
         {
             uint32_t need = 0;
             for (int c = 0; c < 4; ++c)
-                need += pl->list_len[(t + n) * 4 + c];
+                need += (pl->list_len[(t + n) * 4 + c] + 3u) & ~3u;
             if (words + need > MAX_LIST_WORDS)
                 break;
             for (int c = 0; c < 4; ++c)
@@ -662,7 +734,7 @@ pp_status pp_se2_launch_fast(pp_handle h, uint32_t x0, uint32_t y0, uint32_t x1,
                 args.list_off[n][c] = static_cast<uint16_t>(words);
                 args.list_len[n][c] = static_cast<uint16_t>(len);
                 std::memcpy(args.lists + words, pl->lists.data() + pl->list_off[(t + n) * 4 + c], len * sizeof(uint32_t));
-                words += len;
+                words += (len + 3u) & ~3u;  // keep every list 16-byte aligned
             }
             ++n;
         }
