@@ -52,11 +52,11 @@ struct FastArgs
     uint32_t t_first, n_t;
     uint8_t rec_a[MAX_TABLES], rec_b[MAX_TABLES];
     int8_t rec_du[MAX_TABLES], rec_dv[MAX_TABLES];
+    uint8_t lvl_end[8];  // tables [lvl_end[l-1], lvl_end[l]) form dependency level l (table 0 is the costmap)
     uint16_t list_off[MAX_T_PER_LAUNCH][4];
     uint16_t list_len[MAX_T_PER_LAUNCH][4];
     alignas(16) uint32_t lists[MAX_LIST_WORDS];  // byte offsets into shared memory, relative to the thread's base
 };
-static_assert(FT_THREADS == 512, "run_group dispatches 4 groups of 4 warps");
 static_assert(sizeof(FastArgs) < 32764, "kernel parameter block too large");
 
 __device__ __forceinline__ uint32_t bytemax4(uint32_t a, uint32_t b)
@@ -73,180 +73,220 @@ __device__ __forceinline__ uint32_t lds32(uint32_t addr)
     return v;
 }
 
+constexpr int QPT = 8;                                     // quads (4 cells along x) per thread and bin
+constexpr int WARPS_PER_BIN = FT_W / 4 * FT_H / QPT / 32;  // 2
+constexpr int NGROUPS = FT_THREADS / 32 / WARPS_PER_BIN;   // 8 bins in flight per CTA
 
-constexpr int NGROUPS = FT_THREADS / 128;
+// row of quad j of a thread, relative to the thread's first row
+__host__ __device__ constexpr int quad_row(int j) { return (j & 3) * 2 + (j >> 2) * 16; }
 
-template <int T_START>
-__device__ __forceinline__ void run_bins(const FastArgs &a, const uint32_t *sm, const uint8_t *s_cls, int gw, int lane,
-                                         int tx0, int ty0)
+template <int PW>
+__device__ __forceinline__ void load_pair(const uint8_t *smb, uint32_t d1, uint32_t d2, uint32_t (&u)[QPT], uint32_t (&v)[QPT])
 {
-    // T_START is a literal in each instantiation, so the bin index and with it every list offset
-    // stays warp-uniform: descriptors travel through the uniform datapath and LDS takes [R + UR].
-    const int PW = a.PW;
+    // the row pitch is a template parameter, so the QPT row offsets are immediates: LDS [R + imm]
+    const uint32_t *p1 = reinterpret_cast<const uint32_t *>(smb + d1);
+    const uint32_t *p2 = reinterpret_cast<const uint32_t *>(smb + d2);
+#pragma unroll
+    for (int j = 0; j < QPT; ++j)
+    {
+        u[j] = p1[quad_row(j) * PW];
+        v[j] = p2[quad_row(j) * PW];
+    }
+}
+
+__device__ __forceinline__ void accumulate(uint32_t (&odd)[QPT], uint32_t (&even)[QPT], const uint32_t (&u)[QPT], const uint32_t (&v)[QPT])
+{
+#pragma unroll
+    for (int j = 0; j < QPT; ++j)
+    {
+        odd[j] = __vimax3_u16x2(odd[j], u[j], v[j]);
+        even[j] = __vimax3_u16x2(even[j], u[j] * 256u, v[j] * 256u);
+    }
+}
+
+// Output phase for one warp. WARPS_PER_BIN warps serve one bin; group g takes bins g, g+NGROUPS, ...
+// Thread -> quad column (lane & 15) and rows gw + 8*(lane >> 4) + quad_row(j). Half-warps sit 8 rows
+// apart, which is bank-conflict free for PW = 2 (mod 4). The loads of the next sample pair are
+// issued before the max operations of the current one (software pipelining by hand).
+template <int PW>
+__device__ __forceinline__ void run_bins(const FastArgs &a, const uint32_t *sm, const uint8_t *s_cls, int group, int gw,
+                                         int lane, int tx0, int ty0)
+{
     const int q = lane & 15;
     const int row0 = gw + 8 * (lane >> 4);
-    const uint32_t b0 = static_cast<uint32_t>(__cvta_generic_to_shared(sm)) + static_cast<uint32_t>((row0 * PW + q) * 4);
-    const uint32_t b1 = b0 + 4 * PW * 4, b2 = b0 + 16 * PW * 4, b3 = b0 + 20 * PW * 4;
+    const uint8_t *smb = reinterpret_cast<const uint8_t *>(sm + row0 * PW + q);
     const int W = static_cast<int>(a.W), H = static_cast<int>(a.H);
     const int gx = tx0 + 4 * q, gy = ty0 + row0;
     const bool in_x = gx < W;
     const size_t plane = static_cast<size_t>(a.W) * a.H;
     const size_t rs = a.W;
-    uint8_t *out = a.vol + plane * (a.t_first + T_START) + static_cast<size_t>(gy) * a.W + gx;
-    for (uint32_t t = T_START; t < a.n_t; t += NGROUPS, out += NGROUPS * plane)
+    uint8_t *out = a.vol + plane * (a.t_first + group) + static_cast<size_t>(gy) * a.W + gx;
+    for (uint32_t t = group; t < a.n_t; t += NGROUPS, out += NGROUPS * plane)
     {
         const uint32_t cls = s_cls[t];
         if (cls == 255u)
             continue;
-        const uint32_t off = a.list_off[t][cls], len = a.list_len[t][cls];  // len is even
-        uint32_t o0 = 0, e0 = 0, o1 = 0, e1 = 0, o2 = 0, e2 = 0, o3 = 0, e3 = 0;
-#pragma unroll 4
-        for (uint32_t i = 0; i < len; i += 2)
+        const uint32_t *list = a.lists + a.list_off[t][cls];
+        const uint32_t len = a.list_len[t][cls];  // even, >= 2
+        uint32_t odd[QPT], even[QPT];
+#pragma unroll
+        for (int j = 0; j < QPT; ++j)
+            odd[j] = even[j] = 0;
+        uint32_t ua[QPT], va[QPT], ub[QPT], vb[QPT];
+        load_pair<PW>(smb, list[0], list[1], ua, va);
+        uint32_t i = 2;
+#pragma unroll 1
+        for (; i + 2 < len; i += 4)
         {
-            const uint32_t d1 = a.lists[off + i], d2 = a.lists[off + i + 1];
-            const uint32_t u0 = lds32(b0 + d1), v0 = lds32(b0 + d2);
-            const uint32_t u1 = lds32(b1 + d1), v1 = lds32(b1 + d2);
-            const uint32_t u2 = lds32(b2 + d1), v2 = lds32(b2 + d2);
-            const uint32_t u3 = lds32(b3 + d1), v3 = lds32(b3 + d2);
-            o0 = __vimax3_u16x2(o0, u0, v0);
-            e0 = __vimax3_u16x2(e0, u0 * 256u, v0 * 256u);
-            o1 = __vimax3_u16x2(o1, u1, v1);
-            e1 = __vimax3_u16x2(e1, u1 * 256u, v1 * 256u);
-            o2 = __vimax3_u16x2(o2, u2, v2);
-            e2 = __vimax3_u16x2(e2, u2 * 256u, v2 * 256u);
-            o3 = __vimax3_u16x2(o3, u3, v3);
-            e3 = __vimax3_u16x2(e3, u3 * 256u, v3 * 256u);
+            load_pair<PW>(smb, list[i], list[i + 1], ub, vb);
+            accumulate(odd, even, ua, va);
+            load_pair<PW>(smb, list[i + 2], list[i + 3], ua, va);
+            accumulate(odd, even, ub, vb);
+        }
+        if (i < len)
+        {
+            load_pair<PW>(smb, list[i], list[i + 1], ub, vb);
+            accumulate(odd, even, ua, va);
+            accumulate(odd, even, ub, vb);
+        }
+        else
+        {
+            accumulate(odd, even, ua, va);
         }
         if (in_x)
         {
-            if (gy < H)
-                *reinterpret_cast<uint32_t *>(out) = __byte_perm(e0, o0, 0x7351);
-            if (gy + 4 < H)
-                *reinterpret_cast<uint32_t *>(out + 4 * rs) = __byte_perm(e1, o1, 0x7351);
-            if (gy + 16 < H)
-                *reinterpret_cast<uint32_t *>(out + 16 * rs) = __byte_perm(e2, o2, 0x7351);
-            if (gy + 20 < H)
-                *reinterpret_cast<uint32_t *>(out + 20 * rs) = __byte_perm(e3, o3, 0x7351);
+#pragma unroll
+            for (int j = 0; j < QPT; ++j)
+                if (gy + quad_row(j) < H)
+                    *reinterpret_cast<uint32_t *>(out + quad_row(j) * rs) = __byte_perm(even[j], odd[j], 0x7351);
         }
     }
 }
 
-__device__ __forceinline__ void run_group(const FastArgs &a, const uint32_t *sm, const uint8_t *s_cls, int group, int gw,
-                                          int lane, int tx0, int ty0)
-{
-    switch (group)
-    {
-    case 0: run_bins<0>(a, sm, s_cls, gw, lane, tx0, ty0); break;
-    case 1: run_bins<1>(a, sm, s_cls, gw, lane, tx0, ty0); break;
-    case 2: run_bins<2>(a, sm, s_cls, gw, lane, tx0, ty0); break;
-    default: run_bins<3>(a, sm, s_cls, gw, lane, tx0, ty0); break;
-    }
-}
-
+template <int PW>
 __global__ void __launch_bounds__(FT_THREADS, 1) se2_fast_kernel(const __grid_constant__ FastArgs a)
 {
     extern __shared__ __align__(16) uint32_t sm[];
     __shared__ uint8_t s_cls[MAX_T_PER_LAUNCH];
-    __shared__ int s_any;
     const int tid = threadIdx.x;
     const int warp = tid >> 5, lane = tid & 31;
     constexpr int NWARPS = FT_THREADS / 32;
+    constexpr int ROW_ITERS = (FT_H + 2 * MAX_R + NWARPS - 1) / NWARPS;
     const uint32_t tile_x = a.tile_x0 + blockIdx.x, tile_y = a.tile_y0 + blockIdx.y;
-    if (tid == 0)
-        s_any = 0;
-    __syncthreads();
-    for (uint32_t t = tid; t < a.n_t; t += FT_THREADS)
-    {
-        const uint32_t cx = a.xclass[static_cast<size_t>(a.t_first + t) * a.tiles_x + tile_x];
-        const uint32_t cy = a.yclass[static_cast<size_t>(a.t_first + t) * a.tiles_y + tile_y];
-        const uint32_t cls = (cx > 1 || cy > 1) ? 255u : cx * 2 + cy;
-        s_cls[t] = static_cast<uint8_t>(cls);
-        if (cls != 255u)
-            s_any = 1;
-    }
-    __syncthreads();
-    if (!s_any)
-        return;  // every bin of this tile belongs to the generic work list
-
-    const int R = a.R, PW = a.PW, rows = a.rows, CW = a.copy_words;
+    const int R = a.R, rows = a.rows, CW = a.copy_words;
     const int tx0 = static_cast<int>(tile_x) * FT_W, ty0 = static_cast<int>(tile_y) * FT_H;
     const int W = static_cast<int>(a.W), H = static_cast<int>(a.H);
-    const bool wlane = lane < PW;  // one warp per table row, one lane per word (PW <= 30)
 
-    // costmap tile with halo: word w of row r holds columns tx0-R+4w .. +3, zeros outside the map;
-    // the three byte-shifted copies are funnel shifts of neighbouring words (warp shuffle)
+    // bin classes of this tile (one bin per thread), requested before anything else
+    uint32_t my_cx = 255u, my_cy = 255u;
+    if (static_cast<uint32_t>(tid) < a.n_t)
     {
-        const int ax = tx0 - R + 4 * lane;
-        const int ga = ax & ~3, sh = ax & 3;
-        for (int r = warp; r < rows; r += NWARPS)
+        my_cx = __ldg(a.xclass + static_cast<size_t>(a.t_first + tid) * a.tiles_x + tile_x);
+        my_cy = __ldg(a.yclass + static_cast<size_t>(a.t_first + tid) * a.tiles_y + tile_y);
+    }
+    // Costmap tile with halo, one warp per row and one lane per word; every global load of the
+    // tile is issued before the first use. Table word w of row r holds columns X0+4w .. X0+4w+3 with
+    // X0 = tx0 - R - 4: one margin word on the left, so that bricks reaching towards -x never index
+    // before the row. Map rows are 4-byte aligned (W % 4 == 0); a word that straddles two aligned
+    // words is funnelled from both; zeros outside the map.
+    const bool wlane = lane < PW;
+    uint32_t lo[ROW_ITERS], hi[ROW_ITERS];
+    const int ax = tx0 - R - 4 + 4 * lane;
+    const int ga = ax & ~3, sh = ax & 3;
+    const bool lo_ok = wlane && ga >= 0 && ga < W, hi_ok = wlane && sh != 0 && ga + 4 >= 0 && ga + 4 < W;
+#pragma unroll
+    for (int j = 0; j < ROW_ITERS; ++j)
+    {
+        const int r = warp + j * NWARPS;
+        const int gy = ty0 - R + r;
+        const bool row_ok = r < rows && gy >= 0 && gy < H;
+        const uint8_t *rowp = a.cost + static_cast<size_t>(row_ok ? gy : 0) * a.W;
+        lo[j] = (row_ok && lo_ok) ? __ldg(reinterpret_cast<const uint32_t *>(rowp + ga)) : 0u;
+        hi[j] = (row_ok && hi_ok) ? __ldg(reinterpret_cast<const uint32_t *>(rowp + ga + 4)) : 0u;
+    }
+    static_assert(MAX_T_PER_LAUNCH <= FT_THREADS, "one bin class per thread");
+    const uint32_t my_cls = (my_cx > 1 || my_cy > 1) ? 255u : my_cx * 2 + my_cy;
+    if (static_cast<uint32_t>(tid) < a.n_t)
+        s_cls[tid] = static_cast<uint8_t>(my_cls);
+#pragma unroll
+    for (int j = 0; j < ROW_ITERS; ++j)
+    {
+        const int r = warp + j * NWARPS;
+        if (wlane && r < rows)
+            sm[r * PW + lane] = __funnelshift_r(lo[j], hi[j], 8 * sh);
+    }
+    const int any_fast = __syncthreads_or(my_cls != 255u);
+    if (!any_fast)
+        return;  // every bin of this tile belongs to the generic work list
+
+    // Word slots of this thread in a table copy (linear index tid + j*FT_THREADS), with their row
+    // and column worked out once for all tables.
+    constexpr int SLOTS = ((FT_H + 2 * MAX_R) * 30 + FT_THREADS - 1) / FT_THREADS;  // rows * PW <= 62 * 30
+    int slot_r[SLOTS], slot_w[SLOTS];
+#pragma unroll
+    for (int j = 0; j < SLOTS; ++j)
+    {
+        const int i = tid + j * FT_THREADS;
+        slot_r[j] = i < CW ? i / PW : -1000;
+        slot_w[j] = i - (i / PW) * PW;
+    }
+    // byte-shifted copies 1..3 of a table from its copy 0: word i of copy s = bytes s..s+3 of the
+    // word pair (i, i+1) (zero past the end of the row)
+    auto make_copies = [&](uint32_t *T) {
+#pragma unroll
+        for (int j = 0; j < SLOTS; ++j)
         {
-            const int gy = ty0 - R + r;
-            uint32_t v = 0;
-            if (wlane && gy >= 0 && gy < H)
+            const int i = tid + j * FT_THREADS;
+            if (slot_r[j] >= 0)
             {
-                const uint8_t *rowp = a.cost + static_cast<size_t>(gy) * a.W;
-                const uint32_t lo = (ga >= 0 && ga < W) ? __ldg(reinterpret_cast<const uint32_t *>(rowp + ga)) : 0u;
-                const uint32_t hi = (sh && ga + 4 >= 0 && ga + 4 < W) ? __ldg(reinterpret_cast<const uint32_t *>(rowp + ga + 4)) : 0u;
-                v = __funnelshift_r(lo, hi, 8 * sh);
-            }
-            uint32_t nx = __shfl_down_sync(0xffffffffu, v, 1);
-            if (lane + 1 >= PW)
-                nx = 0;
-            if (wlane)
-            {
-                uint32_t *d = sm + r * PW + lane;
-                d[0] = v;
-                d[CW] = __funnelshift_r(v, nx, 8);
-                d[2 * CW] = __funnelshift_r(v, nx, 16);
-                d[3 * CW] = __funnelshift_r(v, nx, 24);
+                const uint32_t v = T[i];
+                const uint32_t nx = (slot_w[j] + 1 < PW) ? T[i + 1] : 0u;
+                T[CW + i] = __funnelshift_r(v, nx, 8);
+                T[2 * CW + i] = __funnelshift_r(v, nx, 16);
+                T[3 * CW + i] = __funnelshift_r(v, nx, 24);
             }
         }
-    }
+    };
+    make_copies(sm);
     __syncthreads();
-    // derived brick tables: T_k = max(T_a, T_b shifted by (du, dv)); copy 0 by that formula, copies
-    // 1..3 as funnel shifts of it
-    for (int k = 1; k < a.n_tables; ++k)
+
+    // derived brick tables, level by level (tables of one level depend only on earlier levels):
+    // T_k = max(T_a, T_b shifted by (du, dv)). Pass 1 writes copy 0 of every table of the level,
+    // pass 2 its shifted copies.
+    int k0 = 1;
+    for (int lvl = 0; lvl < 8; ++lvl)
     {
-        const uint32_t *A = sm + a.rec_a[k] * 4 * CW;
-        const int du = a.rec_du[k], dv = a.rec_dv[k];
-        const uint32_t *B0 = sm + a.rec_b[k] * 4 * CW;
-        const uint32_t *B = B0 + (du & 3) * CW;
-        const int w2 = lane + (du >> 2);
-        const bool w2ok = wlane && w2 >= 0 && w2 < PW;
-        uint32_t *D = sm + k * 4 * CW;
-        for (int r = warp; r < rows; r += NWARPS)
+        const int k_end = a.lvl_end[lvl];
+        for (int k = k0; k < k_end; ++k)
         {
-            const int r2 = r + dv;
-            const uint32_t va = wlane ? A[r * PW + lane] : 0u;
-            uint32_t vb = 0u;
-            if (r2 >= 0 && r2 < rows)
+            const int du = a.rec_du[k], dv = a.rec_dv[k];
+            const int dw = du >> 2;  // floor
+            const uint32_t *A = sm + a.rec_a[k] * 4 * CW;
+            const uint32_t *B = sm + a.rec_b[k] * 4 * CW + (du & 3) * CW + dv * PW + dw;
+            uint32_t *D = sm + k * 4 * CW;
+#pragma unroll
+            for (int j = 0; j < SLOTS; ++j)
             {
-                if (w2ok)
-                    vb = B[r2 * PW + w2];
-                else if (wlane && w2 == -1 && (du & 3) != 0)  // du < 0: columns -(4-s)..s-1, of which only the last s exist
-                    vb = B0[r2 * PW] << (8 * (4 - (du & 3)));
-            }
-            const uint32_t v = bytemax4(va, vb);
-            uint32_t nx = __shfl_down_sync(0xffffffffu, v, 1);
-            if (lane + 1 >= PW)
-                nx = 0;
-            if (wlane)
-            {
-                uint32_t *d = D + r * PW + lane;
-                d[0] = v;
-                d[CW] = __funnelshift_r(v, nx, 8);
-                d[2 * CW] = __funnelshift_r(v, nx, 16);
-                d[3 * CW] = __funnelshift_r(v, nx, 24);
+                const int i = tid + j * FT_THREADS;
+                if (slot_r[j] >= 0)
+                {
+                    const int r2 = slot_r[j] + dv, w2 = slot_w[j] + dw;
+                    const uint32_t vb = (r2 >= 0 && r2 < rows && w2 >= 0 && w2 < PW) ? B[i] : 0u;
+                    D[i] = bytemax4(A[i], vb);
+                }
             }
         }
         __syncthreads();
+        for (int k = k0; k < k_end; ++k)
+            make_copies(sm + k * 4 * CW);
+        __syncthreads();
+        k0 = k_end;
+        if (k0 >= a.n_tables)
+            break;
     }
 
-    // output phase. A group of 4 warps serves one bin: lane -> quad column (lane & 15) and row parity
-    // block (lane >> 4), 4 quads per thread at rows base, base+4, base+16, base+20 with
-    // base = (warp & 3) + 8*(lane >> 4). Half-warps sit 8 rows apart, which is bank-conflict free for
-    // PW = 2 (mod 4). The FT_THREADS/128 groups take bins t = group, group + NGROUPS, ...
-    run_group(a, sm, s_cls, warp >> 2, warp & 3, lane, tx0, ty0);
+    // output phase: WARPS_PER_BIN warps per bin, NGROUPS bins in flight
+    run_bins<PW>(a, sm, s_cls, warp / WARPS_PER_BIN, warp % WARPS_PER_BIN, lane, tx0, ty0);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -262,9 +302,9 @@ using Library = std::vector<Recipe>;
 const Library LIB_STAIRS = {{0, 0, 0, 0}, {0, 0, 1, 0}, {0, 0, 0, 1}, {0, 0, 1, 1}, {0, 0, 1, -1}, {1, 1, 2, 0},
                             {2, 2, 0, 2}, {1, 1, 2, 1}, {1, 1, 2, -1}, {2, 2, 1, 2}, {2, 2, -1, 2}, {5, 5, 4, 0}};
 const Library LIB_RUNS3 = {{0, 0, 0, 0}, {0, 0, 1, 0}, {0, 0, 0, 1}, {0, 0, 1, 1}, {0, 0, 1, -1}, {1, 0, 2, 0},
-                           {2, 0, 0, 2}, {3, 0, 2, 2}, {4, 0, 2, -2}, {5, 5, 3, 0}, {6, 6, 0, 3}, {3, 3, 2, 2}};
+                           {2, 0, 0, 2}, {3, 0, 2, 2}, {4, 0, 2, -2}, {3, 3, 2, 2}, {5, 5, 3, 0}, {6, 6, 0, 3}};
 const Library LIB_BLOCKS = {{0, 0, 0, 0}, {0, 0, 1, 0}, {0, 0, 0, 1}, {1, 1, 0, 1}, {1, 1, 2, 0}, {2, 2, 0, 2},
-                            {3, 3, 2, 0}, {6, 6, 0, 2}, {4, 4, 4, 0}, {5, 5, 0, 4}, {7, 7, 4, 0}, {10, 10, 0, 4}};
+                            {3, 3, 2, 0}, {4, 4, 4, 0}, {5, 5, 0, 4}, {6, 6, 0, 2}, {9, 9, 4, 0}, {10, 10, 0, 4}};
 const Library LIB_RUNS = {{0, 0, 0, 0}, {0, 0, 1, 0}, {0, 0, 0, 1}, {0, 0, 1, 1}, {0, 0, 1, -1}, {1, 1, 2, 0},
                           {2, 2, 0, 2}, {3, 3, 2, 2}, {4, 4, 2, -2}, {5, 5, 4, 0}, {6, 6, 0, 4}};
 
@@ -554,9 +594,8 @@ pp_status build_plan(pp_handle h)
     // 2. geometry
     pl->R = R;
     pl->rows = FT_H + 2 * R;
-    int pw = (FT_W + 2 * R + 3) / 4;
-    while (pw % 4 != 2)
-        ++pw;
+    int pw = (4 + FT_W + 2 * R + 3) / 4;  // one margin word on the left
+    pw = pw <= 22 ? 22 : 26;  // the two instantiated pitches (both 2 mod 4: conflict-free half-warps)
     pl->PW = pw;
     pl->copy_words = pl->rows * pl->PW;
     const size_t table_bytes = static_cast<size_t>(4) * pl->copy_words * 4;
@@ -612,7 +651,7 @@ pp_status build_plan(pp_handle h)
                     std::vector<uint32_t> words;
                     for (const Placement &p : cover_set(S, bricks, R))
                     {
-                        const int ax = R + p.ox, ay = R + p.oy;  // >= 0
+                        const int ax = R + 4 + p.ox, ay = R + p.oy;  // >= 0; +4: the margin word
                         const uint32_t word = static_cast<uint32_t>((p.brick * 4 + (ax & 3)) * pl->copy_words + ay * pl->PW + (ax >> 2));
                         words.push_back(word * 4);
                     }
@@ -667,7 +706,10 @@ pp_status build_plan(pp_handle h)
         PP_CUDA(h, cudaMemcpyAsync(pl->d_work, pl->h_work.data(), pl->h_work.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, h->stream));
     }
     PP_CUDA(h, cudaStreamSynchronize(h->stream));
-    PP_CUDA(h, cudaFuncSetAttribute(se2_fast_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(pl->smem_bytes)));
+    if (pl->PW == 22)
+        PP_CUDA(h, cudaFuncSetAttribute(se2_fast_kernel<22>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(pl->smem_bytes)));
+    else
+        PP_CUDA(h, cudaFuncSetAttribute(se2_fast_kernel<26>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(pl->smem_bytes)));
     pl->usable = true;
     return PP_OK;
 }
@@ -704,6 +746,20 @@ pp_status pp_se2_launch_fast(pp_handle h, uint32_t x0, uint32_t y0, uint32_t x1,
     args.rows = pl->rows;
     args.copy_words = pl->copy_words;
     args.n_tables = pl->n_tables;
+    {
+        // dependency levels; the libraries list their tables in level order
+        int level[MAX_TABLES] = {0};
+        for (int l = 0; l < 8; ++l)
+            args.lvl_end[l] = static_cast<uint8_t>(pl->n_tables);
+        for (int k = 1; k < pl->n_tables; ++k)
+        {
+            level[k] = 1 + std::max(level[pl->lib[k].a], level[pl->lib[k].b]);
+            PP_REQUIRE(h, level[k] >= level[k - 1] && level[k] <= 8, PP_ERR_STATE, "brick library is not in level order");
+        }
+        for (int k = 1; k < pl->n_tables; ++k)
+            for (int l = 0; l < level[k] - 1; ++l)
+                args.lvl_end[l] = std::min<uint8_t>(args.lvl_end[l], static_cast<uint8_t>(k));
+    }
     for (int k = 0; k < pl->n_tables; ++k)
     {
         args.rec_a[k] = static_cast<uint8_t>(pl->lib[k].a);
@@ -741,7 +797,10 @@ pp_status pp_se2_launch_fast(pp_handle h, uint32_t x0, uint32_t y0, uint32_t x1,
         PP_REQUIRE(h, n > 0, PP_ERR_RANGE, "a single heading bin needs more than %d sample words", MAX_LIST_WORDS);
         args.t_first = t;
         args.n_t = n;
-        se2_fast_kernel<<<grid, FT_THREADS, pl->smem_bytes, h->stream>>>(args);
+        if (pl->PW == 22)
+            se2_fast_kernel<22><<<grid, FT_THREADS, pl->smem_bytes, h->stream>>>(args);
+        else
+            se2_fast_kernel<26><<<grid, FT_THREADS, pl->smem_bytes, h->stream>>>(args);
         h->launches++;
         PP_CUDA(h, cudaGetLastError());
         // bookkeeping + the exact path for the (tile, bin) pairs outside uniform ranges
