@@ -34,7 +34,7 @@
 
 namespace
 {
-constexpr int FT_W = 64, FT_H = 32, FT_THREADS = 512;
+constexpr int FT_W = 64, FT_H = 32, FT_THREADS = 768;
 constexpr int MAX_TABLES = 12;
 constexpr int MAX_T_PER_LAUNCH = 160;
 constexpr int MAX_LIST_WORDS = 6400;
@@ -315,14 +315,6 @@ struct Placement
     int brick, ox, oy;
 };
 
-struct Bits
-{
-    uint64_t w[16];
-    void clear() { std::memset(w, 0, sizeof(w)); }
-    void set(int i) { w[i >> 6] |= 1ull << (i & 63); }
-    bool get(int i) const { return (w[i >> 6] >> (i & 63)) & 1ull; }
-};
-
 std::vector<Offsets> brick_points(const Library &lib, int n)
 {
     std::vector<Offsets> pts(n);
@@ -339,94 +331,184 @@ std::vector<Offsets> brick_points(const Library &lib, int n)
     return pts;
 }
 
-// Greedy exact cover of S by brick placements that lie entirely inside S, then reverse deletion
-// of placements made redundant by later ones.
-std::vector<Placement> cover_set(const Offsets &S, const std::vector<Offsets> &bricks, int R)
+// Minimum exact cover of S by brick placements that lie entirely inside S (overlaps allowed).
+// Cells of S are numbered by rank, so a placement is a bit mask of at most MASK_WORDS*64 bits.
+// Greedy gives the first solution; a depth-first branch and bound (branch on the uncovered cell
+// with the fewest covering placements, bound by ceil(uncovered / largest brick)) then improves it
+// within a node budget. Deterministic.
+constexpr int MASK_WORDS = 3;
+struct Mask
 {
-    const int side = 2 * R + 1;
-    auto idx = [&](int x, int y) { return (y + R) * side + (x + R); };
-    Bits in;
-    in.clear();
-    for (auto &p : S)
-        in.set(idx(p.first, p.second));
+    uint64_t w[MASK_WORDS];
+    bool empty() const { return (w[0] | w[1] | w[2]) == 0; }
+    int count() const { return __builtin_popcountll(w[0]) + __builtin_popcountll(w[1]) + __builtin_popcountll(w[2]); }
+    Mask andnot(const Mask &o) const { return {{w[0] & ~o.w[0], w[1] & ~o.w[1], w[2] & ~o.w[2]}}; }
+    int overlap(const Mask &o) const
+    {
+        return __builtin_popcountll(w[0] & o.w[0]) + __builtin_popcountll(w[1] & o.w[1]) + __builtin_popcountll(w[2] & o.w[2]);
+    }
+    bool subset_of(const Mask &o) const { return ((w[0] & ~o.w[0]) | (w[1] & ~o.w[1]) | (w[2] & ~o.w[2])) == 0; }
+    bool operator==(const Mask &o) const { return w[0] == o.w[0] && w[1] == o.w[1] && w[2] == o.w[2]; }
+    int first() const
+    {
+        for (int i = 0; i < MASK_WORDS; ++i)
+            if (w[i])
+                return i * 64 + __builtin_ctzll(w[i]);
+        return -1;
+    }
+    bool test(int b) const { return (w[b >> 6] >> (b & 63)) & 1ull; }
+};
+
+struct CoverSearch
+{
     struct Cand
     {
         Placement pl;
-        Bits mask;
+        Mask mask;
         int npts;
     };
     std::vector<Cand> cands;
+    std::vector<std::vector<int>> covering;  // per cell: candidates that contain it
+    int max_pts = 1;
+    std::vector<int> best, stack;
+    long nodes = 0, node_budget = 0;
+
+    void dfs(const Mask &unc)
+    {
+        if (unc.empty())
+        {
+            if (stack.size() < best.size())
+                best = stack;
+            return;
+        }
+        if (++nodes > node_budget)
+            return;
+        const int left = unc.count();
+        if (static_cast<int>(stack.size()) + (left + max_pts - 1) / max_pts >= static_cast<int>(best.size()))
+            return;
+        // the uncovered cell with the fewest useful placements
+        int cell = -1, cell_n = 1 << 30;
+        for (int i = 0; i < MASK_WORDS; ++i)
+        {
+            uint64_t m = unc.w[i];
+            while (m)
+            {
+                const int b = i * 64 + __builtin_ctzll(m);
+                m &= m - 1;
+                const int n = static_cast<int>(covering[b].size());
+                if (n < cell_n)
+                {
+                    cell_n = n;
+                    cell = b;
+                }
+            }
+        }
+        // its placements by decreasing gain
+        std::vector<std::pair<int, int>> order;
+        for (int c : covering[cell])
+            order.emplace_back(-cands[c].mask.overlap(unc), c);
+        std::sort(order.begin(), order.end());
+        for (auto &o : order)
+        {
+            stack.push_back(o.second);
+            dfs(unc.andnot(cands[o.second].mask));
+            stack.pop_back();
+            if (nodes > node_budget)
+                return;
+        }
+    }
+};
+
+std::vector<Placement> cover_set(const Offsets &S, const std::vector<Offsets> &bricks, int R, long node_budget)
+{
+    const int n = static_cast<int>(S.size());
+    const int side = 2 * R + 1;
+    std::vector<int> rank(static_cast<size_t>(side) * side, -1);
+    auto idx = [&](int x, int y) { return (y + R) * side + (x + R); };
+    for (int i = 0; i < n; ++i)
+        rank[idx(S[i].first, S[i].second)] = i;
+    CoverSearch cs;
+    if (n > MASK_WORDS * 64)
+    {
+        // too many cells for the mask: one point per sample (still exact, just not compressed)
+        std::vector<Placement> out;
+        for (auto &p : S)
+            out.push_back({0, p.first, p.second});
+        return out;
+    }
     // every valid placement has its first (smallest) brick point on a cell of S, so anchoring that
     // point on each cell of S enumerates each placement exactly once
     for (int k = static_cast<int>(bricks.size()) - 1; k >= 0; --k)
         for (auto &anchor : S)
         {
             const int ox = anchor.first - bricks[k][0].first, oy = anchor.second - bricks[k][0].second;
+            CoverSearch::Cand c;
+            c.mask = {{0, 0, 0}};
             bool ok = true;
-            Cand c;
-            c.mask.clear();
             for (auto &q : bricks[k])
             {
                 const int x = ox + q.first, y = oy + q.second;
-                if (x < -R || x > R || y < -R || y > R || !in.get(idx(x, y)))
+                if (x < -R || x > R || y < -R || y > R || rank[idx(x, y)] < 0)
                 {
                     ok = false;
                     break;
                 }
-                c.mask.set(idx(x, y));
+                const int b = rank[idx(x, y)];
+                c.mask.w[b >> 6] |= 1ull << (b & 63);
             }
             if (!ok)
                 continue;
             c.pl = {k, ox, oy};
             c.npts = static_cast<int>(bricks[k].size());
-            cands.push_back(c);
+            cs.cands.push_back(c);
         }
-    Bits unc = in;
-    std::vector<int> chosen;
-    size_t remaining = S.size();
-    while (remaining > 0)
+    // drop placements whose cells are a subset of another placement's
     {
-        int best = -1, best_gain = 0;
-        for (size_t c = 0; c < cands.size(); ++c)
+        std::vector<CoverSearch::Cand> kept;
+        for (size_t i = 0; i < cs.cands.size(); ++i)
         {
-            int g = 0;
-            for (int i = 0; i < 16; ++i)
-                g += __builtin_popcountll(cands[c].mask.w[i] & unc.w[i]);
-            if (g > best_gain || (g == best_gain && g > 0 && best >= 0 && cands[c].npts < cands[best].npts))
+            bool dominated = false;
+            for (size_t j = 0; j < cs.cands.size() && !dominated; ++j)
+                if (i != j && cs.cands[i].mask.subset_of(cs.cands[j].mask) && (!(cs.cands[i].mask == cs.cands[j].mask) || j < i))
+                    dominated = true;
+            if (!dominated)
+                kept.push_back(cs.cands[i]);
+        }
+        cs.cands.swap(kept);
+    }
+    cs.covering.assign(n, {});
+    for (size_t c = 0; c < cs.cands.size(); ++c)
+    {
+        cs.max_pts = std::max(cs.max_pts, cs.cands[c].mask.count());
+        for (int b = 0; b < n; ++b)
+            if (cs.cands[c].mask.test(b))
+                cs.covering[b].push_back(static_cast<int>(c));
+    }
+    // greedy start
+    Mask unc = {{0, 0, 0}};
+    for (int b = 0; b < n; ++b)
+        unc.w[b >> 6] |= 1ull << (b & 63);
+    const Mask all = unc;
+    while (!unc.empty())
+    {
+        int bestc = -1, gain = 0;
+        for (size_t c = 0; c < cs.cands.size(); ++c)
+        {
+            const int g = cs.cands[c].mask.overlap(unc);
+            if (g > gain)
             {
-                best = static_cast<int>(c);
-                best_gain = g;
+                gain = g;
+                bestc = static_cast<int>(c);
             }
         }
-        chosen.push_back(best);
-        for (int i = 0; i < 16; ++i)
-            unc.w[i] &= ~cands[best].mask.w[i];
-        remaining -= best_gain;
+        cs.best.push_back(bestc);
+        unc = unc.andnot(cs.cands[bestc].mask);
     }
-    // reverse deletion
-    std::vector<char> keep(chosen.size(), 1);
-    for (size_t c = 0; c < chosen.size(); ++c)
-    {
-        Bits others;
-        others.clear();
-        for (size_t d = 0; d < chosen.size(); ++d)
-            if (d != c && keep[d])
-                for (int i = 0; i < 16; ++i)
-                    others.w[i] |= cands[chosen[d]].mask.w[i];
-        bool redundant = true;
-        for (int i = 0; i < 16; ++i)
-            if (cands[chosen[c]].mask.w[i] & ~others.w[i])
-            {
-                redundant = false;
-                break;
-            }
-        if (redundant)
-            keep[c] = 0;
-    }
+    cs.node_budget = node_budget;
+    cs.dfs(all);
     std::vector<Placement> out;
-    for (size_t c = 0; c < chosen.size(); ++c)
-        if (keep[c])
-            out.push_back(cands[chosen[c]].pl);
+    for (int c : cs.best)
+        out.push_back(cs.cands[c].pl);
     return out;
 }
 
@@ -624,7 +706,7 @@ pp_status build_plan(pp_handle h)
         auto bricks = brick_points(*cand, n);
         size_t total = 0;
         for (uint32_t t = 0; t < nt; t += step)
-            total += cover_set(make_set(t, 0, 0), bricks, R).size();
+            total += cover_set(make_set(t, 0, 0), bricks, R, 2000).size();
         if (total < best_total)
         {
             best_total = total;
@@ -649,7 +731,7 @@ pp_status build_plan(pp_handle h)
                 if (it == memo.end())
                 {
                     std::vector<uint32_t> words;
-                    for (const Placement &p : cover_set(S, bricks, R))
+                    for (const Placement &p : cover_set(S, bricks, R, 60000))
                     {
                         const int ax = R + 4 + p.ox, ay = R + p.oy;  // >= 0; +4: the margin word
                         const uint32_t word = static_cast<uint32_t>((p.brick * 4 + (ax & 3)) * pl->copy_words + ay * pl->PW + (ax >> 2));
