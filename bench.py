@@ -46,23 +46,57 @@ def measured_peak_gbs():
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
-    FIELDS = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
-              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
-              "clocks_event_reasons.sw_power_cap")
+    """SM clock and throttle reasons sampled DURING the timed region: an NVML polling thread (5 ms
+    period, so even a short region gets samples), falling back to `nvidia-smi -lms` where NVML is
+    not importable."""
+    REASONS = {"hw_slowdown": 0x8, "sw_thermal_slowdown": 0x20, "hw_thermal_slowdown": 0x40, "sw_power_cap": 0x4}
 
     def __init__(self, gpu_index):
-        self.tmp = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        import threading
+        self.sm, self.reason_bits, self.max_mhz = [], 0, None
+        self.stop_flag = False
+        self.thread = None
         self.proc = None
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(gpu_index), "--query-gpu=" + self.FIELDS,
-                                          "--format=csv,noheader,nounits", "-lms", "200"], stdout=self.tmp,
-                                         stderr=subprocess.DEVNULL)
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.dev = pynvml.nvmlDeviceGetHandleByIndex(gpu_index)
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self.dev, pynvml.NVML_CLOCK_SM))
+            self.thread = threading.Thread(target=self._poll, daemon=True)
+            self.thread.start()
         except Exception:
-            self.proc = None
+            self.nv = None
+            self.tmp = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+            try:
+                self.proc = subprocess.Popen(
+                    ["nvidia-smi", "-i", str(gpu_index), "--query-gpu=clocks.sm,clocks.max.sm,clocks_event_reasons.active",
+                     "--format=csv,noheader,nounits", "-lms", "100"], stdout=self.tmp, stderr=subprocess.DEVNULL)
+            except Exception:
+                self.proc = None
+
+    def _poll(self):
+        nv = self.nv
+        while not self.stop_flag:
+            try:
+                self.sm.append(float(nv.nvmlDeviceGetClockInfo(self.dev, nv.NVML_CLOCK_SM)))
+                self.reason_bits |= int(nv.nvmlDeviceGetCurrentClocksEventReasons(self.dev))
+            except Exception:
+                pass
+            time.sleep(0.005)
 
     def stop(self):
-        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if self.thread is not None:
+            self.stop_flag = True
+            self.thread.join(timeout=2)
+            if self.sm:
+                out["sm_mhz"] = float(np.median(self.sm))
+                out["sm_max_mhz"] = self.max_mhz
+                out["samples"] = len(self.sm)
+            out["reasons"] = sorted(k for k, bit in self.REASONS.items() if self.reason_bits & bit)
+            out["source"] = "nvml"
+            return out
         if self.proc is None:
             return out
         self.proc.terminate()
@@ -72,28 +106,23 @@ class ClockSampler:
             self.proc.kill()
         self.tmp.flush()
         self.tmp.seek(0)
-        sm, mx, reasons = [], [], set()
+        sm, mx, bits = [], [], 0
         for line in self.tmp.read().splitlines():
             p = [x.strip() for x in line.split(",")]
-            if len(p) < 9:
-                continue
             try:
-                sm.append(float(p[1]))
-                mx.append(float(p[2]))
-            except ValueError:
+                sm.append(float(p[0]))
+                mx.append(float(p[1]))
+                bits |= int(p[2], 16)
+            except (ValueError, IndexError):
                 continue
-            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), p[5:9]):
-                if v.lower().startswith("active"):
-                    reasons.add(name)
         try:
             os.unlink(self.tmp.name)
         except OSError:
             pass
         if sm:
-            out["sm_mhz"] = float(np.median(sm))
-            out["sm_max_mhz"] = float(max(mx))
-        out["reasons"] = sorted(reasons)
-        out["samples"] = len(sm)
+            out["sm_mhz"], out["sm_max_mhz"], out["samples"] = float(np.median(sm)), float(max(mx)), len(sm)
+        out["reasons"] = sorted(k for k, bit in self.REASONS.items() if bits & bit)
+        out["source"] = "nvidia-smi"
         return out
 
 
@@ -118,7 +147,7 @@ def cpu_volume_sample(cost, target_seconds, threads):
     t = time.perf_counter()
     run(4)
     probe = time.perf_counter() - t
-    rows = int(max(4, min(1024, 4 * target_seconds / max(probe, 1e-3))))
+    rows = int(max(4, min(2048, 4 * target_seconds / max(probe, 1e-3))))
     t = time.perf_counter()
     run(rows)
     dt = time.perf_counter() - t
@@ -154,7 +183,7 @@ def run_reference(args, rank):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=100)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")

@@ -30,6 +30,7 @@
 #include <cmath>
 #include <cstring>
 #include <map>
+#include <utility>
 #include <vector>
 
 namespace
@@ -41,6 +42,49 @@ constexpr int MAX_LIST_WORDS = 6400;
 constexpr int MAX_R = 15;
 constexpr size_t SMEM_LIMIT = 227 * 1024;
 
+
+// ---------------------------------------------------------------------------------------------
+// Brick libraries. Table 0 is the costmap itself (the one-point brick); table k > 0 is
+// T_k = max(T_a, T_b shifted by (du, dv)). Tables are listed in dependency-level order. The
+// recipes are compile-time data so that the table build below unrolls completely.
+//   STAIRS  runs of 2/4/8 along x, 2/4 along y, the two diagonals, and four 4-cell "stair" bricks
+//           (two 2-runs offset by (2,+-1) or (+-1,2)) that follow rasterised oblique edges
+//   RUNS3   runs of 2/3/6 along x and y, diagonals of 2/3/4
+//   BLOCKS  rectangles 2x2 .. 8x8 for solid footprints
+//   RUNS    runs of 2/4/8 along x and y, diagonals of 2/4
+// ---------------------------------------------------------------------------------------------
+struct Recipe
+{
+    int a, b, du, dv;
+};
+constexpr int N_LIBS = 4;
+__host__ __device__ constexpr int lib_size(int lib) { return lib == 3 ? 11 : 12; }
+__host__ __device__ constexpr Recipe lib_recipe(int lib, int k)
+{
+    constexpr Recipe T[N_LIBS][MAX_TABLES] = {
+        {{0, 0, 0, 0}, {0, 0, 1, 0}, {0, 0, 0, 1}, {0, 0, 1, 1}, {0, 0, 1, -1}, {1, 1, 2, 0}, {2, 2, 0, 2}, {1, 1, 2, 1}, {1, 1, 2, -1}, {2, 2, 1, 2}, {2, 2, -1, 2}, {5, 5, 4, 0}},
+        {{0, 0, 0, 0}, {0, 0, 1, 0}, {0, 0, 0, 1}, {0, 0, 1, 1}, {0, 0, 1, -1}, {1, 0, 2, 0}, {2, 0, 0, 2}, {3, 0, 2, 2}, {4, 0, 2, -2}, {3, 3, 2, 2}, {5, 5, 3, 0}, {6, 6, 0, 3}},
+        {{0, 0, 0, 0}, {0, 0, 1, 0}, {0, 0, 0, 1}, {1, 1, 0, 1}, {1, 1, 2, 0}, {2, 2, 0, 2}, {3, 3, 2, 0}, {4, 4, 4, 0}, {5, 5, 0, 4}, {6, 6, 0, 2}, {9, 9, 4, 0}, {10, 10, 0, 4}},
+        {{0, 0, 0, 0}, {0, 0, 1, 0}, {0, 0, 0, 1}, {0, 0, 1, 1}, {0, 0, 1, -1}, {1, 1, 2, 0}, {2, 2, 0, 2}, {3, 3, 2, 2}, {4, 4, 2, -2}, {5, 5, 4, 0}, {6, 6, 0, 4}, {0, 0, 0, 0}}};
+    return T[lib][k];
+}
+__host__ __device__ constexpr int lib_level(int lib, int k)
+{
+    if (k == 0)
+        return 0;
+    const Recipe r = lib_recipe(lib, k);
+    const int la = lib_level(lib, r.a), lb = lib_level(lib, r.b);
+    return 1 + (la > lb ? la : lb);
+}
+constexpr int MAX_LEVEL = 6;
+__host__ __device__ constexpr bool level_in_use(int lib, int lvl)
+{
+    for (int k = 0; k < lib_size(lib); ++k)
+        if (lib_level(lib, k) == lvl)
+            return true;
+    return false;
+}
+
 struct FastArgs
 {
     const uint8_t *cost;
@@ -50,9 +94,6 @@ struct FastArgs
     uint32_t W, H, tiles_x, tiles_y, tile_x0, tile_y0;
     int32_t R, PW, rows, copy_words, n_tables;
     uint32_t t_first, n_t;
-    uint8_t rec_a[MAX_TABLES], rec_b[MAX_TABLES];
-    int8_t rec_du[MAX_TABLES], rec_dv[MAX_TABLES];
-    uint8_t lvl_end[8];  // tables [lvl_end[l-1], lvl_end[l]) form dependency level l (table 0 is the costmap)
     uint16_t list_off[MAX_T_PER_LAUNCH][4];
     uint16_t list_len[MAX_T_PER_LAUNCH][4];
     alignas(16) uint32_t lists[MAX_LIST_WORDS];  // byte offsets into shared memory, relative to the thread's base
@@ -163,7 +204,99 @@ __device__ __forceinline__ void run_bins(const FastArgs &a, const uint32_t *sm, 
     }
 }
 
-template <int PW>
+
+// Table build. Recipes and levels are compile-time constants (forced through template arguments),
+// so for every level both passes unroll over the tables of that level and all shared-memory loads
+// of a word are issued before the first dependent operation.
+//   pass 1: copy 0 of T_k = max(T_a, T_b shifted by (du, dv))
+//   pass 2: copies 1..3 = bytes s..s+3 of the word pair (i, i+1) of copy 0 (zero past the row end)
+// Each thread owns the words tid, tid + FT_THREADS, ... of a table copy.
+template <int LIB, int K>
+struct TableInfo
+{
+    static constexpr Recipe rc = lib_recipe(LIB, K < lib_size(LIB) ? K : 0);
+    static constexpr int level = K < lib_size(LIB) ? lib_level(LIB, K) : -1;
+};
+
+template <int... Ks, class F>
+__device__ __forceinline__ void for_each_index(std::integer_sequence<int, Ks...>, F &&f)
+{
+    (f(std::integral_constant<int, Ks>{}), ...);
+}
+
+template <int PW, int LIB, int LVL>
+__device__ __forceinline__ void build_level(uint32_t *sm, int CW, int rows, int n_tables, int tid)
+{
+    using AllTables = std::make_integer_sequence<int, MAX_TABLES>;
+    if constexpr (!level_in_use(LIB, LVL))
+        return;
+    if constexpr (LVL > 0)
+    {
+#pragma unroll 1
+        for (int i = tid; i < CW; i += FT_THREADS)
+        {
+            const int sr = i / PW, sw = i % PW;
+            uint32_t va[MAX_TABLES], vb[MAX_TABLES];
+            for_each_index(AllTables{}, [&](auto kc) {
+                constexpr int k = decltype(kc)::value;
+                if constexpr (TableInfo<LIB, k>::level == LVL)
+                {
+                    constexpr Recipe rc = TableInfo<LIB, k>::rc;
+                    constexpr int dw = rc.du >> 2;  // floor
+                    if (k < n_tables)
+                    {
+                        const int r2 = sr + rc.dv, w2 = sw + dw;
+                        va[k] = sm[rc.a * 4 * CW + i];
+                        vb[k] = (r2 >= 0 && r2 < rows && w2 >= 0 && w2 < PW) ? sm[rc.b * 4 * CW + (rc.du & 3) * CW + i + rc.dv * PW + dw] : 0u;
+                    }
+                }
+            });
+            for_each_index(AllTables{}, [&](auto kc) {
+                constexpr int k = decltype(kc)::value;
+                if constexpr (TableInfo<LIB, k>::level == LVL)
+                    if (k < n_tables)
+                        sm[k * 4 * CW + i] = bytemax4(va[k], vb[k]);
+            });
+        }
+        __syncthreads();
+    }
+#pragma unroll 1
+    for (int i = tid; i < CW; i += FT_THREADS)
+    {
+        const bool has_next = i % PW + 1 < PW;
+        uint32_t v[MAX_TABLES], nx[MAX_TABLES];
+        for_each_index(AllTables{}, [&](auto kc) {
+            constexpr int k = decltype(kc)::value;
+            if constexpr (TableInfo<LIB, k>::level == LVL)
+                if (k < n_tables)
+                {
+                    v[k] = sm[k * 4 * CW + i];
+                    nx[k] = has_next ? sm[k * 4 * CW + i + 1] : 0u;
+                }
+        });
+        for_each_index(AllTables{}, [&](auto kc) {
+            constexpr int k = decltype(kc)::value;
+            if constexpr (TableInfo<LIB, k>::level == LVL)
+                if (k < n_tables)
+                {
+                    uint32_t *T = sm + k * 4 * CW + i;
+                    T[CW] = __funnelshift_r(v[k], nx[k], 8);
+                    T[2 * CW] = __funnelshift_r(v[k], nx[k], 16);
+                    T[3 * CW] = __funnelshift_r(v[k], nx[k], 24);
+                }
+        });
+    }
+    __syncthreads();
+}
+
+template <int PW, int LIB, int... LVLs>
+__device__ __forceinline__ void build_all_levels(uint32_t *sm, int CW, int rows, int n_tables, int tid,
+                                                 std::integer_sequence<int, LVLs...>)
+{
+    (build_level<PW, LIB, LVLs>(sm, CW, rows, n_tables, tid), ...);
+}
+
+template <int PW, int LIB>
 __global__ void __launch_bounds__(FT_THREADS, 1) se2_fast_kernel(const __grid_constant__ FastArgs a)
 {
     extern __shared__ __align__(16) uint32_t sm[];
@@ -219,94 +352,45 @@ __global__ void __launch_bounds__(FT_THREADS, 1) se2_fast_kernel(const __grid_co
     if (!any_fast)
         return;  // every bin of this tile belongs to the generic work list
 
-    // Word slots of this thread in a table copy (linear index tid + j*FT_THREADS), with their row
-    // and column worked out once for all tables.
-    constexpr int SLOTS = ((FT_H + 2 * MAX_R) * 30 + FT_THREADS - 1) / FT_THREADS;  // rows * PW <= 62 * 30
-    int slot_r[SLOTS], slot_w[SLOTS];
-#pragma unroll
-    for (int j = 0; j < SLOTS; ++j)
-    {
-        const int i = tid + j * FT_THREADS;
-        slot_r[j] = i < CW ? i / PW : -1000;
-        slot_w[j] = i - (i / PW) * PW;
-    }
-    // byte-shifted copies 1..3 of a table from its copy 0: word i of copy s = bytes s..s+3 of the
-    // word pair (i, i+1) (zero past the end of the row)
-    auto make_copies = [&](uint32_t *T) {
-#pragma unroll
-        for (int j = 0; j < SLOTS; ++j)
-        {
-            const int i = tid + j * FT_THREADS;
-            if (slot_r[j] >= 0)
-            {
-                const uint32_t v = T[i];
-                const uint32_t nx = (slot_w[j] + 1 < PW) ? T[i + 1] : 0u;
-                T[CW + i] = __funnelshift_r(v, nx, 8);
-                T[2 * CW + i] = __funnelshift_r(v, nx, 16);
-                T[3 * CW + i] = __funnelshift_r(v, nx, 24);
-            }
-        }
-    };
-    make_copies(sm);
-    __syncthreads();
-
-    // derived brick tables, level by level (tables of one level depend only on earlier levels):
-    // T_k = max(T_a, T_b shifted by (du, dv)). Pass 1 writes copy 0 of every table of the level,
-    // pass 2 its shifted copies.
-    int k0 = 1;
-    for (int lvl = 0; lvl < 8; ++lvl)
-    {
-        const int k_end = a.lvl_end[lvl];
-        for (int k = k0; k < k_end; ++k)
-        {
-            const int du = a.rec_du[k], dv = a.rec_dv[k];
-            const int dw = du >> 2;  // floor
-            const uint32_t *A = sm + a.rec_a[k] * 4 * CW;
-            const uint32_t *B = sm + a.rec_b[k] * 4 * CW + (du & 3) * CW + dv * PW + dw;
-            uint32_t *D = sm + k * 4 * CW;
-#pragma unroll
-            for (int j = 0; j < SLOTS; ++j)
-            {
-                const int i = tid + j * FT_THREADS;
-                if (slot_r[j] >= 0)
-                {
-                    const int r2 = slot_r[j] + dv, w2 = slot_w[j] + dw;
-                    const uint32_t vb = (r2 >= 0 && r2 < rows && w2 >= 0 && w2 < PW) ? B[i] : 0u;
-                    D[i] = bytemax4(A[i], vb);
-                }
-            }
-        }
-        __syncthreads();
-        for (int k = k0; k < k_end; ++k)
-            make_copies(sm + k * 4 * CW);
-        __syncthreads();
-        k0 = k_end;
-        if (k0 >= a.n_tables)
-            break;
-    }
+    // brick tables, level by level (tables of one level depend only on earlier levels)
+    build_all_levels<PW, LIB>(sm, CW, rows, a.n_tables, tid, std::make_integer_sequence<int, MAX_LEVEL + 1>{});
 
     // output phase: WARPS_PER_BIN warps per bin, NGROUPS bins in flight
     run_bins<PW>(a, sm, s_cls, warp / WARPS_PER_BIN, warp % WARPS_PER_BIN, lane, tx0, ty0);
 }
 
+
+// one instantiation per (pitch, library)
+template <class F>
+auto dispatch_fast(int pw, int lib, F f)
+{
+#define PP_CASE(P, L) \
+    if (pw == P && lib == L) return f(se2_fast_kernel<P, L>);
+    PP_CASE(22, 0) PP_CASE(22, 1) PP_CASE(22, 2) PP_CASE(22, 3)
+    PP_CASE(26, 0) PP_CASE(26, 1) PP_CASE(26, 2)
+#undef PP_CASE
+    return f(se2_fast_kernel<26, 3>);
+}
+cudaError_t set_fast_smem(int pw, int lib, size_t bytes)
+{
+    return dispatch_fast(pw, lib, [&](auto kernel) { return cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(bytes)); });
+}
+void launch_fast(int pw, int lib, dim3 grid, size_t smem, cudaStream_t stream, const FastArgs &args)
+{
+    dispatch_fast(pw, lib, [&](auto kernel) { kernel<<<grid, FT_THREADS, smem, stream>>>(args); return cudaSuccess; });
+}
+
 // ---------------------------------------------------------------------------------------------
 // host planner
 // ---------------------------------------------------------------------------------------------
-struct Recipe
-{
-    int a, b, du, dv;
-};
 using Library = std::vector<Recipe>;
-
-// index 0 is always the costmap itself (the one-point brick)
-const Library LIB_STAIRS = {{0, 0, 0, 0}, {0, 0, 1, 0}, {0, 0, 0, 1}, {0, 0, 1, 1}, {0, 0, 1, -1}, {1, 1, 2, 0},
-                            {2, 2, 0, 2}, {1, 1, 2, 1}, {1, 1, 2, -1}, {2, 2, 1, 2}, {2, 2, -1, 2}, {5, 5, 4, 0}};
-const Library LIB_RUNS3 = {{0, 0, 0, 0}, {0, 0, 1, 0}, {0, 0, 0, 1}, {0, 0, 1, 1}, {0, 0, 1, -1}, {1, 0, 2, 0},
-                           {2, 0, 0, 2}, {3, 0, 2, 2}, {4, 0, 2, -2}, {3, 3, 2, 2}, {5, 5, 3, 0}, {6, 6, 0, 3}};
-const Library LIB_BLOCKS = {{0, 0, 0, 0}, {0, 0, 1, 0}, {0, 0, 0, 1}, {1, 1, 0, 1}, {1, 1, 2, 0}, {2, 2, 0, 2},
-                            {3, 3, 2, 0}, {4, 4, 4, 0}, {5, 5, 0, 4}, {6, 6, 0, 2}, {9, 9, 4, 0}, {10, 10, 0, 4}};
-const Library LIB_RUNS = {{0, 0, 0, 0}, {0, 0, 1, 0}, {0, 0, 0, 1}, {0, 0, 1, 1}, {0, 0, 1, -1}, {1, 1, 2, 0},
-                          {2, 2, 0, 2}, {3, 3, 2, 2}, {4, 4, 2, -2}, {5, 5, 4, 0}, {6, 6, 0, 4}};
+Library make_library(int lib)
+{
+    Library out;
+    for (int k = 0; k < lib_size(lib); ++k)
+        out.push_back(lib_recipe(lib, k));
+    return out;
+}
 
 using Offsets = std::vector<std::pair<int, int>>;  // sorted, unique (dx, dy)
 
@@ -534,6 +618,7 @@ struct Se2Plan
     int R = 0, PW = 0, rows = 0, copy_words = 0, n_tables = 0;
     size_t smem_bytes = 0;
     Library lib;
+    int lib_id = 0;
     uint32_t tiles_x = 0, tiles_y = 0;
     uint8_t *d_xclass = nullptr, *d_yclass = nullptr;
     std::vector<uint8_t> h_xclass, h_yclass;
@@ -696,14 +781,14 @@ pp_status build_plan(pp_handle h)
         return S;
     };
     // 4. choose the library on a sample of bins
-    const Library *candidates[] = {&LIB_STAIRS, &LIB_RUNS3, &LIB_BLOCKS, &LIB_RUNS};
-    const Library *best_lib = nullptr;
+    int best_lib = 0;
     size_t best_total = ~static_cast<size_t>(0);
     const uint32_t step = std::max(1u, nt / 18);
-    for (const Library *cand : candidates)
+    for (int cand = 0; cand < N_LIBS; ++cand)
     {
-        const int n = std::min<int>(slots, static_cast<int>(cand->size()));
-        auto bricks = brick_points(*cand, n);
+        const Library lib = make_library(cand);
+        const int n = std::min<int>(slots, static_cast<int>(lib.size()));
+        auto bricks = brick_points(lib, n);
         size_t total = 0;
         for (uint32_t t = 0; t < nt; t += step)
             total += cover_set(make_set(t, 0, 0), bricks, R, 2000).size();
@@ -713,8 +798,12 @@ pp_status build_plan(pp_handle h)
             best_lib = cand;
         }
     }
-    pl->n_tables = std::min<int>(slots, static_cast<int>(best_lib->size()));
-    pl->lib.assign(best_lib->begin(), best_lib->begin() + pl->n_tables);
+    {
+        const Library lib = make_library(best_lib);
+        pl->lib_id = best_lib;
+        pl->n_tables = std::min<int>(slots, static_cast<int>(lib.size()));
+        pl->lib.assign(lib.begin(), lib.begin() + pl->n_tables);
+    }
     pl->smem_bytes = table_bytes * pl->n_tables;
     auto bricks = brick_points(pl->lib, pl->n_tables);
 
@@ -788,10 +877,7 @@ pp_status build_plan(pp_handle h)
         PP_CUDA(h, cudaMemcpyAsync(pl->d_work, pl->h_work.data(), pl->h_work.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, h->stream));
     }
     PP_CUDA(h, cudaStreamSynchronize(h->stream));
-    if (pl->PW == 22)
-        PP_CUDA(h, cudaFuncSetAttribute(se2_fast_kernel<22>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(pl->smem_bytes)));
-    else
-        PP_CUDA(h, cudaFuncSetAttribute(se2_fast_kernel<26>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(pl->smem_bytes)));
+    PP_CUDA(h, set_fast_smem(pl->PW, pl->lib_id, pl->smem_bytes));
     pl->usable = true;
     return PP_OK;
 }
@@ -828,27 +914,6 @@ pp_status pp_se2_launch_fast(pp_handle h, uint32_t x0, uint32_t y0, uint32_t x1,
     args.rows = pl->rows;
     args.copy_words = pl->copy_words;
     args.n_tables = pl->n_tables;
-    {
-        // dependency levels; the libraries list their tables in level order
-        int level[MAX_TABLES] = {0};
-        for (int l = 0; l < 8; ++l)
-            args.lvl_end[l] = static_cast<uint8_t>(pl->n_tables);
-        for (int k = 1; k < pl->n_tables; ++k)
-        {
-            level[k] = 1 + std::max(level[pl->lib[k].a], level[pl->lib[k].b]);
-            PP_REQUIRE(h, level[k] >= level[k - 1] && level[k] <= 8, PP_ERR_STATE, "brick library is not in level order");
-        }
-        for (int k = 1; k < pl->n_tables; ++k)
-            for (int l = 0; l < level[k] - 1; ++l)
-                args.lvl_end[l] = std::min<uint8_t>(args.lvl_end[l], static_cast<uint8_t>(k));
-    }
-    for (int k = 0; k < pl->n_tables; ++k)
-    {
-        args.rec_a[k] = static_cast<uint8_t>(pl->lib[k].a);
-        args.rec_b[k] = static_cast<uint8_t>(pl->lib[k].b);
-        args.rec_du[k] = static_cast<int8_t>(pl->lib[k].du);
-        args.rec_dv[k] = static_cast<int8_t>(pl->lib[k].dv);
-    }
     const dim3 grid(tx_hi - tx_lo, ty_hi - ty_lo, 1);
     const uint64_t n_tiles = static_cast<uint64_t>(grid.x) * grid.y;
     double sample_sum = 0.0;
@@ -879,10 +944,7 @@ pp_status pp_se2_launch_fast(pp_handle h, uint32_t x0, uint32_t y0, uint32_t x1,
         PP_REQUIRE(h, n > 0, PP_ERR_RANGE, "a single heading bin needs more than %d sample words", MAX_LIST_WORDS);
         args.t_first = t;
         args.n_t = n;
-        if (pl->PW == 22)
-            se2_fast_kernel<22><<<grid, FT_THREADS, pl->smem_bytes, h->stream>>>(args);
-        else
-            se2_fast_kernel<26><<<grid, FT_THREADS, pl->smem_bytes, h->stream>>>(args);
+        launch_fast(pl->PW, pl->lib_id, grid, pl->smem_bytes, h->stream, args);
         h->launches++;
         PP_CUDA(h, cudaGetLastError());
         // bookkeeping + the exact path for the (tile, bin) pairs outside uniform ranges
