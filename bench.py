@@ -226,8 +226,9 @@ def main():
         return float(t.item())
 
     cost = make_inputs()
-    per = N_THETA // world
-    t0, t1 = rank * per, (rank + 1) * per
+    from path_planner_b200.sharding import bin_range
+    t0, t1 = bin_range(N_THETA, rank, world)
+    per = t1 - t0
     h = capi.Handle(local_rank)
     pinned_cost = capi.PinnedBuffer(W * H)
     pinned_cost.array.reshape(H, W)[:] = cost
