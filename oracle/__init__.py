@@ -22,6 +22,65 @@ f32p = np.ctypeslib.ndpointer(np.float32, flags="C_CONTIGUOUS")
 f64p = np.ctypeslib.ndpointer(np.float64, flags="C_CONTIGUOUS")
 
 
+class PlanParams(C.Structure):
+    """Search parameters, defaults from src/path_planner/config/params.yaml:32-45."""
+    _fields_ = [("motion_type", C.c_int), ("n_theta", C.c_uint32), ("minimum_turning_radius", C.c_float),
+                ("cost_penalty", C.c_float), ("change_penalty", C.c_float), ("non_straight_penalty", C.c_float),
+                ("reverse_penalty", C.c_float), ("analytic_expansion_ratio", C.c_float),
+                ("analytic_expansion_tolerance", C.c_float), ("tolerance", C.c_float), ("max_iterations", C.c_uint32),
+                ("max_on_approach_iterations", C.c_uint32)]
+
+
+def plan_params(motion_type=2, n_theta=72, minimum_turning_radius=0.84, cost_penalty=2.0, change_penalty=0.01,
+                non_straight_penalty=1.2, reverse_penalty=3.0, analytic_expansion_ratio=1.0,
+                analytic_expansion_tolerance=3.0, tolerance=0.6, max_iterations=100000, max_on_approach_iterations=1000):
+    return PlanParams(motion_type, n_theta, minimum_turning_radius, cost_penalty, change_penalty, non_straight_penalty,
+                      reverse_penalty, analytic_expansion_ratio, analytic_expansion_tolerance, tolerance, max_iterations,
+                      max_on_approach_iterations)
+
+
+class E2E:
+    """oracle/_ref/libpp_e2e.so: the reference search over the drop-in CollisionChecker (see e2e_harness.cpp)."""
+
+    def __init__(self):
+        path = os.path.join(_HERE, "_ref", "libpp_e2e.so")
+        if not os.path.exists(path):
+            raise FileNotFoundError(path)
+        self.lib = C.CDLL(path)
+        self.lib.e2e_heading_fraction.restype = C.c_float
+        self.lib.e2e_heading_fraction.argtypes = [C.c_float, C.c_uint32]
+        self.lib.e2e_plan.argtypes = [C.c_int, u8p, C.c_uint32, C.c_uint32, C.c_double, f32p, C.c_int, C.c_int, C.c_void_p,
+                                      C.POINTER(PlanParams), f32p, f32p, f32p, C.c_int, C.POINTER(C.c_int),
+                                      C.POINTER(C.c_int), C.POINTER(C.c_double), C.POINTER(C.c_double),
+                                      C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
+
+    def heading_fraction(self, start_theta, n_theta):
+        return float(self.lib.e2e_heading_fraction(start_theta, n_theta))
+
+    def plan(self, mode, cost, res, boundary, hole, start, goal, oracle_volume=None, params=None):
+        P = plan_params(**(params or {}))
+        H, W = cost.shape
+        b = np.ascontiguousarray(boundary, np.float32)
+        path = np.zeros((20000, 3), np.float32)
+        n, it = C.c_int(0), C.c_int(0)
+        ms, prep = C.c_double(0), C.c_double(0)
+        lk, ex = C.c_uint64(0), C.c_uint64(0)
+        s = np.ascontiguousarray(start, np.float32)
+        g = np.ascontiguousarray(goal, np.float32)
+        vol = None if oracle_volume is None else oracle_volume.ctypes.data_as(C.c_void_p)
+        ok = self.lib.e2e_plan(mode, cost, W, H, res, b, len(b), int(hole), vol, C.byref(P), s, g, path, len(path),
+                               C.byref(n), C.byref(it), C.byref(ms), C.byref(prep), C.byref(lk), C.byref(ex))
+        return {"ok": ok, "path": path[:n.value].copy(), "iterations": it.value, "plan_ms": ms.value,
+                "prepare_ms": prep.value, "lookups": lk.value, "exact_calls": ex.value}
+
+
+def load_e2e():
+    try:
+        return E2E()
+    except (FileNotFoundError, OSError):
+        return None
+
+
 def build(verbose=False):
     """Compile the port (always) and _ref (only where /root/reference exists)."""
     r = subprocess.run(["make", "-C", _HERE, "all"], capture_output=True, text=True)
@@ -200,6 +259,21 @@ class Ref:
                                  C.byref(qs))
         self.last_build_seconds, self.last_query_seconds = bs.value, qs.value
         return idx, d2, cnt, found
+
+    def plan(self, cost, res, boundary, hole, start, goal, params=None):
+        """Unmodified reference planner (AstarHybrid::createPath). Returns (ok, path[n,3], iterations, ms)."""
+        P = plan_params(**(params or {}))
+        H, W = cost.shape
+        b = np.ascontiguousarray(boundary, np.float32)
+        path = np.zeros((20000, 3), np.float32)
+        n, it, ms = C.c_int(0), C.c_int(0), C.c_double(0)
+        s = np.ascontiguousarray(start, np.float32)
+        g = np.ascontiguousarray(goal, np.float32)
+        self.lib.ref_plan.argtypes = [u8p, C.c_uint32, C.c_uint32, C.c_double, f32p, C.c_int, C.c_int, C.POINTER(PlanParams),
+                                      f32p, f32p, f32p, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_double)]
+        ok = self.lib.ref_plan(cost, W, H, res, b, len(b), int(hole), C.byref(P), s, g, path, len(path), C.byref(n),
+                               C.byref(it), C.byref(ms))
+        return bool(ok), path[:n.value].copy(), it.value, ms.value
 
 
 def load_port():

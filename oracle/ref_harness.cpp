@@ -218,4 +218,53 @@ int ref_radius_topk(const double *pts_xy, uint32_t N, const double *q_xy, uint32
         *query_seconds = std::chrono::duration<double>(toc - mid).count();
     return 0;
 }
+
+// The unmodified reference planner (continuous-pose footprint checks, its own lazy heuristic),
+// AstarHybrid::createPath astar_hybrid.cpp:392-433. Reported for context next to the table-driven runs.
+struct RefPlanParams
+{
+    int motion_type;  // 1 Dubins, 2 ReedsShepp
+    unsigned int n_theta;
+    float minimum_turning_radius, cost_penalty, change_penalty, non_straight_penalty, reverse_penalty;
+    float analytic_expansion_ratio, analytic_expansion_tolerance, tolerance;
+    unsigned int max_iterations, max_on_approach_iterations;
+};
+
+int ref_plan(const uint8_t *cost, uint32_t W, uint32_t H, double res, const float *boundary, int nb, int hole,
+             const RefPlanParams *p, const float *start_xyt, const float *goal_xyt, float *path_out, int max_pts, int *n_pts,
+             int *iterations, double *plan_ms)
+{
+    Scene s(cost, W, H, res, 0.0, 0.0, boundary, nb, hole);
+    SearchInfo info;
+    info.size_theta = p->n_theta;
+    info.minimum_turning_radius = p->minimum_turning_radius;
+    info.cost_penalty = p->cost_penalty;
+    info.change_penalty = p->change_penalty;
+    info.non_straight_penalty = p->non_straight_penalty;
+    info.reverse_penalty = p->reverse_penalty;
+    info.analytic_expansion_ratio = p->analytic_expansion_ratio;
+    info.analytic_expansion_tolerance = p->analytic_expansion_tolerance;
+    info.tolerance = p->tolerance;
+    info.max_iterations = p->max_iterations;
+    info.max_on_approach_iterations = p->max_on_approach_iterations;
+    info.motion_type = p->motion_type == 2 ? MotionType::ReedsShepp : MotionType::Dubins;
+    info.max_millsec = 1000000000;
+    AstarHybrid astar(&info, &s.checker);
+    Coordinate start(start_xyt[0], start_xyt[1], start_xyt[2]), goal(goal_xyt[0], goal_xyt[1], goal_xyt[2]);
+    Coordinates path;
+    int it = 0;
+    auto tic = std::chrono::steady_clock::now();
+    const bool ok = astar.createPath(start, goal, path, it);
+    *plan_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - tic).count();
+    *iterations = it;
+    const int n = static_cast<int>(path.size());
+    *n_pts = n;
+    for (int i = 0; i < n && i < max_pts; ++i)
+    {
+        path_out[3 * i] = path[i].x;
+        path_out[3 * i + 1] = path[i].y;
+        path_out[3 * i + 2] = path[i].theta;
+    }
+    return ok ? 1 : 0;
+}
 }

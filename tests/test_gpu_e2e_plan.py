@@ -1,0 +1,87 @@
+"""GPU: the north star's third correctness gate -- with the GPU tables substituted in, the
+reference's own Hybrid-A* search (astar_hybrid.cpp, compiled from the reference sources with one
+hook line, see oracle/e2e_harness.cpp) returns the identical path.
+  (A) oracle-built volume + the reference's own lazily grown heuristic
+  (B) GPU-built volume + GPU heuristic field injected
+Pass = identical Coordinates and identical iteration count. The unmodified reference (C) is run
+for context: it checks continuous poses, (A)/(B) quantise them to cell centre and nearest bin."""
+import numpy as np
+import pytest
+
+import oracle
+from path_planner_b200.synth import make_costmap
+
+pytestmark = pytest.mark.gpu
+RES = 0.05
+
+
+def scene(W, seed, coverage, start, goal, radius=25):
+    """Planning scenes: no speckled NO_INFORMATION cells (any 255 under the footprint is a collision,
+    collision_checker.cpp:165) and start/goal pockets wider than the footprint reach."""
+    pockets = [(int(start[0] / RES), int(start[1] / RES), radius), (int(goal[0] / RES), int(goal[1] / RES), radius)]
+    return make_costmap(W, W, seed=seed, coverage=coverage, unknown_frac=0.0, pockets=pockets)
+
+
+def run_case(cost, boundary, hole, start, goal, params, port):
+    e2e = oracle.load_e2e()
+    if e2e is None:
+        pytest.skip("oracle/_ref/libpp_e2e.so not built (needs the reference sources at build time)")
+    n_theta = params.get("n_theta", 72)
+    frac = e2e.heading_fraction(start[2], n_theta)
+    pts = port.footprint_points(RES, boundary, hole)
+    vol = port.se2_volume(cost, pts, n_theta, 0.5, 0.5, frac, nthreads=0)
+    a = e2e.plan(0, cost, RES, boundary, hole, start, goal, oracle_volume=vol, params=params)
+    b = e2e.plan(1, cost, RES, boundary, hole, start, goal, params=params)
+    return a, b
+
+
+def check_identical(a, b):
+    assert a["ok"] == 1 and b["ok"] == 1, (a["ok"], b["ok"])
+    assert a["iterations"] == b["iterations"], (a["iterations"], b["iterations"])
+    assert a["path"].shape == b["path"].shape
+    assert np.array_equal(a["path"], b["path"])
+    assert b["exact_calls"] == 0 and b["lookups"] > 0  # every footprint check was a table lookup
+
+
+def test_identical_path_config1_400x400_rect(port):
+    """BASELINE config 1: 400x400 @0.05 m, 72 bins, rectangular footprint, Reeds-Shepp."""
+    start, goal = (2.0, 2.0, 0.3), (17.5, 17.0, 1.2)
+    a, b = run_case(scene(400, 3, 0.06, start, goal), [0.64, 0.46], True, start, goal, {"motion_type": 2}, port)
+    check_identical(a, b)
+    assert len(a["path"]) > 50 and a["iterations"] > 10000  # a long search: ~9e4 expansions
+    print("config1: iterations %d, plan %.1f ms (A) vs %.1f ms (B; prepare %.1f ms)" % (a["iterations"], a["plan_ms"], b["plan_ms"], b["prepare_ms"]))
+
+
+@pytest.mark.parametrize("seed,start,goal", [(5, (1.5, 1.5, 0.0), (18.0, 3.0, -1.0)), (8, (3.0, 17.0, -0.5), (16.0, 2.5, 0.0)),
+                                             (9, (10.0, 10.0, 2.0), (2.0, 18.0, 3.0))])
+def test_identical_path_more_scenes(port, seed, start, goal):
+    a, b = run_case(scene(400, seed, 0.05, start, goal), [0.64, 0.46], True, start, goal, {"motion_type": 2}, port)
+    if a["ok"] != 1:
+        assert b["ok"] == a["ok"] and a["iterations"] == b["iterations"]  # both fail the same way
+        return
+    check_identical(a, b)
+
+
+def test_identical_path_config2_2048_box(port):
+    """BASELINE config 2: 2048x2048 with random obstacles, 72 bins, the asymmetric 4-number box
+    (the reference checker's closest thing to a polygon footprint)."""
+    start, goal = (5.0, 5.0, 0.5), (60.0, 45.0, 0.0)
+    cost = scene(2048, 2, 0.04, start, goal)
+    a, b = run_case(cost, [-0.2, -0.25, 0.6, 0.25], True, start, goal, {"motion_type": 2, "max_iterations": 400000}, port)
+    check_identical(a, b)
+    print("config2: iterations %d, plan %.1f ms (A, CPU tables) vs %.1f ms (B, GPU tables; prepare %.1f ms)"
+          % (a["iterations"], a["plan_ms"], b["plan_ms"], b["prepare_ms"]))
+
+
+def test_unmodified_reference_for_context(port, ref):
+    """(C): not a parity gate -- shows how far the cell-quantised tables move the plan."""
+    if ref is None:
+        pytest.skip("oracle/_ref not built")
+    start, goal = (1.5, 1.5, 0.0), (18.0, 3.0, -1.0)
+    cost = scene(400, 5, 0.05, start, goal)
+    ok, path, it, ms = ref.plan(cost, RES, [0.64, 0.46], True, start, goal, {"motion_type": 2})
+    a, b = run_case(cost, [0.64, 0.46], True, start, goal, {"motion_type": 2}, port)
+    assert ok and b["ok"] == 1
+    assert np.allclose(path[0], b["path"][0]) and np.allclose(path[-1], b["path"][-1])  # same endpoints
+    print("reference: %d iterations %.1f ms; table-driven: %d iterations %.1f ms (+%.1f ms prepare)"
+          % (it, ms, b["iterations"], b["plan_ms"], b["prepare_ms"]))
