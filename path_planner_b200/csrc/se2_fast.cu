@@ -28,6 +28,7 @@
 
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <utility>
@@ -145,28 +146,39 @@ __device__ __forceinline__ void accumulate(uint32_t (&odd)[QPT], uint32_t (&even
     }
 }
 
-// Output phase for one warp. WARPS_PER_BIN warps serve one bin; group g takes bins g, g+NGROUPS, ...
-// Thread -> quad column (lane & 15) and rows gw + 8*(lane >> 4) + quad_row(j). Half-warps sit 8 rows
-// apart, which is bank-conflict free for PW = 2 (mod 4). The loads of the next sample pair are
-// issued before the max operations of the current one (software pipelining by hand).
+// Output phase. A work unit is (bin, half of the tile's rows): one warp computes 16 quad columns x
+// 16 rows of one bin, 8 quads per thread. Thread -> quad column (lane & 15) and rows
+// 8*(lane >> 4) + half + quad_row(j): half-warps sit 8 rows apart, which is bank-conflict free for
+// PW = 2 (mod 4). Warps fetch units from a shared counter, so bins with long and short sample
+// lists balance out. The loads of the next sample pair are issued before the max operations of
+// the current one (software pipelining by hand).
 template <int PW>
-__device__ __forceinline__ void run_bins(const FastArgs &a, const uint32_t *sm, const uint8_t *s_cls, int group, int gw,
-                                         int lane, int tx0, int ty0)
+__device__ __forceinline__ void run_units(const FastArgs &a, const uint32_t *sm, const uint8_t *s_cls, uint32_t *s_next,
+                                          int lane, int tx0, int ty0)
 {
     const int q = lane & 15;
-    const int row0 = gw + 8 * (lane >> 4);
-    const uint8_t *smb = reinterpret_cast<const uint8_t *>(sm + row0 * PW + q);
     const int W = static_cast<int>(a.W), H = static_cast<int>(a.H);
-    const int gx = tx0 + 4 * q, gy = ty0 + row0;
+    const int gx = tx0 + 4 * q;
     const bool in_x = gx < W;
     const size_t plane = static_cast<size_t>(a.W) * a.H;
     const size_t rs = a.W;
-    uint8_t *out = a.vol + plane * (a.t_first + group) + static_cast<size_t>(gy) * a.W + gx;
-    for (uint32_t t = group; t < a.n_t; t += NGROUPS, out += NGROUPS * plane)
+    const uint32_t n_units = 2 * a.n_t;
+    while (true)
     {
+        uint32_t unit = 0;
+        if (lane == 0)
+            unit = atomicAdd(s_next, 1u);
+        unit = __shfl_sync(0xffffffffu, unit, 0);
+        if (unit >= n_units)
+            break;
+        const uint32_t t = unit >> 1;
         const uint32_t cls = s_cls[t];
         if (cls == 255u)
             continue;
+        const int row0 = static_cast<int>(unit & 1) + 8 * (lane >> 4);
+        const uint8_t *smb = reinterpret_cast<const uint8_t *>(sm + row0 * PW + q);
+        const int gy = ty0 + row0;
+        uint8_t *out = a.vol + plane * (a.t_first + t) + static_cast<size_t>(gy) * a.W + gx;
         const uint32_t *list = a.lists + a.list_off[t][cls];
         const uint32_t len = a.list_len[t][cls];  // even, >= 2
         uint32_t odd[QPT], even[QPT];
@@ -203,7 +215,6 @@ __device__ __forceinline__ void run_bins(const FastArgs &a, const uint32_t *sm, 
         }
     }
 }
-
 
 // Table build. Recipes and levels are compile-time constants (forced through template arguments),
 // so for every level both passes unroll over the tables of that level and all shared-memory loads
@@ -301,6 +312,7 @@ __global__ void __launch_bounds__(FT_THREADS, 1) se2_fast_kernel(const __grid_co
 {
     extern __shared__ __align__(16) uint32_t sm[];
     __shared__ uint8_t s_cls[MAX_T_PER_LAUNCH];
+    __shared__ uint32_t s_next;
     const int tid = threadIdx.x;
     const int warp = tid >> 5, lane = tid & 31;
     constexpr int NWARPS = FT_THREADS / 32;
@@ -341,6 +353,8 @@ __global__ void __launch_bounds__(FT_THREADS, 1) se2_fast_kernel(const __grid_co
     const uint32_t my_cls = (my_cx > 1 || my_cy > 1) ? 255u : my_cx * 2 + my_cy;
     if (static_cast<uint32_t>(tid) < a.n_t)
         s_cls[tid] = static_cast<uint8_t>(my_cls);
+    if (tid == 0)
+        s_next = 0;
 #pragma unroll
     for (int j = 0; j < ROW_ITERS; ++j)
     {
@@ -355,8 +369,8 @@ __global__ void __launch_bounds__(FT_THREADS, 1) se2_fast_kernel(const __grid_co
     // brick tables, level by level (tables of one level depend only on earlier levels)
     build_all_levels<PW, LIB>(sm, CW, rows, a.n_tables, tid, std::make_integer_sequence<int, MAX_LEVEL + 1>{});
 
-    // output phase: WARPS_PER_BIN warps per bin, NGROUPS bins in flight
-    run_bins<PW>(a, sm, s_cls, warp / WARPS_PER_BIN, warp % WARPS_PER_BIN, lane, tx0, ty0);
+    // output phase: warps fetch (bin, row half) units until none are left
+    run_units<PW>(a, sm, s_cls, &s_next, lane, tx0, ty0);
 }
 
 
@@ -766,8 +780,10 @@ pp_status build_plan(pp_handle h)
     pl->PW = pw;
     pl->copy_words = pl->rows * pl->PW;
     const size_t table_bytes = static_cast<size_t>(4) * pl->copy_words * 4;
-    const int slots = static_cast<int>(std::min<size_t>(MAX_TABLES, (SMEM_LIMIT - 1024) / table_bytes));
-    if (slots < 3)
+    int slots = static_cast<int>(std::min<size_t>(MAX_TABLES, (SMEM_LIMIT - 1024) / table_bytes));
+    if (const char *cap = getenv("PP_SE2_MAX_TABLES"))  // tuning knob for experiments
+        slots = std::max(1, std::min(slots, atoi(cap)));
+    if (slots < 1)
         return PP_OK;
 
     // 3. distinct offset sets per (bin, class)
