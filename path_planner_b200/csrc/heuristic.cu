@@ -36,7 +36,7 @@ __global__ void heur_init_kernel(float *field, size_t n, uint32_t *flags, size_t
         flags[k] = (k == goal_tile) ? 1u : 0u;  // the goal's tile is the only active one in generation 0
 }
 
-// flags layout: [0, nT) generation 0, [nT, 2nT) generation 1, then 4 round counters
+// flags layout: [0, nT) generation 0, [nT, 2nT) generation 1, then 4 round counters + 2 statistics + 2 spare
 __global__ void __launch_bounds__(HT_THREADS) heur_round_kernel(float *__restrict__ field, const uint8_t *__restrict__ cost,
                                                                 const float *__restrict__ travel, uint32_t W, uint32_t H,
                                                                 uint32_t tiles_x, uint32_t tiles_y, uint32_t *flags,
@@ -88,12 +88,14 @@ __global__ void __launch_bounds__(HT_THREADS) heur_round_kernel(float *__restric
     }
     __syncthreads();
 
-    // thread owns cells (row, col0 + 8*k): consecutive lanes -> consecutive columns
-    const int col0 = tid & 7, rowq = tid >> 3;  // 8 columns phase x 32 rows
+    // thread owns cells (rowq + 8*k, col): a warp works on one row at a time, lane = column, so every
+    // shared-memory access of the relaxation is bank-conflict free (row pitch 35 words)
+    const int col = tid & 31, rowq = tid >> 5;
     float init[4];
 #pragma unroll
     for (int k = 0; k < 4; ++k)
-        init[k] = F[rowq + 1][col0 + 8 * k + 1];
+        init[k] = F[rowq + 8 * k + 1][col + 1];
+    uint32_t iters = 0;
 
     int changed;
     do
@@ -102,7 +104,7 @@ __global__ void __launch_bounds__(HT_THREADS) heur_round_kernel(float *__restric
 #pragma unroll
         for (int k = 0; k < 4; ++k)
         {
-            const int r = rowq + 1, c = col0 + 8 * k + 1;
+            const int r = rowq + 8 * k + 1, c = col + 1;
             const float ms = fminf(fminf(F[r - 1][c], F[r + 1][c]), fminf(F[r][c - 1], F[r][c + 1]));
             const float md = fminf(fminf(F[r - 1][c - 1], F[r + 1][c + 1]), fminf(F[r - 1][c + 1], F[r + 1][c - 1]));
             const float cand = fminf(__fadd_rn(ms, WS[r - 1][c - 1]), __fadd_rn(md, WD[r - 1][c - 1]));
@@ -113,14 +115,20 @@ __global__ void __launch_bounds__(HT_THREADS) heur_round_kernel(float *__restric
             }
         }
         changed = __syncthreads_or(local);
+        ++iters;
     } while (changed);
 
     // write back what changed and note which borders moved
     cur[tile] = 0;  // benign if several threads do it; cleared for reuse two rounds later
+    if (tid == 0)
+    {
+        atomicAdd(&counters[4], 1u);      // tile visits
+        atomicAdd(&counters[5], iters);   // in-tile relaxation sweeps
+    }
 #pragma unroll
     for (int k = 0; k < 4; ++k)
     {
-        const int r = rowq, c = col0 + 8 * k;
+        const int r = rowq + 8 * k, c = col;
         const float v = F[r + 1][c + 1];
         if (v < init[k])
         {
@@ -174,7 +182,7 @@ pp_status pp_heuristic_build(pp_handle h, uint32_t goal_x, uint32_t goal_y, floa
     const uint32_t W = h->W, H = h->H;
     const size_t n = static_cast<size_t>(W) * H;
     const uint32_t tiles_x = (W + HT - 1) / HT, tiles_y = (H + HT - 1) / HT, nT = tiles_x * tiles_y;
-    const size_t n_flags = 2 * static_cast<size_t>(nT) + 4;
+    const size_t n_flags = 2 * static_cast<size_t>(nT) + 8;
     PP_CUDA(h, pp_reserve(h->d_field, h->field_cap, n));
     PP_CUDA(h, pp_reserve(h->d_tile_flags, h->tile_flags_cap, n_flags));
     size_t travel_cap = h->d_travel ? 512 : 0;
@@ -216,13 +224,15 @@ pp_status pp_heuristic_build(pp_handle h, uint32_t goal_x, uint32_t goal_y, floa
         }
         PP_CUDA(h, cudaGetLastError());
         // counters[(round) & 3] holds the number of tiles flagged for the round that would run next
-        PP_CUDA(h, cudaMemcpyAsync(h->h_counter, h->d_tile_flags + 2 * static_cast<size_t>(nT), 4 * sizeof(uint32_t),
+        PP_CUDA(h, cudaMemcpyAsync(h->h_counter, h->d_tile_flags + 2 * static_cast<size_t>(nT), 8 * sizeof(uint32_t),
                                    cudaMemcpyDeviceToHost, h->stream));
         PP_CUDA(h, cudaStreamSynchronize(h->stream));
         done = h->h_counter[round & 3] == 0;
         PP_REQUIRE(h, round < max_rounds, PP_ERR_STATE, "pp_heuristic_build: relaxation did not converge");
     }
     h->heur_rounds = round;
+    h->heur_tile_visits = h->h_counter[4];
+    h->heur_sweeps = h->h_counter[5];
     heur_finalize_kernel<<<148 * 8, 256, 0, h->stream>>>(h->d_field, n);
     h->launches++;
     PP_CUDA(h, cudaGetLastError());
@@ -285,7 +295,7 @@ pp_status pp_heuristic_stats(pp_handle h, uint32_t *rounds, uint64_t *tile_visit
 namespace
 {
 constexpr uint32_t NOALLOC_MAX_TILES = (4096 / HT) * (4096 / HT);
-constexpr size_t NOALLOC_FLAG_WORDS = 2 * static_cast<size_t>(NOALLOC_MAX_TILES) + 4;
+constexpr size_t NOALLOC_FLAG_WORDS = 2 * static_cast<size_t>(NOALLOC_MAX_TILES) + 8;
 constexpr size_t NOALLOC_WORDS = NOALLOC_FLAG_WORDS + 512;  // flags + counters, then the 2x256 travel table
 constexpr int NOALLOC_MAX_DEVICES = 64;
 
@@ -347,7 +357,7 @@ extern "C" pp_status pp_heuristic_build_noalloc(const uint8_t *d_cost, uint32_t 
         return pp_fail(nullptr, PP_ERR_CUDA, "pp_heuristic_build_noalloc: travel table upload: %s", cudaGetErrorString(e));
 
     const size_t n = static_cast<size_t>(W) * H;
-    const size_t n_flags = 2 * static_cast<size_t>(nT) + 4;
+    const size_t n_flags = 2 * static_cast<size_t>(nT) + 8;
     const uint32_t goal_index = goal_y * W + goal_x;
     const uint32_t goal_tile = (goal_y / HT) * tiles_x + goal_x / HT;
     // the init kernel clears every flag and counter this call will touch, and seeds the goal

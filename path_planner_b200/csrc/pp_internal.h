@@ -56,7 +56,7 @@ struct pp_ctx
     float *d_travel = nullptr;  // 2 x 256 travel-cost table (straight, diagonal)
     uint32_t *h_counter = nullptr;  // pinned
     uint32_t heur_rounds = 0;
-    uint64_t heur_tile_visits = 0;
+    uint64_t heur_tile_visits = 0, heur_sweeps = 0;
 
     // K3 TEB
     double *d_pts = nullptr;

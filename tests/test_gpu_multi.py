@@ -1,0 +1,67 @@
+"""GPU, 2 devices: heading-sharded build + pp_se2_volume_allgather (NCCL) must give every rank a
+volume byte-identical to the single-GPU one. Skipped on single-GPU boxes."""
+import os
+import socket
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, q):
+    import torch
+    import torch.distributed as dist
+    from path_planner_b200 import capi
+    from path_planner_b200.sharding import bin_range
+    from path_planner_b200.synth import make_costmap
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    try:
+        cost = make_costmap(512, 384, seed=12)
+        h = capi.Handle(rank)
+        h.costmap_upload(cost)
+        h.footprint_from_boundary(0.05, [0.64, 0.46], True)
+        obj = [capi.comm_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(obj, src=0)
+        h.comm_init(obj[0], rank, world)
+        t0, t1 = bin_range(72, rank, world)
+        h.se2_volume_build(72, 0.5, 0.5, 0.0, t0, t1)
+        h.se2_volume_allgather()
+        h.sync()
+        gathered = h.se2_volume_download()
+        h.se2_volume_build(72)  # the whole volume on this GPU alone
+        single = h.se2_volume_download()
+        q.put((rank, bool(np.array_equal(gathered, single)), int(gathered.sum() % 1000003)))
+        h.close()
+    finally:
+        dist.destroy_process_group()
+
+
+def test_two_gpu_allgather_is_byte_identical():
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs (run with gpurun --gpus 2)")
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = sorted(q.get(timeout=300) for _ in procs)
+    for p in procs:
+        p.join(timeout=120)
+        assert p.exitcode == 0
+    assert res[0][1] and res[1][1]
+    assert res[0][2] == res[1][2]
