@@ -202,6 +202,12 @@ def main():
     if N_THETA % world:
         raise SystemExit(f"{N_THETA} heading bins do not split evenly over {world} ranks")
 
+    # Libraries (NCCL prints its version on stdout) must not break the one-JSON-line contract: send
+    # everything that lands on fd 1 to stderr and keep the real stdout for the result line.
+    sys.stdout.flush()
+    result_fd = os.dup(1)
+    os.dup2(2, 1)
+
     import torch
     import torch.distributed as dist
     from path_planner_b200 import capi
@@ -289,6 +295,29 @@ def main():
         gathered = {"value": total_cells / (g_ms * 1e-3), "unit": UNIT, "ms_per_step": g_ms,
                     "collective": "ncclAllGather of heading slabs, in place",
                     "bytes_received_per_gpu": int(W * H * (N_THETA - per))}
+
+    # ---- fused build + peer stores: slabs land in every GPU's volume while they are computed -----
+    if world > 1:
+        h.se2_volume_reserve(N_THETA)
+        handles = [None] * world
+        dist.all_gather_object(handles, h.se2_volume_ipc_export())
+        h.se2_volume_ipc_open(handles, rank, world)
+        h.se2_volume_set_push(True)
+        for _ in range(2):
+            step()
+        h.sync()
+        barrier()
+        p_ms = 0.0
+        for _ in range(args.steps):
+            h.l2_flush()
+            h.timer_start()
+            step()
+            p_ms += h.timer_stop()
+        barrier()
+        p_ms = max_over_ranks(p_ms / args.steps)
+        h.se2_volume_set_push(False)
+        gathered["fused_push"] = {"value": total_cells / (p_ms * 1e-3), "unit": UNIT, "ms_per_step": p_ms,
+                                  "how": "build kernels store every output word to all ranks' volumes over NVLink peer mappings (CUDA IPC); no separate collective"}
 
     # ---- end to end through the C ABI with host buffers (`e2e`) ----------------------------------
     out_pinned = capi.PinnedBuffer(W * H * per)
@@ -386,7 +415,8 @@ def main():
             line["cpu_baseline"]["note"] = f"heuristic/teb baseline failed: {e}"
 
     if rank == 0:
-        print(json.dumps(line), flush=True)
+        sys.stdout.flush()
+        os.write(result_fd, (json.dumps(line) + "\n").encode())
     out_pinned.free()
     pinned_cost.free()
     h.close()

@@ -187,6 +187,22 @@ pp_status pp_comm_unique_id(void *id_out);
 pp_status pp_comm_init(pp_handle h, const void *id, int rank, int world);
 pp_status pp_se2_volume_allgather(pp_handle h);
 
+/* Fused build + exchange (no counterpart in the reference). Instead of building a slab and then
+ * gathering, the build kernels store every output word into the volume of EVERY rank over
+ * NVLink/NVSwitch peer mappings, so the slabs arrive while they are being computed and no separate
+ * collective runs. Set-up, once per handle: every rank calls pp_se2_volume_reserve (allocates the
+ * full-size volume; later builds of the same size do not move it) and pp_se2_volume_ipc_export,
+ * the 64-byte handles are exchanged by any means, and every rank calls pp_se2_volume_ipc_open with
+ * all of them (indexed by rank). pp_se2_volume_set_push(h, 1) then makes pp_se2_volume_build /
+ * _refresh write to all mapped volumes. A rank's data is complete on every peer once that rank's
+ * stream has been synchronised; a barrier across ranks after that makes the whole volume valid
+ * everywhere. At most 8 ranks. */
+#define PP_IPC_HANDLE_BYTES 64
+pp_status pp_se2_volume_reserve(pp_handle h, uint32_t n_theta);
+pp_status pp_se2_volume_ipc_export(pp_handle h, void *handle_out);
+pp_status pp_se2_volume_ipc_open(pp_handle h, const void *handles, int rank, int world);
+pp_status pp_se2_volume_set_push(pp_handle h, int enable);
+
 #ifdef __cplusplus
 }
 #endif

@@ -19,7 +19,8 @@ SYMBOLS = [
     "pp_footprint_from_boundary", "pp_footprint_set", "pp_footprint_get", "pp_se2_volume_build",
     "pp_se2_volume_refresh", "pp_se2_volume_download", "pp_se2_volume_ptr", "pp_se2_volume_set_mode",
     "pp_se2_volume_stats", "pp_footprint_cost_batch", "pp_heuristic_build", "pp_heuristic_ptr", "pp_heuristic_stats", "pp_heuristic_build_noalloc",
-    "pp_obstacles_extract", "pp_radius_topk", "pp_comm_unique_id", "pp_comm_init", "pp_se2_volume_allgather",
+    "pp_obstacles_extract", "pp_radius_topk", "pp_comm_unique_id", "pp_comm_init", "pp_se2_volume_allgather", "pp_se2_volume_reserve",
+    "pp_se2_volume_ipc_export", "pp_se2_volume_ipc_open", "pp_se2_volume_set_push",
 ]
 
 _vp = C.c_void_p
@@ -76,6 +77,10 @@ def load():
     L.pp_comm_unique_id.argtypes = [_vp]
     L.pp_comm_init.argtypes = [_vp, _vp, C.c_int, C.c_int]
     L.pp_se2_volume_allgather.argtypes = [_vp]
+    L.pp_se2_volume_reserve.argtypes = [_vp, _u32]
+    L.pp_se2_volume_ipc_export.argtypes = [_vp, _vp]
+    L.pp_se2_volume_ipc_open.argtypes = [_vp, _vp, C.c_int, C.c_int]
+    L.pp_se2_volume_set_push.argtypes = [_vp, C.c_int]
     _lib = L
     return L
 
@@ -273,6 +278,23 @@ class Handle:
 
     def se2_volume_allgather(self):
         self._ck(self.L.pp_se2_volume_allgather(self.h))
+
+    def se2_volume_reserve(self, n_theta):
+        self.n_theta = n_theta
+        self._ck(self.L.pp_se2_volume_reserve(self.h, n_theta))
+
+    def se2_volume_ipc_export(self):
+        buf = C.create_string_buffer(64)
+        self._ck(self.L.pp_se2_volume_ipc_export(self.h, buf))
+        return buf.raw
+
+    def se2_volume_ipc_open(self, handles, rank, world):
+        blob = b"".join(handles)
+        assert len(blob) == 64 * world
+        self._ck(self.L.pp_se2_volume_ipc_open(self.h, C.create_string_buffer(blob, len(blob)), rank, world))
+
+    def se2_volume_set_push(self, enable):
+        self._ck(self.L.pp_se2_volume_set_push(self.h, int(enable)))
 
 
 def heuristic_build_noalloc(d_cost_ptr, W, H, goal_x, goal_y, cost_penalty, d_field_ptr, stream=None):

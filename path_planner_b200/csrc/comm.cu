@@ -108,8 +108,89 @@ pp_status pp_se2_volume_allgather(pp_handle h)
 
 }  // extern "C"
 
+
+int pp_volume_targets(pp_handle h, uint8_t **out)
+{
+    int n = 0;
+    out[n++] = h->d_vol;
+    if (h->push)
+        for (int r = 0; r < h->n_peer; ++r)
+            if (h->peer_vol[r] && h->peer_vol[r] != h->d_vol)
+                out[n++] = h->peer_vol[r];
+    return n;
+}
+
+extern "C" {
+
+pp_status pp_se2_volume_reserve(pp_handle h, uint32_t n_theta)
+{
+    if (!h)
+        return PP_ERR_INVALID;
+    PP_REQUIRE(h, h->d_cost, PP_ERR_STATE, "pp_se2_volume_reserve: upload a costmap first (its size fixes the volume size)");
+    PP_REQUIRE(h, n_theta > 0 && n_theta <= 4096, PP_ERR_RANGE, "n_theta %u outside 1..4096", n_theta);
+    PP_CUDA(h, cudaSetDevice(h->device));
+    PP_CUDA(h, pp_reserve(h->d_vol, h->vol_cap, static_cast<size_t>(h->W) * h->H * n_theta));
+    return PP_OK;
+}
+
+pp_status pp_se2_volume_ipc_export(pp_handle h, void *handle_out)
+{
+    if (!h || !handle_out)
+        return PP_ERR_INVALID;
+    PP_REQUIRE(h, h->d_vol, PP_ERR_STATE, "pp_se2_volume_ipc_export: call pp_se2_volume_reserve first");
+    static_assert(sizeof(cudaIpcMemHandle_t) == PP_IPC_HANDLE_BYTES, "IPC handle size");
+    PP_CUDA(h, cudaSetDevice(h->device));
+    cudaIpcMemHandle_t mh;
+    PP_CUDA(h, cudaIpcGetMemHandle(&mh, h->d_vol));
+    std::memcpy(handle_out, &mh, sizeof(mh));
+    return PP_OK;
+}
+
+pp_status pp_se2_volume_ipc_open(pp_handle h, const void *handles, int rank, int world)
+{
+    if (!h || !handles)
+        return PP_ERR_INVALID;
+    PP_REQUIRE(h, world >= 1 && world <= 8 && rank >= 0 && rank < world, PP_ERR_RANGE, "pp_se2_volume_ipc_open: rank %d of %d (at most 8)", rank, world);
+    PP_REQUIRE(h, h->d_vol, PP_ERR_STATE, "pp_se2_volume_ipc_open: call pp_se2_volume_reserve first");
+    PP_CUDA(h, cudaSetDevice(h->device));
+    for (int r = 0; r < world; ++r)
+    {
+        if (r == rank)
+        {
+            h->peer_vol[r] = h->d_vol;
+            continue;
+        }
+        cudaIpcMemHandle_t mh;
+        std::memcpy(&mh, static_cast<const char *>(handles) + static_cast<size_t>(r) * PP_IPC_HANDLE_BYTES, sizeof(mh));
+        void *p = nullptr;
+        cudaError_t e = cudaIpcOpenMemHandle(&p, mh, cudaIpcMemLazyEnablePeerAccess);
+        PP_REQUIRE(h, e == cudaSuccess, PP_ERR_COMM, "cudaIpcOpenMemHandle(rank %d): %s", r, cudaGetErrorString(e));
+        h->peer_vol[r] = static_cast<uint8_t *>(p);
+    }
+    h->n_peer = world;
+    h->rank = rank;
+    h->world = world;
+    return PP_OK;
+}
+
+pp_status pp_se2_volume_set_push(pp_handle h, int enable)
+{
+    if (!h)
+        return PP_ERR_INVALID;
+    PP_REQUIRE(h, !enable || h->n_peer > 0, PP_ERR_STATE, "pp_se2_volume_set_push: no peer volumes mapped (pp_se2_volume_ipc_open)");
+    h->push = enable != 0;
+    return PP_OK;
+}
+
+}  // extern "C"
+
 void pp_comm_destroy(pp_handle h)
 {
+    for (int r = 0; r < h->n_peer; ++r)
+        if (h->peer_vol[r] && h->peer_vol[r] != h->d_vol)
+            cudaIpcCloseMemHandle(h->peer_vol[r]);
+    h->n_peer = 0;
+    h->push = false;
     if (!h->comm)
         return;
     std::string why;

@@ -72,6 +72,9 @@ struct pp_ctx
     size_t topk_cap = 0, topk_q_cap = 0;
 
     // multi-GPU
+    uint8_t *peer_vol[8] = {};  // peer_vol[r] = rank r's volume mapped here (own volume at [rank]); null if not opened
+    int n_peer = 0;             // world size of the mapping
+    bool push = false;          // builds store to every mapped volume
     void *comm = nullptr;  // ncclComm_t
     int rank = 0, world = 1;
 };
@@ -118,3 +121,5 @@ inline cudaError_t pp_reserve(T *&ptr, size_t &cap, size_t need)
 pp_status pp_se2_launch(pp_handle h, uint32_t x0, uint32_t y0, uint32_t x1, uint32_t y1);
 void pp_se2_plan_free(pp_handle h);
 void pp_comm_destroy(pp_handle h);
+// fills up to 8 destination volumes for a build (own first); returns how many
+int pp_volume_targets(pp_handle h, uint8_t **out);

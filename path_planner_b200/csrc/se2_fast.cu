@@ -89,7 +89,9 @@ __host__ __device__ constexpr bool level_in_use(int lib, int lvl)
 struct FastArgs
 {
     const uint8_t *cost;
-    uint8_t *vol;
+    uint8_t *vol;             // own volume
+    long long peer_delta[7];  // byte distance from the own volume to each mapped peer volume
+    int n_peers;              // fused exchange: every output word is also stored to these
     const uint8_t *xclass;  // [n_theta][tiles_x]: 0/1 = column range class, 255 = not uniform
     const uint8_t *yclass;  // [n_theta][tiles_y]
     uint32_t W, H, tiles_x, tiles_y, tile_x0, tile_y0;
@@ -211,7 +213,13 @@ __device__ __forceinline__ void run_units(const FastArgs &a, const uint32_t *sm,
 #pragma unroll
             for (int j = 0; j < QPT; ++j)
                 if (gy + quad_row(j) < H)
-                    *reinterpret_cast<uint32_t *>(out + quad_row(j) * rs) = __byte_perm(even[j], odd[j], 0x7351);
+                {
+                    const uint32_t word = __byte_perm(even[j], odd[j], 0x7351);
+                    uint8_t *dst = out + quad_row(j) * rs;
+                    *reinterpret_cast<uint32_t *>(dst) = word;
+                    for (int p = 0; p < a.n_peers; ++p)  // peer volumes over NVLink
+                        *reinterpret_cast<uint32_t *>(dst + a.peer_delta[p]) = word;
+                }
         }
     }
 }
@@ -917,6 +925,13 @@ pp_status pp_se2_launch_fast(pp_handle h, uint32_t x0, uint32_t y0, uint32_t x1,
     static thread_local FastArgs args;  // ~28 KB: keep it off the stack
     args.cost = h->d_cost;
     args.vol = h->d_vol;
+    {
+        uint8_t *targets[8];
+        const int n = pp_volume_targets(h, targets);
+        args.n_peers = n - 1;
+        for (int p = 1; p < n; ++p)
+            args.peer_delta[p - 1] = static_cast<long long>(reinterpret_cast<uintptr_t>(targets[p]) - reinterpret_cast<uintptr_t>(targets[0]));
+    }
     args.xclass = pl->d_xclass;
     args.yclass = pl->d_yclass;
     args.W = h->W;

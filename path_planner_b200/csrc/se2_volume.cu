@@ -27,7 +27,8 @@ constexpr int GT_PCHUNK = 256;  // footprint points tabulated per pass
 struct GenericArgs
 {
     const uint8_t *cost;
-    uint8_t *vol;
+    uint8_t *vol[8];  // destination volumes: own first, then mapped peers (fused exchange)
+    int n_vol;
     const float2 *trig;
     const int32_t *fp;
     uint32_t W, H, P;
@@ -138,7 +139,11 @@ __global__ void __launch_bounds__(GT_THREADS) se2_generic_kernel(GenericArgs a)
             {
                 const int gy = ty0 + yg + k * (GT_THREADS / GT_W);
                 if (gy < static_cast<int>(a.y1))
-                    a.vol[plane * t + static_cast<size_t>(gy) * a.W + gx] = static_cast<uint8_t>(acc[k]);
+                {
+                    const size_t at = plane * t + static_cast<size_t>(gy) * a.W + gx;
+                    for (int v = 0; v < a.n_vol; ++v)
+                        a.vol[v][at] = static_cast<uint8_t>(acc[k]);
+                }
             }
         }
     }
@@ -158,7 +163,7 @@ static pp_status launch_generic(pp_handle h, uint32_t x0, uint32_t y0, uint32_t 
 {
     GenericArgs a;
     a.cost = h->d_cost;
-    a.vol = h->d_vol;
+    a.n_vol = pp_volume_targets(h, a.vol);
     a.trig = h->d_trig;
     a.fp = h->d_fp;
     a.W = h->W;

@@ -1,5 +1,6 @@
-"""GPU, 2 devices: heading-sharded build + pp_se2_volume_allgather (NCCL) must give every rank a
-volume byte-identical to the single-GPU one. Skipped on single-GPU boxes."""
+"""GPU, 2 devices: heading-sharded build + pp_se2_volume_allgather (NCCL), and the fused build that
+stores into every rank's volume over peer mappings, must both give every rank a volume
+byte-identical to the single-GPU one. Skipped on single-GPU boxes."""
 import os
 import socket
 
@@ -40,9 +41,26 @@ def _worker(rank, world, port, q):
         h.se2_volume_allgather()
         h.sync()
         gathered = h.se2_volume_download()
+        # fused build + exchange: every rank's kernels store into every rank's volume (CUDA IPC peers)
+        h2 = capi.Handle(rank)
+        h2.costmap_upload(cost)
+        h2.footprint_from_boundary(0.05, [0.64, 0.46], True)
+        h2.se2_volume_reserve(72)
+        handles = [None] * world
+        dist.all_gather_object(handles, h2.se2_volume_ipc_export())
+        h2.se2_volume_ipc_open(handles, rank, world)
+        h2.se2_volume_set_push(True)
+        h2.se2_volume_build(72, 0.5, 0.5, 0.0, t0, t1)
+        h2.sync()
+        dist.barrier()          # every rank's slab has landed everywhere
+        pushed = h2.se2_volume_download()
+        dist.barrier()          # nobody tears its volume down while a peer may still read/write it
         h.se2_volume_build(72)  # the whole volume on this GPU alone
         single = h.se2_volume_download()
-        q.put((rank, bool(np.array_equal(gathered, single)), int(gathered.sum() % 1000003)))
+        q.put((rank, bool(np.array_equal(gathered, single)) and bool(np.array_equal(pushed, single)),
+               int(gathered.sum() % 1000003)))
+        dist.barrier()
+        h2.close()
         h.close()
     finally:
         dist.destroy_process_group()
