@@ -315,6 +315,29 @@ def main():
             p_ms += h.timer_stop()
         barrier()
         p_ms = max_over_ranks(p_ms / args.steps)
+        # spatial sharding: every rank builds ALL bins of its row band (per-tile table build paid once
+        # per tile in the whole job instead of once per rank) and pushes them to every volume
+        from path_planner_b200.sharding import row_band
+        y0, y1 = row_band(H, rank, world)
+        h.se2_volume_set_rows(y0, y1)
+        for push_on, key in ((False, "row_sharded"), (True, "row_sharded_fused_push")):
+            h.se2_volume_set_push(push_on)
+            for _ in range(2):
+                h.se2_volume_build(N_THETA, 0.5, 0.5, 0.0, 0, N_THETA)
+            h.sync()
+            barrier()
+            r_ms = 0.0
+            for _ in range(args.steps):
+                h.l2_flush()
+                h.timer_start()
+                h.se2_volume_build(N_THETA, 0.5, 0.5, 0.0, 0, N_THETA)
+                r_ms += h.timer_stop()
+            barrier()
+            r_ms = max_over_ranks(r_ms / args.steps)
+            gathered[key] = {"value": total_cells / (r_ms * 1e-3), "unit": UNIT, "ms_per_step": r_ms}
+        gathered["row_sharded"]["how"] = "rank g builds all 72 bins of map rows band g (no exchange); results identical"
+        gathered["row_sharded_fused_push"]["how"] = "same, every output word also stored to all other ranks' volumes"
+        h.se2_volume_set_rows(0, 0)
         h.se2_volume_set_push(False)
         gathered["fused_push"] = {"value": total_cells / (p_ms * 1e-3), "unit": UNIT, "ms_per_step": p_ms,
                                   "how": "build kernels store every output word to all ranks' volumes over NVLink peer mappings (CUDA IPC); no separate collective"}

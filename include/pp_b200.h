@@ -202,6 +202,13 @@ pp_status pp_se2_volume_reserve(pp_handle h, uint32_t n_theta);
 pp_status pp_se2_volume_ipc_export(pp_handle h, void *handle_out);
 pp_status pp_se2_volume_ipc_open(pp_handle h, const void *handles, int rank, int world);
 pp_status pp_se2_volume_set_push(pp_handle h, int enable);
+/* Row-band sharding (no counterpart in the reference): restrict pp_se2_volume_build to the map rows
+ * [y_begin, y_end) (all columns, the bins given to the build). Whole 32-row tiles that overlap the
+ * band are computed, so neighbouring bands may both write a few identical rows. y_end == 0 restores
+ * the whole map. Together with pp_se2_volume_set_push this shards the volume spatially across GPUs:
+ * every rank pays the per-tile table build only for its own band, which scales linearly, whereas
+ * heading-bin sharding repeats that cost on every rank. */
+pp_status pp_se2_volume_set_rows(pp_handle h, uint32_t y_begin, uint32_t y_end);
 
 #ifdef __cplusplus
 }

@@ -20,7 +20,7 @@ SYMBOLS = [
     "pp_se2_volume_refresh", "pp_se2_volume_download", "pp_se2_volume_ptr", "pp_se2_volume_set_mode",
     "pp_se2_volume_stats", "pp_footprint_cost_batch", "pp_heuristic_build", "pp_heuristic_ptr", "pp_heuristic_stats", "pp_heuristic_build_noalloc",
     "pp_obstacles_extract", "pp_radius_topk", "pp_comm_unique_id", "pp_comm_init", "pp_se2_volume_allgather", "pp_se2_volume_reserve",
-    "pp_se2_volume_ipc_export", "pp_se2_volume_ipc_open", "pp_se2_volume_set_push",
+    "pp_se2_volume_ipc_export", "pp_se2_volume_ipc_open", "pp_se2_volume_set_push", "pp_se2_volume_set_rows",
 ]
 
 _vp = C.c_void_p
@@ -81,6 +81,7 @@ def load():
     L.pp_se2_volume_ipc_export.argtypes = [_vp, _vp]
     L.pp_se2_volume_ipc_open.argtypes = [_vp, _vp, C.c_int, C.c_int]
     L.pp_se2_volume_set_push.argtypes = [_vp, C.c_int]
+    L.pp_se2_volume_set_rows.argtypes = [_vp, _u32, _u32]
     _lib = L
     return L
 
@@ -295,6 +296,9 @@ class Handle:
 
     def se2_volume_set_push(self, enable):
         self._ck(self.L.pp_se2_volume_set_push(self.h, int(enable)))
+
+    def se2_volume_set_rows(self, y_begin, y_end):
+        self._ck(self.L.pp_se2_volume_set_rows(self.h, y_begin, y_end))
 
 
 def heuristic_build_noalloc(d_cost_ptr, W, H, goal_x, goal_y, cost_penalty, d_field_ptr, stream=None):

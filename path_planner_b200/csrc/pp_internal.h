@@ -75,6 +75,7 @@ struct pp_ctx
     uint8_t *peer_vol[8] = {};  // peer_vol[r] = rank r's volume mapped here (own volume at [rank]); null if not opened
     int n_peer = 0;             // world size of the mapping
     bool push = false;          // builds store to every mapped volume
+    uint32_t band_y0 = 0, band_y1 = 0;  // row band of pp_se2_volume_build (0,0 = whole map)
     void *comm = nullptr;  // ncclComm_t
     int rank = 0, world = 1;
 };

@@ -297,11 +297,22 @@ pp_status pp_se2_volume_build(pp_handle h, uint32_t n_theta, float ox, float oy,
     PP_CUDA(h, cudaStreamSynchronize(h->stream));  // `trig` is pageable and about to go out of scope
     h->host_trig.swap(trig);
 
-    pp_status s = pp_se2_launch(h, 0, 0, h->W, h->H);
+    const bool banded = h->band_y1 > h->band_y0;
+    pp_status s = pp_se2_launch(h, 0, banded ? std::min(h->band_y0, h->H) : 0, h->W, banded ? std::min(h->band_y1, h->H) : h->H);
     if (s != PP_OK)
         return s;
     h->vol_valid = true;
     h->dirty = false;
+    return PP_OK;
+}
+
+pp_status pp_se2_volume_set_rows(pp_handle h, uint32_t y_begin, uint32_t y_end)
+{
+    if (!h)
+        return PP_ERR_INVALID;
+    PP_REQUIRE(h, y_end == 0 || y_begin < y_end, PP_ERR_INVALID, "pp_se2_volume_set_rows: empty band [%u,%u)", y_begin, y_end);
+    h->band_y0 = y_end ? y_begin : 0;
+    h->band_y1 = y_end;
     return PP_OK;
 }
 

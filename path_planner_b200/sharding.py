@@ -33,3 +33,14 @@ def gather_slabs(local_slab, dist):
     out = torch.empty((world * slab.shape[0],) + tuple(slab.shape[1:]), dtype=slab.dtype)
     dist.all_gather_into_tensor(out, slab)
     return out
+
+
+def row_band(height, rank, world, tile_rows=32):
+    """Half-open range of map rows of `rank` for spatial sharding: bands are whole 32-row tiles
+    (the kernel's tile height), as equal as the tile count allows; together they cover [0, height)."""
+    if world < 1 or not 0 <= rank < world:
+        raise ValueError(f"rank {rank} of {world}")
+    tiles = (height + tile_rows - 1) // tile_rows
+    lo = (tiles * rank) // world * tile_rows
+    hi = (tiles * (rank + 1)) // world * tile_rows
+    return min(lo, height), min(hi, height)

@@ -54,10 +54,24 @@ def _worker(rank, world, port, q):
         h2.sync()
         dist.barrier()          # every rank's slab has landed everywhere
         pushed = h2.se2_volume_download()
-        dist.barrier()          # nobody tears its volume down while a peer may still read/write it
+        dist.barrier()          # nobody overwrites its volume while a peer may still read it
+        # spatial sharding: every rank builds all 72 bins of its row band and pushes them to everyone
+        from path_planner_b200.sharding import row_band
+        y0, y1 = row_band(cost.shape[0], rank, world)
+        h2.se2_volume_set_rows(y0, y1)
+        h2.costmap_upload(cost[::-1].copy())      # a different map, so stale data cannot pass
+        h2.se2_volume_build(72)
+        h2.sync()
+        dist.barrier()
+        banded = h2.se2_volume_download()
+        dist.barrier()
+        h.costmap_upload(cost[::-1].copy())
+        h.se2_volume_build(72)
+        banded_ok = bool(np.array_equal(banded, h.se2_volume_download()))
+        h.costmap_upload(cost)
         h.se2_volume_build(72)  # the whole volume on this GPU alone
         single = h.se2_volume_download()
-        q.put((rank, bool(np.array_equal(gathered, single)) and bool(np.array_equal(pushed, single)),
+        q.put((rank, bool(np.array_equal(gathered, single)) and bool(np.array_equal(pushed, single)) and banded_ok,
                int(gathered.sum() % 1000003)))
         dist.barrier()
         h2.close()

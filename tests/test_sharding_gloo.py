@@ -23,6 +23,16 @@ def test_bin_ranges_cover_exactly():
         bin_range(72, 2, 2)
 
 
+def test_row_bands_cover_exactly():
+    from path_planner_b200.sharding import row_band
+    for H in (1, 31, 32, 33, 400, 4096, 8192):
+        for world in (1, 2, 4, 8):
+            r = [row_band(H, g, world) for g in range(world)]
+            assert r[0][0] == 0 and r[-1][1] == H
+            assert all(r[i][1] == r[i + 1][0] for i in range(world - 1))
+            assert all(a % 32 == 0 for a, _ in r)
+
+
 def _free_port():
     s = socket.socket()
     s.bind(("127.0.0.1", 0))
