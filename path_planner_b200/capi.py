@@ -10,7 +10,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libpp_b200.so")
+LIB_PATH = os.environ.get("PP_B200_LIB", os.path.join(_HERE, "libpp_b200.so"))  # override: A/B runs of two builds
 
 # every symbol include/pp_b200.h declares
 SYMBOLS = [

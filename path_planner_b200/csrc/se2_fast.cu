@@ -182,31 +182,43 @@ __device__ __forceinline__ void run_units(const FastArgs &a, const uint32_t *sm,
         const int gy = ty0 + row0;
         uint8_t *out = a.vol + plane * (a.t_first + t) + static_cast<size_t>(gy) * a.W + gx;
         const uint32_t *list = a.lists + a.list_off[t][cls];
-        const uint32_t len = a.list_len[t][cls];  // even, >= 2
+        const uint32_t n_samples = a.list_len[t][cls];  // >= 1; the stored list is padded to an even count
+        const uint32_t len = n_samples & ~1u;            // samples consumed in pairs
         uint32_t odd[QPT], even[QPT];
 #pragma unroll
         for (int j = 0; j < QPT; ++j)
             odd[j] = even[j] = 0;
         uint32_t ua[QPT], va[QPT], ub[QPT], vb[QPT];
-        load_pair<PW>(smb, list[0], list[1], ua, va);
-        uint32_t i = 2;
+        if (len)
+        {
+            load_pair<PW>(smb, list[0], list[1], ua, va);
+            uint32_t i = 2;
 #pragma unroll 1
-        for (; i + 2 < len; i += 4)
-        {
-            load_pair<PW>(smb, list[i], list[i + 1], ub, vb);
-            accumulate(odd, even, ua, va);
-            load_pair<PW>(smb, list[i + 2], list[i + 3], ua, va);
-            accumulate(odd, even, ub, vb);
+            for (; i + 2 < len; i += 4)
+            {
+                load_pair<PW>(smb, list[i], list[i + 1], ub, vb);
+                accumulate(odd, even, ua, va);
+                load_pair<PW>(smb, list[i + 2], list[i + 3], ua, va);
+                accumulate(odd, even, ub, vb);
+            }
+            if (i < len)
+            {
+                load_pair<PW>(smb, list[i], list[i + 1], ub, vb);
+                accumulate(odd, even, ua, va);
+                accumulate(odd, even, ub, vb);
+            }
+            else
+            {
+                accumulate(odd, even, ua, va);
+            }
         }
-        if (i < len)
+        if (n_samples & 1u)  // the last sample of an odd list: one load, used for both operands
         {
-            load_pair<PW>(smb, list[i], list[i + 1], ub, vb);
-            accumulate(odd, even, ua, va);
-            accumulate(odd, even, ub, vb);
-        }
-        else
-        {
-            accumulate(odd, even, ua, va);
+            const uint32_t *p1 = reinterpret_cast<const uint32_t *>(smb + list[n_samples - 1]);
+#pragma unroll
+            for (int j = 0; j < QPT; ++j)
+                ua[j] = p1[quad_row(j) * PW];
+            accumulate(odd, even, ua, ua);
         }
         if (in_x)
         {
@@ -844,14 +856,12 @@ pp_status build_plan(pp_handle h)
                 if (it == memo.end())
                 {
                     std::vector<uint32_t> words;
-                    for (const Placement &p : cover_set(S, bricks, R, 60000))
+                    for (const Placement &p : cover_set(S, bricks, R, 400000))
                     {
                         const int ax = R + 4 + p.ox, ay = R + p.oy;  // >= 0; +4: the margin word
                         const uint32_t word = static_cast<uint32_t>((p.brick * 4 + (ax & 3)) * pl->copy_words + ay * pl->PW + (ax >> 2));
                         words.push_back(word * 4);
                     }
-                    if (words.size() & 1)
-                        words.push_back(words.back());  // samples are consumed in pairs
                     it = memo.emplace(S, words).first;
                 }
                 pl->list_off[t * 4 + cx * 2 + cy] = static_cast<uint32_t>(pl->lists.size());
