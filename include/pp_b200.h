@@ -146,8 +146,8 @@ pp_status pp_heuristic_stats(pp_handle h, uint32_t *rounds, uint64_t *tile_visit
  * processes that forbid allocation after start-up): it needs no handle and calls no cudaMalloc,
  * cudaFree or other allocating routine. The caller passes the costmap and the output field as
  * DEVICE pointers (W*H bytes in, W*H floats out) and the stream to run on (a cudaStream_t, or
- * NULL for the default stream); the kernel's scratch (per-tile activity flags, travel-cost table)
- * lives in a fixed ~130 KB array inside the library image, held by every GPU that loads the
+ * NULL for the default stream); the kernel's scratch (per-tile keys and work lists, travel-cost table)
+ * lives in a fixed ~260 KB array inside the library image, held by every GPU that loads the
  * library until the process exits.
  *   limit    ceil(W/32) * ceil(H/32) <= 16384 tiles (e.g. 4096 x 4096); larger maps are refused
  *            with PP_ERR_RANGE and a message on stderr

@@ -14,7 +14,9 @@
 // come from a 2x256 table evaluated on the host with the reference's exact float expression.
 #include "pp_internal.h"
 
+#include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <limits>
 #include <vector>
 
@@ -23,45 +25,91 @@ namespace
 constexpr int HT = 32;            // tile edge
 constexpr int HT_THREADS = 256;   // 4 cells per thread
 constexpr int HT_PITCH = HT + 2 + 1;
-constexpr int ROUNDS_PER_CHECK = 8;
+constexpr int ROUNDS_PER_CHECK = 16;
+constexpr uint32_t ROUND_GRID = 148 * 8;  // CTAs per relaxation round: they walk the round's work list
+
+constexpr uint32_t INACTIVE = 0xFFFFFFFFu;  // tile key: bit pattern of the smallest pending value, or this
+constexpr int N_COUNTERS = 16;              // [0..3] tiles flagged per round, [4] visits, [5] sweeps, [8..11] min key per round
 
 __global__ void heur_init_kernel(float *field, size_t n, uint32_t *flags, size_t n_flags, uint32_t goal_index,
                                  uint32_t goal_tile)
 {
     const size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x;
     const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+    const uint32_t goal_key = __float_as_uint(0.00001f);
     for (size_t k = i; k < n; k += stride)
         field[k] = (k == goal_index) ? 0.00001f : __int_as_float(0x7f800000);
+    // layout: [0,nT) keys gen 0 | [nT,2nT) keys gen 1 | [2nT,3nT) list gen 0 | [3nT,4nT) list gen 1 | counters
+    const size_t counters_at = n_flags - N_COUNTERS;
+    const size_t nT = counters_at / 4;
     for (size_t k = i; k < n_flags; k += stride)
-        flags[k] = (k == goal_tile) ? 1u : 0u;  // the goal's tile is the only active one in generation 0
+    {
+        uint32_t v = INACTIVE;                       // tile keys of both generations
+        if (k == goal_tile)
+            v = goal_key;                            // the goal's tile is the only active one in generation 0
+        else if (k >= 2 * nT && k < counters_at)
+            v = (k == 2 * nT) ? goal_tile : 0u;      // work lists; generation 0 holds the goal's tile
+        else if (k >= counters_at)
+        {
+            const size_t c = k - counters_at;
+            v = (c >= 8 && c < 12) ? (c == 8 ? goal_key : INACTIVE) : (c == 0 ? 1u : 0u);
+        }
+        flags[k] = v;
+    }
 }
 
-// flags layout: [0, nT) generation 0, [nT, 2nT) generation 1, then 4 round counters + 2 statistics + 2 spare
+// flags layout: [0, nT) tile keys of generation 0, [nT, 2nT) generation 1, then N_COUNTERS words.
+// Scheduling: a tile's key is the smallest value that reached its border since it last ran. A
+// round only runs the tiles whose key is within `delta` of the smallest key of the round (a
+// delta-stepping bucket over tiles); the others carry their key over to the next round. This keeps
+// tiles far behind the wavefront from being re-relaxed every time a slightly better value trickles
+// in, without changing the fixed point that is reached.
 __global__ void __launch_bounds__(HT_THREADS) heur_round_kernel(float *__restrict__ field, const uint8_t *__restrict__ cost,
                                                                 const float *__restrict__ travel, uint32_t W, uint32_t H,
                                                                 uint32_t tiles_x, uint32_t tiles_y, uint32_t *flags,
-                                                                uint32_t round)
+                                                                uint32_t round, float delta)
 {
     const uint32_t nT = tiles_x * tiles_y;
     uint32_t *cur = flags + (round & 1) * nT;
     uint32_t *nxt = flags + ((round + 1) & 1) * nT;
-    uint32_t *counters = flags + 2 * nT;
-    const uint32_t tile = blockIdx.x;
-    if (tile == 0 && threadIdx.x == 0)
-        counters[(round + 2) & 3] = 0;  // will count the tiles flagged during round+1
-    if (cur[tile] == 0)
-        return;
+    const uint32_t *list_cur = flags + (2 + (round & 1)) * nT;
+    uint32_t *list_nxt = flags + (2 + ((round + 1) & 1)) * nT;
+    uint32_t *counters = flags + 4 * nT;
+    if (blockIdx.x == 0 && threadIdx.x == 0)
+    {
+        counters[(round + 2) & 3] = 0;               // will count the tiles listed during round+1
+        counters[8 + ((round + 2) & 3)] = INACTIVE;  // and hold their smallest key
+    }
+    const uint32_t n_active = counters[round & 3];
+    const float threshold = __uint_as_float(counters[8 + (round & 3)]) + delta;
     __shared__ float F[HT + 2][HT_PITCH];
     __shared__ float WS[HT][HT];
     __shared__ float WD[HT][HT];
-    __shared__ uint32_t edge_changed[8];
+    __shared__ uint32_t edge_min[8];  // smallest new value on each border / corner (bit pattern), INACTIVE if unchanged
+    for (uint32_t entry = blockIdx.x; entry < n_active; entry += gridDim.x)
+    {
+    const uint32_t tile = list_cur[entry];
+    const uint32_t key = cur[tile];
+    __syncthreads();  // every thread has read the key (and is done with the previous tile's shared memory)
+    if (__uint_as_float(key) > threshold)
+    {
+        // not in this round's bucket: carry the key over
+        if (threadIdx.x == 0)
+        {
+            cur[tile] = INACTIVE;
+            if (atomicMin(&nxt[tile], key) == INACTIVE)
+                list_nxt[atomicAdd(&counters[(round + 1) & 3], 1u)] = tile;
+            atomicMin(&counters[8 + ((round + 1) & 3)], key);
+        }
+        continue;
+    }
 
     const uint32_t tx = tile % tiles_x, ty = tile / tiles_x;
     const int x0 = static_cast<int>(tx * HT), y0 = static_cast<int>(ty * HT);
     const int tid = threadIdx.x;
     const float INF = __int_as_float(0x7f800000);
     if (tid < 8)
-        edge_changed[tid] = 0;
+        edge_min[tid] = INACTIVE;
     for (int i = tid; i < (HT + 2) * (HT + 2); i += HT_THREADS)
     {
         const int r = i / (HT + 2), c = i - r * (HT + 2);
@@ -119,7 +167,8 @@ __global__ void __launch_bounds__(HT_THREADS) heur_round_kernel(float *__restric
     } while (changed);
 
     // write back what changed and note which borders moved
-    cur[tile] = 0;  // benign if several threads do it; cleared for reuse two rounds later
+    if (tid == 0)
+        cur[tile] = INACTIVE;  // off the current generation; neighbours may list it again for the next round
     if (tid == 0)
     {
         atomicAdd(&counters[4], 1u);      // tile visits
@@ -135,18 +184,19 @@ __global__ void __launch_bounds__(HT_THREADS) heur_round_kernel(float *__restric
             const int gy = y0 + r, gx = x0 + c;
             if (gy < static_cast<int>(H) && gx < static_cast<int>(W))
                 field[static_cast<size_t>(gy) * W + gx] = v;
-            if (r == 0) edge_changed[0] = 1;                       // N
-            if (r == HT - 1) edge_changed[1] = 1;                  // S
-            if (c == 0) edge_changed[2] = 1;                       // W
-            if (c == HT - 1) edge_changed[3] = 1;                  // E
-            if (r == 0 && c == 0) edge_changed[4] = 1;             // NW
-            if (r == 0 && c == HT - 1) edge_changed[5] = 1;        // NE
-            if (r == HT - 1 && c == 0) edge_changed[6] = 1;        // SW
-            if (r == HT - 1 && c == HT - 1) edge_changed[7] = 1;   // SE
+            const uint32_t vb = __float_as_uint(v);
+            if (r == 0) atomicMin(&edge_min[0], vb);                       // N
+            if (r == HT - 1) atomicMin(&edge_min[1], vb);                  // S
+            if (c == 0) atomicMin(&edge_min[2], vb);                       // W
+            if (c == HT - 1) atomicMin(&edge_min[3], vb);                  // E
+            if (r == 0 && c == 0) atomicMin(&edge_min[4], vb);             // NW
+            if (r == 0 && c == HT - 1) atomicMin(&edge_min[5], vb);        // NE
+            if (r == HT - 1 && c == 0) atomicMin(&edge_min[6], vb);        // SW
+            if (r == HT - 1 && c == HT - 1) atomicMin(&edge_min[7], vb);   // SE
         }
     }
     __syncthreads();
-    if (tid < 8 && edge_changed[tid])
+    if (tid < 8 && edge_min[tid] != INACTIVE)
     {
         const int dxs[8] = {0, 0, -1, 1, -1, 1, -1, 1};
         const int dys[8] = {-1, 1, 0, 0, -1, -1, 1, 1};
@@ -154,10 +204,13 @@ __global__ void __launch_bounds__(HT_THREADS) heur_round_kernel(float *__restric
         if (ntx >= 0 && ntx < static_cast<int>(tiles_x) && nty >= 0 && nty < static_cast<int>(tiles_y))
         {
             const uint32_t nt = nty * tiles_x + ntx;
-            if (atomicExch(&nxt[nt], 1u) == 0u)
-                atomicAdd(&counters[(round + 1) & 3], 1u);
+            const uint32_t k = edge_min[tid];
+            if (atomicMin(&nxt[nt], k) == INACTIVE)
+                list_nxt[atomicAdd(&counters[(round + 1) & 3], 1u)] = nt;
+            atomicMin(&counters[8 + ((round + 1) & 3)], k);
         }
     }
+    }  // work list
 }
 
 __global__ void heur_finalize_kernel(float *field, size_t n)
@@ -167,6 +220,15 @@ __global__ void heur_finalize_kernel(float *field, size_t n)
     for (size_t k = i; k < n; k += stride)
         if (field[k] == __int_as_float(0x7f800000))
             field[k] = 0.0f;  // unreachable: the reference leaves 0 (unseen) there
+}
+// bucket width of the tile schedule, in cost units (a straight step over a free cell costs 1)
+float heur_delta()
+{
+    static const float d = [] {
+        const char *e = getenv("PP_HEUR_DELTA");  // tuning knob for experiments
+        return e ? static_cast<float>(atof(e)) : 96.0f;
+    }();
+    return d;
 }
 }  // namespace
 
@@ -182,7 +244,7 @@ pp_status pp_heuristic_build(pp_handle h, uint32_t goal_x, uint32_t goal_y, floa
     const uint32_t W = h->W, H = h->H;
     const size_t n = static_cast<size_t>(W) * H;
     const uint32_t tiles_x = (W + HT - 1) / HT, tiles_y = (H + HT - 1) / HT, nT = tiles_x * tiles_y;
-    const size_t n_flags = 2 * static_cast<size_t>(nT) + 8;
+    const size_t n_flags = 4 * static_cast<size_t>(nT) + N_COUNTERS;
     PP_CUDA(h, pp_reserve(h->d_field, h->field_cap, n));
     PP_CUDA(h, pp_reserve(h->d_tile_flags, h->tile_flags_cap, n_flags));
     size_t travel_cap = h->d_travel ? 512 : 0;
@@ -218,13 +280,13 @@ pp_status pp_heuristic_build(pp_handle h, uint32_t goal_x, uint32_t goal_y, floa
     {
         for (int k = 0; k < ROUNDS_PER_CHECK; ++k, ++round)
         {
-            heur_round_kernel<<<nT, HT_THREADS, 0, h->stream>>>(h->d_field, h->d_cost, h->d_travel, W, H, tiles_x, tiles_y,
-                                                                h->d_tile_flags, round);
+            heur_round_kernel<<<std::min<uint32_t>(nT, ROUND_GRID), HT_THREADS, 0, h->stream>>>(h->d_field, h->d_cost, h->d_travel, W, H, tiles_x, tiles_y,
+                                                                h->d_tile_flags, round, heur_delta());
             h->launches++;
         }
         PP_CUDA(h, cudaGetLastError());
         // counters[(round) & 3] holds the number of tiles flagged for the round that would run next
-        PP_CUDA(h, cudaMemcpyAsync(h->h_counter, h->d_tile_flags + 2 * static_cast<size_t>(nT), 8 * sizeof(uint32_t),
+        PP_CUDA(h, cudaMemcpyAsync(h->h_counter, h->d_tile_flags + 4 * static_cast<size_t>(nT), N_COUNTERS * sizeof(uint32_t),
                                    cudaMemcpyDeviceToHost, h->stream));
         PP_CUDA(h, cudaStreamSynchronize(h->stream));
         done = h->h_counter[round & 3] == 0;
@@ -276,7 +338,7 @@ pp_status pp_heuristic_stats(pp_handle h, uint32_t *rounds, uint64_t *tile_visit
 // allocations. Such a caller owns its buffers; what it cannot supply is this kernel's scratch
 // memory: the two generations of per-tile activity flags with their round counters, and the
 // travel-cost table. Here that scratch lives in a fixed array in device global memory that is part
-// of the library image, so every GPU that loads the library carries these ~130 KB until the
+// of the library image, so every GPU that loads the library carries these ~260 KB until the
 // process exits.
 //
 // Limit: at most 16384 tiles of 32x32 cells, i.e. ceil(W/32)*ceil(H/32) <= 16384 (4096 x 4096 fits);
@@ -295,7 +357,7 @@ pp_status pp_heuristic_stats(pp_handle h, uint32_t *rounds, uint64_t *tile_visit
 namespace
 {
 constexpr uint32_t NOALLOC_MAX_TILES = (4096 / HT) * (4096 / HT);
-constexpr size_t NOALLOC_FLAG_WORDS = 2 * static_cast<size_t>(NOALLOC_MAX_TILES) + 8;
+constexpr size_t NOALLOC_FLAG_WORDS = 4 * static_cast<size_t>(NOALLOC_MAX_TILES) + N_COUNTERS;
 constexpr size_t NOALLOC_WORDS = NOALLOC_FLAG_WORDS + 512;  // flags + counters, then the 2x256 travel table
 constexpr int NOALLOC_MAX_DEVICES = 64;
 
@@ -357,21 +419,21 @@ extern "C" pp_status pp_heuristic_build_noalloc(const uint8_t *d_cost, uint32_t 
         return pp_fail(nullptr, PP_ERR_CUDA, "pp_heuristic_build_noalloc: travel table upload: %s", cudaGetErrorString(e));
 
     const size_t n = static_cast<size_t>(W) * H;
-    const size_t n_flags = 2 * static_cast<size_t>(nT) + 8;
+    const size_t n_flags = 4 * static_cast<size_t>(nT) + N_COUNTERS;
     const uint32_t goal_index = goal_y * W + goal_x;
     const uint32_t goal_tile = (goal_y / HT) * tiles_x + goal_x / HT;
     // the init kernel clears every flag and counter this call will touch, and seeds the goal
     heur_init_kernel<<<148 * 8, 256, 0, stream>>>(d_field_out, n, flags, n_flags, goal_index, goal_tile);
     uint32_t round = 0;
-    uint32_t counters[4];
+    uint32_t counters[N_COUNTERS];
     const uint64_t max_rounds = static_cast<uint64_t>(n) + 8;
     for (;;)
     {
         for (int k = 0; k < ROUNDS_PER_CHECK; ++k, ++round)
-            heur_round_kernel<<<nT, HT_THREADS, 0, stream>>>(d_field_out, d_cost, travel_dev, W, H, tiles_x, tiles_y, flags, round);
+            heur_round_kernel<<<std::min<uint32_t>(nT, ROUND_GRID), HT_THREADS, 0, stream>>>(d_field_out, d_cost, travel_dev, W, H, tiles_x, tiles_y, flags, round, heur_delta());
         e = cudaGetLastError();
         if (e == cudaSuccess)
-            e = cudaMemcpyAsync(counters, flags + 2 * static_cast<size_t>(nT), sizeof(counters), cudaMemcpyDeviceToHost, stream);
+            e = cudaMemcpyAsync(counters, flags + 4 * static_cast<size_t>(nT), sizeof(counters), cudaMemcpyDeviceToHost, stream);
         if (e == cudaSuccess)
             e = cudaStreamSynchronize(stream);
         if (e != cudaSuccess)
