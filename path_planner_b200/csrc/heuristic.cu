@@ -273,7 +273,7 @@ pp_status pp_heuristic_build(pp_handle h, uint32_t goal_x, uint32_t goal_y, floa
     h->heur_tile_visits = 0;
     // every round moves information across at least one tile border, and a shortest path visits a
     // cell at most once, so W*H rounds is a (very loose) hard bound
-    const uint64_t max_rounds = static_cast<uint64_t>(n) + 8;
+    const uint64_t max_rounds = 4 * static_cast<uint64_t>(n) + 64;  // loose: every round moves some value forward
     uint32_t round = 0;
     bool done = false;
     while (!done)
@@ -290,7 +290,7 @@ pp_status pp_heuristic_build(pp_handle h, uint32_t goal_x, uint32_t goal_y, floa
                                    cudaMemcpyDeviceToHost, h->stream));
         PP_CUDA(h, cudaStreamSynchronize(h->stream));
         done = h->h_counter[round & 3] == 0;
-        PP_REQUIRE(h, round < max_rounds, PP_ERR_STATE, "pp_heuristic_build: relaxation did not converge");
+        PP_REQUIRE(h, done || round < max_rounds, PP_ERR_STATE, "pp_heuristic_build: relaxation did not converge");
     }
     h->heur_rounds = round;
     h->heur_tile_visits = h->h_counter[4];
@@ -426,7 +426,7 @@ extern "C" pp_status pp_heuristic_build_noalloc(const uint8_t *d_cost, uint32_t 
     heur_init_kernel<<<148 * 8, 256, 0, stream>>>(d_field_out, n, flags, n_flags, goal_index, goal_tile);
     uint32_t round = 0;
     uint32_t counters[N_COUNTERS];
-    const uint64_t max_rounds = static_cast<uint64_t>(n) + 8;
+    const uint64_t max_rounds = 4 * static_cast<uint64_t>(n) + 64;
     for (;;)
     {
         for (int k = 0; k < ROUNDS_PER_CHECK; ++k, ++round)

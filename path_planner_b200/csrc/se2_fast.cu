@@ -8,22 +8,23 @@
 //   V[t][y][x] = max_i T_{B_i}[y + o_i.y][x + o_i.x],   T_B = dilation of the costmap tile by B.
 // The brick tables are heading-independent: a CTA stages one 64x32 tile (+ halo) of the costmap in
 // shared memory, derives up to 11 brick tables from it by doubling (each table is the max of two
-// shifted earlier tables), and then serves ALL heading bins of the launch from them, turning the
-// P = 48 gathers per cell of the reference into ~17 aligned 32-bit shared-memory loads per four
-// cells. Every table is stored in four byte-shifted copies so that the word for any x offset is an
-// aligned LDS.32.
+// shifted earlier tables; recipes are compile-time data), and then serves ALL heading bins of the
+// launch from them, turning the P = 48 gathers per cell of the reference into ~15.5 aligned 32-bit
+// shared-memory loads per four cells. Every table is stored in four byte-shifted copies so that
+// the word for any x offset is an aligned LDS.32.
 //
 // sm_100a has no native per-byte max (__vmaxu4 is emulated with ~7 instructions). It does have the
 // 3-input VIMNMX3.U16x2. A u16 max is decided by the high byte, so on a raw word (b0,b1,b2,b3) it
 // yields the correct maxima of b1 and b3, and on the word shifted left by 8 bits those of b0 and
-// b2; the low bytes are don't-cares. Two accumulators per thread, two samples per instruction;
+// b2; the low bytes are don't-cares. Two accumulators per quad, two samples per instruction;
 // the shift is an IMAD on the otherwise idle FMA pipe.
 //
 // Exactness: the host planner evaluates the reference expression for every column, row, point
 // and bin with the same float operations (and the host libm's cosf/sinf), finds the ranges of
 // columns / rows over which all offsets are constant, and lets the fast kernel handle only tiles
 // that lie inside such ranges (up to 2 ranges per axis and bin). All other (tile, bin) pairs go
-// to the exact generic kernel through a work list.
+// to the exact generic kernel through a work list. Covers are minimum exact set covers found by
+// greedy + branch and bound.
 #include "se2_plan.h"
 
 #include <algorithm>
@@ -110,16 +111,8 @@ __device__ __forceinline__ uint32_t bytemax4(uint32_t a, uint32_t b)
     return __byte_perm(even, odd, 0x7351);
 }
 
-__device__ __forceinline__ uint32_t lds32(uint32_t addr)
-{
-    uint32_t v;
-    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr));
-    return v;
-}
-
 constexpr int QPT = 8;                                     // quads (4 cells along x) per thread and bin
-constexpr int WARPS_PER_BIN = FT_W / 4 * FT_H / QPT / 32;  // 2
-constexpr int NGROUPS = FT_THREADS / 32 / WARPS_PER_BIN;   // 8 bins in flight per CTA
+static_assert(FT_W / 4 * FT_H / QPT / 32 == 2, "a work unit is half the rows of a tile: one warp, QPT quads per thread");
 
 // row of quad j of a thread, relative to the thread's first row
 __host__ __device__ constexpr int quad_row(int j) { return (j & 3) * 2 + (j >> 2) * 16; }

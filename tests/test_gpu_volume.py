@@ -149,3 +149,48 @@ def test_error_paths(handle):
         handle.footprint_from_boundary(RES, [1.0, 2.0, 3.0], True)  # 3 numbers: the reference asserts
     with pytest.raises(PPError):
         handle.se2_volume_refresh()  # nothing built yet
+
+
+def test_arbitrary_footprints_through_both_paths(handle, port):
+    """pp_footprint_set with random offset lists (duplicates, lopsided shapes, single points): the
+    planner has to find exact covers for sets no library was designed for."""
+    cost = make_costmap(320, 192, seed=31)
+    rng = np.random.default_rng(7)
+    handle.costmap_upload(cost)
+    for trial in range(6):
+        n = int(rng.integers(1, 70))
+        offs = rng.integers(-9, 10, size=(n, 2)).astype(np.int32)
+        if trial == 0:
+            offs = np.array([[0, 0]], np.int32)
+        if trial == 1:
+            offs = np.concatenate([offs, offs[:5]])  # duplicates
+        want = port.se2_volume(cost, offs, 72, 0.5, 0.5, 0.0)
+        for mode in (0, 1):
+            handle.footprint_set(offs)
+            handle.se2_volume_set_mode(mode)
+            handle.se2_volume_build(72)
+            assert np.array_equal(handle.se2_volume_download(), want), (trial, mode)
+    handle.se2_volume_set_mode(0)
+
+
+@pytest.mark.parametrize("n_theta,off", [(7, (0.5, 0.5, 0.0)), (144, (0.25, 0.75, 0.5)), (1, (0.0, 0.0, 0.0)), (72, (-0.3, 0.9, 0.0))])
+def test_odd_bin_counts_and_offsets(handle, port, n_theta, off):
+    cost = make_costmap(260, 130, seed=32)
+    pts = port.footprint_points(RES, [0.64, 0.46], True)
+    handle.costmap_upload(cost)
+    handle.footprint_from_boundary(RES, [0.64, 0.46], True)
+    handle.se2_volume_build(n_theta, *off)
+    assert np.array_equal(handle.se2_volume_download(), port.se2_volume(cost, pts, n_theta, *off))
+
+
+def test_large_footprint_and_coarse_resolution(handle, port):
+    """reach 22 cells (beyond the fast path's halo limit: everything goes to the generic kernel)
+    and the 0.1 m resolution of the shipped map (28-point rim)."""
+    cost = make_costmap(200, 160, seed=33)
+    handle.costmap_upload(cost)
+    for res, b, hole in [(0.05, [1.6, 1.2], True), (0.1, [0.64, 0.46], True), (0.05, [1.0], False)]:
+        pts = port.footprint_points(res, b, hole)
+        handle.footprint_from_boundary(res, b, hole)
+        handle.se2_volume_build(72, t_begin=30, t_end=40)
+        got = handle.se2_volume_download(30, 40)
+        assert np.array_equal(got, port.se2_volume(cost, pts, 72, t0=30, t1=40)), (res, b)
