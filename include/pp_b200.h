@@ -159,6 +159,29 @@ pp_status pp_heuristic_stats(pp_handle h, uint32_t *rounds, uint64_t *tile_visit
 pp_status pp_heuristic_build_noalloc(const uint8_t *d_cost, uint32_t W, uint32_t H, uint32_t goal_x, uint32_t goal_y,
                                      float cost_penalty, float *d_field_out, void *cuda_stream);
 
+/* ---- N1: Hybrid-A* plan over the GPU tables --------------------------------------------------
+ * Replaces AstarHybrid::createPath (astar_hybrid.cpp:392-515) as PathPlannerROS::goalSetCallback
+ * calls it (path_planner_ros.cpp:136): builds the SE2 volume for the start pose's heading phase and
+ * the heuristic field for the goal on the GPU, mirrors both in pinned host memory and runs the
+ * reference's search on the host with O(1) table lookups (path_planner_b200/host/hybrid_astar.h).
+ * The parameters are SearchInfo's (planner/commons.h:26-48; defaults config/params.yaml:32-45).
+ * Poses are (x [m], y [m], yaw [rad]) in the map frame; the path comes back goal -> start, like the
+ * reference's before path_planner_ros.cpp:140 reverses it. *found_out is 0 when the search fails
+ * (that is a result, not an error). Needs an uploaded costmap and a footprint.
+ * Footprint checks use the pose's cell centre and nearest heading bin. */
+typedef struct pp_plan_params
+{
+    int32_t motion_type; /* 1 Dubins, 2 Reeds-Shepp */
+    uint32_t n_theta;
+    float minimum_turning_radius, cost_penalty, change_penalty, non_straight_penalty, reverse_penalty;
+    float analytic_expansion_ratio, analytic_expansion_tolerance, tolerance;
+    uint32_t max_iterations, max_on_approach_iterations;
+} pp_plan_params;
+pp_status pp_plan(pp_handle h, const pp_plan_params *params, double resolution, double origin_x, double origin_y,
+                  const float *start_xyt, const float *goal_xyt, float *path_xyt_out, uint32_t max_points,
+                  uint32_t *n_points_out, int32_t *iterations_out, int32_t *found_out, double *tables_ms_out,
+                  double *search_ms_out);
+
 /* ---- K3: TEB obstacle association -----------------------------------------------------------
  * pp_obstacles_extract replaces TebFollower::addObstacles (teb_follower.cpp:140-169): all cells
  * with cost >= 253, as world points (cell centres), filtered by the +-1.2*max_follow_range box

@@ -18,7 +18,7 @@ SYMBOLS = [
     "pp_timer_start", "pp_timer_stop", "pp_l2_flush", "pp_launch_count", "pp_costmap_upload", "pp_costmap_update_rect", "pp_costmap_download",
     "pp_footprint_from_boundary", "pp_footprint_set", "pp_footprint_get", "pp_se2_volume_build",
     "pp_se2_volume_refresh", "pp_se2_volume_download", "pp_se2_volume_ptr", "pp_se2_volume_set_mode",
-    "pp_se2_volume_stats", "pp_footprint_cost_batch", "pp_heuristic_build", "pp_heuristic_ptr", "pp_heuristic_stats", "pp_heuristic_build_noalloc",
+    "pp_se2_volume_stats", "pp_footprint_cost_batch", "pp_heuristic_build", "pp_heuristic_ptr", "pp_heuristic_stats", "pp_heuristic_build_noalloc", "pp_plan",
     "pp_obstacles_extract", "pp_radius_topk", "pp_comm_unique_id", "pp_comm_init", "pp_se2_volume_allgather", "pp_se2_volume_reserve",
     "pp_se2_volume_ipc_export", "pp_se2_volume_ipc_open", "pp_se2_volume_set_push", "pp_se2_volume_set_rows",
 ]
@@ -26,6 +26,23 @@ SYMBOLS = [
 _vp = C.c_void_p
 _u32 = C.c_uint32
 _lib = None
+
+
+class PlanParams(C.Structure):
+    """pp_plan_params; defaults from the reference's config/params.yaml:32-45."""
+    _fields_ = [("motion_type", C.c_int32), ("n_theta", C.c_uint32), ("minimum_turning_radius", C.c_float),
+                ("cost_penalty", C.c_float), ("change_penalty", C.c_float), ("non_straight_penalty", C.c_float),
+                ("reverse_penalty", C.c_float), ("analytic_expansion_ratio", C.c_float),
+                ("analytic_expansion_tolerance", C.c_float), ("tolerance", C.c_float), ("max_iterations", C.c_uint32),
+                ("max_on_approach_iterations", C.c_uint32)]
+
+    @classmethod
+    def make(cls, motion_type=2, n_theta=72, minimum_turning_radius=0.84, cost_penalty=2.0, change_penalty=0.01,
+             non_straight_penalty=1.2, reverse_penalty=3.0, analytic_expansion_ratio=1.0,
+             analytic_expansion_tolerance=3.0, tolerance=0.6, max_iterations=100000, max_on_approach_iterations=1000):
+        return cls(motion_type, n_theta, minimum_turning_radius, cost_penalty, change_penalty, non_straight_penalty,
+                   reverse_penalty, analytic_expansion_ratio, analytic_expansion_tolerance, tolerance, max_iterations,
+                   max_on_approach_iterations)
 
 
 class PPError(RuntimeError):
@@ -70,6 +87,9 @@ def load():
     L.pp_footprint_cost_batch.argtypes = [_vp, _vp, _u32, _vp, _vp]
     L.pp_heuristic_build.argtypes = [_vp, _u32, _u32, C.c_float, _vp]
     L.pp_heuristic_build_noalloc.argtypes = [_vp, _u32, _u32, _u32, _u32, C.c_float, _vp, _vp]
+    L.pp_plan.argtypes = [_vp, C.POINTER(PlanParams), C.c_double, C.c_double, C.c_double, _vp, _vp, _vp, _u32,
+                          C.POINTER(_u32), C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_double),
+                          C.POINTER(C.c_double)]
     L.pp_heuristic_ptr.argtypes = [_vp, C.POINTER(_vp)]
     L.pp_heuristic_stats.argtypes = [_vp, C.POINTER(_u32), C.POINTER(C.c_uint64)]
     L.pp_obstacles_extract.argtypes = [_vp] + [C.c_double] * 8 + [_vp, _u32, C.POINTER(_u32)]
@@ -243,6 +263,19 @@ class Handle:
         r, v = _u32(0), C.c_uint64(0)
         self._ck(self.L.pp_heuristic_stats(self.h, C.byref(r), C.byref(v)))
         return {"rounds": r.value, "tile_visits": v.value}
+
+    # N1
+    def plan(self, resolution, origin, start, goal, params=None, max_points=20000):
+        P = PlanParams.make(**(params or {}))
+        s = np.ascontiguousarray(start, np.float32)
+        g = np.ascontiguousarray(goal, np.float32)
+        path = np.zeros((max_points, 3), np.float32)
+        n, it, found = _u32(0), C.c_int32(0), C.c_int32(0)
+        t_ms, s_ms = C.c_double(0), C.c_double(0)
+        self._ck(self.L.pp_plan(self.h, C.byref(P), resolution, origin[0], origin[1], _ptr(s), _ptr(g), _ptr(path), max_points,
+                                C.byref(n), C.byref(it), C.byref(found), C.byref(t_ms), C.byref(s_ms)))
+        return {"ok": found.value, "path": path[:n.value].copy(), "iterations": it.value, "tables_ms": t_ms.value,
+                "search_ms": s_ms.value}
 
     # K3
     def obstacles_extract(self, resolution, origin, robot_pose, max_follow_range, behind_ignore_range, download=True):

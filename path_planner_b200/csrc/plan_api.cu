@@ -1,0 +1,103 @@
+// N1: pp_plan -- GPU tables + host Hybrid-A* (see include/pp_b200.h, host/hybrid_astar.h).
+#include "pp_internal.h"
+#include "../host/hybrid_astar.h"
+
+#include <chrono>
+
+namespace
+{
+template <class T>
+cudaError_t reserve_pinned(T *&ptr, size_t &cap, size_t need)
+{
+    if (need <= cap && ptr)
+        return cudaSuccess;
+    if (ptr)
+        cudaFreeHost(ptr);
+    ptr = nullptr;
+    cap = 0;
+    cudaError_t e = cudaHostAlloc(reinterpret_cast<void **>(&ptr), need * sizeof(T), cudaHostAllocDefault);
+    if (e == cudaSuccess)
+        cap = need;
+    return e;
+}
+}  // namespace
+
+extern "C" pp_status pp_plan(pp_handle h, const pp_plan_params *params, double resolution, double origin_x, double origin_y,
+                             const float *start_xyt, const float *goal_xyt, float *path_xyt_out, uint32_t max_points,
+                             uint32_t *n_points_out, int32_t *iterations_out, int32_t *found_out, double *tables_ms_out,
+                             double *search_ms_out)
+{
+    if (!h)
+        return PP_ERR_INVALID;
+    PP_REQUIRE(h, params && start_xyt && goal_xyt && n_points_out && iterations_out && found_out, PP_ERR_INVALID, "pp_plan: null argument");
+    PP_REQUIRE(h, h->d_cost, PP_ERR_STATE, "pp_plan: upload a costmap first");
+    PP_REQUIRE(h, !h->fp.empty(), PP_ERR_STATE, "pp_plan: set a footprint first");
+    PP_REQUIRE(h, params->motion_type == 1 || params->motion_type == 2, PP_ERR_INVALID, "pp_plan: motion_type must be 1 (Dubins) or 2 (Reeds-Shepp)");
+    PP_REQUIRE(h, params->n_theta > 0 && resolution > 0.0, PP_ERR_INVALID, "pp_plan: n_theta and resolution must be positive");
+    *n_points_out = 0;
+    *iterations_out = 0;
+    *found_out = 0;
+
+    ppb::PlanParams pp;
+    pp.motion_type = params->motion_type;
+    pp.n_theta = params->n_theta;
+    pp.minimum_turning_radius = params->minimum_turning_radius;
+    pp.cost_penalty = params->cost_penalty;
+    pp.change_penalty = params->change_penalty;
+    pp.non_straight_penalty = params->non_straight_penalty;
+    pp.reverse_penalty = params->reverse_penalty;
+    pp.analytic_expansion_ratio = params->analytic_expansion_ratio;
+    pp.analytic_expansion_tolerance = params->analytic_expansion_tolerance;
+    pp.tolerance = params->tolerance;
+    pp.max_iterations = params->max_iterations;
+    pp.max_on_approach_iterations = params->max_on_approach_iterations;
+    ppb::HybridAStar search(pp, h->W, h->H, resolution, origin_x, origin_y);
+    const ppb::Pose start{start_xyt[0], start_xyt[1], start_xyt[2]}, goal{goal_xyt[0], goal_xyt[1], goal_xyt[2]};
+
+    const auto tic = std::chrono::steady_clock::now();
+    unsigned int gx = 0, gy = 0;
+    if (!search.goalCell(goal, gx, gy))
+        return PP_OK;  // goal outside the map: no path, like worldToMap failing at astar_hybrid.cpp:407
+    const float frac = search.headingFraction(start.theta);
+    pp_status st = pp_se2_volume_build(h, params->n_theta, 0.5f, 0.5f, frac, 0, params->n_theta);
+    if (st != PP_OK)
+        return st;
+    const size_t cells = static_cast<size_t>(h->W) * h->H;
+    PP_CUDA(h, reserve_pinned(h->h_vol_mirror, h->vol_mirror_cap, cells * params->n_theta));
+    PP_CUDA(h, reserve_pinned(h->h_field_mirror, h->field_mirror_cap, cells));
+    PP_CUDA(h, cudaMemcpyAsync(h->h_vol_mirror, h->d_vol, cells * params->n_theta, cudaMemcpyDeviceToHost, h->stream));
+    st = pp_heuristic_build(h, gx, gy, params->cost_penalty, nullptr);
+    if (st != PP_OK)
+        return st;
+    PP_CUDA(h, cudaMemcpyAsync(h->h_field_mirror, h->d_field, cells * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
+    PP_CUDA(h, cudaStreamSynchronize(h->stream));
+    const auto mid = std::chrono::steady_clock::now();
+
+    ppb::Tables tb;
+    tb.volume = h->h_vol_mirror;
+    tb.field = h->h_field_mirror;
+    tb.W = h->W;
+    tb.H = h->H;
+    tb.n_theta = params->n_theta;
+    tb.heading_fraction = frac;
+    std::vector<ppb::Pose> path;
+    int iterations = 0;
+    const bool found = search.plan(tb, start, goal, path, iterations);
+    const auto toc = std::chrono::steady_clock::now();
+
+    *found_out = found ? 1 : 0;
+    *iterations_out = iterations;
+    *n_points_out = static_cast<uint32_t>(path.size());
+    if (path_xyt_out)
+        for (size_t i = 0; i < path.size() && i < max_points; ++i)
+        {
+            path_xyt_out[3 * i] = path[i].x;
+            path_xyt_out[3 * i + 1] = path[i].y;
+            path_xyt_out[3 * i + 2] = path[i].theta;
+        }
+    if (tables_ms_out)
+        *tables_ms_out = std::chrono::duration<double, std::milli>(mid - tic).count();
+    if (search_ms_out)
+        *search_ms_out = std::chrono::duration<double, std::milli>(toc - mid).count();
+    return PP_OK;
+}

@@ -58,6 +58,12 @@ struct pp_ctx
     uint32_t heur_rounds = 0;
     uint64_t heur_tile_visits = 0, heur_sweeps = 0;
 
+    // N1 plan: pinned host mirrors of the tables
+    uint8_t *h_vol_mirror = nullptr;
+    size_t vol_mirror_cap = 0;
+    float *h_field_mirror = nullptr;
+    size_t field_mirror_cap = 0;
+
     // K3 TEB
     double *d_pts = nullptr;
     size_t pts_cap = 0;

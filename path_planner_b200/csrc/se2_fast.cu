@@ -460,13 +460,6 @@ struct Mask
     }
     bool subset_of(const Mask &o) const { return ((w[0] & ~o.w[0]) | (w[1] & ~o.w[1]) | (w[2] & ~o.w[2])) == 0; }
     bool operator==(const Mask &o) const { return w[0] == o.w[0] && w[1] == o.w[1] && w[2] == o.w[2]; }
-    int first() const
-    {
-        for (int i = 0; i < MASK_WORDS; ++i)
-            if (w[i])
-                return i * 64 + __builtin_ctzll(w[i]);
-        return -1;
-    }
     bool test(int b) const { return (w[b >> 6] >> (b & 63)) & 1ull; }
 };
 
@@ -640,6 +633,9 @@ struct Se2Plan
     uint32_t W = 0, H = 0, n_theta = 0;
     float ox = 0, oy = 0, ot = 0;
     std::vector<int32_t> fp;
+    // how hard the cover search tried (0 quick, 1 thorough) and how often the plan has been used
+    int effort = 0;
+    uint32_t uses = 0;
     // geometry
     bool usable = false;
     int R = 0, PW = 0, rows = 0, copy_words = 0, n_tables = 0;
@@ -749,10 +745,14 @@ bool plan_matches(const Se2Plan *p, pp_handle h)
            p->ot == h->ot && p->fp == h->fp;
 }
 
-pp_status build_plan(pp_handle h)
+pp_status build_plan(pp_handle h, int effort)
 {
     Se2Plan *pl = new Se2Plan();
     h->plan = pl;
+    pl->effort = effort;
+    // branch-and-bound nodes per offset set: a one-off build (pp_plan) should not wait for the last
+    // few percent; a plan that keeps being reused is re-planned thoroughly (see pp_se2_launch_fast)
+    const long node_budget = effort > 0 ? 400000 : 3000;
     pl->W = h->W;
     pl->H = h->H;
     pl->n_theta = h->n_theta;
@@ -849,7 +849,7 @@ pp_status build_plan(pp_handle h)
                 if (it == memo.end())
                 {
                     std::vector<uint32_t> words;
-                    for (const Placement &p : cover_set(S, bricks, R, 400000))
+                    for (const Placement &p : cover_set(S, bricks, R, node_budget))
                     {
                         const int ax = R + 4 + p.ox, ay = R + p.oy;  // >= 0; +4: the margin word
                         const uint32_t word = static_cast<uint32_t>((p.brick * 4 + (ax & 3)) * pl->copy_words + ay * pl->PW + (ax >> 2));
@@ -915,7 +915,15 @@ pp_status pp_se2_launch_fast(pp_handle h, uint32_t x0, uint32_t y0, uint32_t x1,
     if (!plan_matches(h->plan, h))
     {
         pp_se2_plan_free(h);
-        pp_status s = build_plan(h);
+        pp_status s = build_plan(h, 0);
+        if (s != PP_OK)
+            return s;
+    }
+    else if (h->plan->effort == 0 && ++h->plan->uses >= 2)
+    {
+        // third build with the same map size, footprint, bins and offsets: worth a thorough plan
+        pp_se2_plan_free(h);
+        pp_status s = build_plan(h, 1);
         if (s != PP_OK)
             return s;
     }

@@ -1,0 +1,101 @@
+// Host Hybrid-A* driver over the GPU-built tables.
+//
+// Same search as the reference's AstarHybrid::createPath (astar_hybrid.cpp:392-515, with
+// getNeighbors :264-291, getTravelCost :368-390, getHeuristicCost :242-247,
+// tryAnalyticExpansion / getAnalyticExpansion :293-366, MotionHybrid motion_hybrid.cpp:10-92),
+// written from scratch against two O(1) tables instead of per-pose work:
+//   * footprint checks  -> SE2 volume lookup at the pose's cell and nearest heading bin
+//                          (what CollisionChecker::checkAndGetFootprintCost costs P gathers for)
+//   * obstacle heuristic -> max(field[cell], diagonal distance): the table-hit branch of
+//                          getObstacleHeuristic (:177-183); the lazy A* (:97-165, :184-239) is gone
+// Evaluation order, float widths and the priority-queue discipline follow the reference so that,
+// on the same tables, the same path and iteration count come out
+// (tests/test_gpu_e2e_plan.py compares against the reference's own search).
+// The wall-clock cut-off of the reference (max_millsec, :469) is not reproduced: it makes the
+// result depend on machine load.
+#pragma once
+#include "curves.h"
+
+#include <cstdint>
+#include <memory>
+#include <queue>
+#include <unordered_map>
+#include <vector>
+
+namespace ppb
+{
+struct PlanParams  // SearchInfo, planner/commons.h:26-48; defaults of config/params.yaml:32-45
+{
+    int motion_type = 2;  // 1 Dubins, 2 Reeds-Shepp
+    unsigned int n_theta = 72;
+    float minimum_turning_radius = 0.84f, cost_penalty = 2.0f, change_penalty = 0.01f, non_straight_penalty = 1.2f,
+          reverse_penalty = 3.0f;
+    float analytic_expansion_ratio = 1.0f, analytic_expansion_tolerance = 3.0f, tolerance = 0.6f;
+    unsigned int max_iterations = 100000, max_on_approach_iterations = 1000;
+};
+
+struct Pose
+{
+    float x, y, theta;
+};
+
+struct Tables
+{
+    const uint8_t *volume = nullptr;  // [n_theta][H][W], built with sample offsets (0.5, 0.5, heading_fraction)
+    const float *field = nullptr;     // [H][W] obstacle heuristic for the goal cell, 0 = unreachable
+    unsigned int W = 0, H = 0, n_theta = 0;
+    float heading_fraction = 0.0f;
+};
+
+class HybridAStar
+{
+public:
+    HybridAStar(const PlanParams &params, unsigned int W, unsigned int H, double resolution, double origin_x, double origin_y);
+
+    // fractional part of the heading coordinate every node of a search from `start_theta` has
+    float headingFraction(float start_theta) const;
+    // goal cell of a world pose (for building the heuristic field); false if outside the map
+    bool goalCell(const Pose &goal_world, unsigned int &gx, unsigned int &gy) const;
+
+    // world poses in (metres, metres, radians); path runs goal -> start like the reference's
+    // (path_planner_ros.cpp:140 reverses it afterwards)
+    bool plan(const Tables &tables, const Pose &start_world, const Pose &goal_world, std::vector<Pose> &path, int &iterations);
+
+private:
+    struct Node
+    {
+        Node *parent = nullptr;
+        bool visited = false;
+        float cell_cost;
+        float g;
+        unsigned int index;
+        unsigned int motion;
+        Pose at{0.0f, 0.0f, 0.0f};
+        explicit Node(unsigned int i);
+    };
+    using QItem = std::pair<float, Node *>;
+    struct Later
+    {
+        bool operator()(const QItem &a, const QItem &b) const { return a.first > b.first; }
+    };
+
+    Node *node(unsigned int index);
+    unsigned int indexOf(unsigned int x, unsigned int y, unsigned int t) const { return t + x * _n_theta + y * _n_theta * _W; }
+    void wrapHeading(float &h) const;
+    bool footprint(const Tables &tb, float x, float y, float theta_rad, float &cost) const;
+    float heuristic(const Tables &tb, const Pose &at) const;
+    float travelCost(const Node *from, const Node *to) const;
+    void expand(const Tables &tb, Node *n, std::vector<Node *> &out);
+    Node *analyticExpansion(const Tables &tb, Node *n);
+    bool backtrace(Node *n, std::vector<Pose> &path) const;
+
+    PlanParams _p;
+    unsigned int _W, _H, _n_theta;
+    double _res, _ox, _oy;
+    float _n_theta_f, _bin, _turn_cells, _tol_cells, _ae_ratio_cells, _ae_tol_cells, _neutral;
+    std::vector<Pose> _motions;
+    std::unique_ptr<CurveSpace> _curves;
+    std::unordered_map<unsigned int, Node> _graph;
+    Node *_start = nullptr, *_goal = nullptr;
+};
+}  // namespace ppb

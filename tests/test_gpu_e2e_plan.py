@@ -85,3 +85,47 @@ def test_unmodified_reference_for_context(port, ref):
     assert np.allclose(path[0], b["path"][0]) and np.allclose(path[-1], b["path"][-1])  # same endpoints
     print("reference: %d iterations %.1f ms; table-driven: %d iterations %.1f ms (+%.1f ms prepare)"
           % (it, ms, b["iterations"], b["plan_ms"], b["prepare_ms"]))
+
+
+@pytest.mark.parametrize("W,seed,cov,start,goal,boundary,extra", [
+    (400, 3, 0.06, (2.0, 2.0, 0.3), (17.5, 17.0, 1.2), [0.64, 0.46], {}),
+    (400, 5, 0.05, (1.5, 1.5, 0.0), (18.0, 3.0, -1.0), [0.64, 0.46], {}),
+    (400, 8, 0.05, (3.0, 17.0, -0.5), (16.0, 2.5, 0.0), [0.64, 0.46], {}),
+    (400, 9, 0.05, (10.0, 10.0, 2.0), (2.0, 18.0, 3.0), [0.64, 0.46], {"motion_type": 1}),
+    (2048, 2, 0.04, (5.0, 5.0, 0.5), (60.0, 45.0, 0.0), [-0.2, -0.25, 0.6, 0.25], {"max_iterations": 400000}),
+])
+def test_product_search_matches_reference_search(handle, port, W, seed, cov, start, goal, boundary, extra):
+    """pp_plan (the library's own host Hybrid-A* over the GPU tables, host/hybrid_astar.cpp) against
+    the reference's search code running over the same kind of tables: same path, same iterations."""
+    e2e = oracle.load_e2e()
+    if e2e is None:
+        pytest.skip("oracle/_ref/libpp_e2e.so not built")
+    params = {"motion_type": 2}
+    params.update(extra)
+    cost = scene(W, seed, cov, start, goal)
+    ref_run = e2e.plan(1, cost, RES, boundary, True, start, goal, params=params)
+    handle.costmap_upload(cost)
+    handle.footprint_from_boundary(RES, boundary, True)
+    got = handle.plan(RES, (0.0, 0.0), start, goal, params)
+    assert got["ok"] == ref_run["ok"]
+    assert got["iterations"] == ref_run["iterations"]
+    assert got["path"].shape == ref_run["path"].shape
+    assert np.array_equal(got["path"], ref_run["path"])
+    print("pp_plan %dx%d: %d iterations, tables %.1f ms + search %.1f ms (reference search on tables: %.1f ms)"
+          % (W, W, got["iterations"], got["tables_ms"], got["search_ms"], ref_run["plan_ms"]))
+
+
+def test_plan_rejects_and_fails_cleanly(handle):
+    from path_planner_b200.capi import PPError
+    with pytest.raises(PPError):
+        handle.plan(RES, (0.0, 0.0), (1.0, 1.0, 0.0), (2.0, 2.0, 0.0))  # no costmap
+    cost = np.zeros((100, 100), np.uint8)
+    cost[:, 50] = 254  # a wall: the goal side is unreachable
+    handle.costmap_upload(cost)
+    handle.footprint_from_boundary(RES, [0.2], False)
+    r = handle.plan(RES, (0.0, 0.0), (1.0, 2.5, 0.0), (4.0, 2.5, 0.0))
+    assert r["ok"] == 0 and len(r["path"]) == 0
+    r = handle.plan(RES, (0.0, 0.0), (1.0, 2.5, 0.0), (40.0, 2.5, 0.0))  # goal outside the map
+    assert r["ok"] == 0
+    r = handle.plan(RES, (0.0, 0.0), (0.6, 0.6, 0.0), (1.9, 1.2, 0.5))
+    assert r["ok"] == 1 and len(r["path"]) > 2
