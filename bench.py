@@ -131,6 +131,21 @@ def make_inputs():
     return make_costmap(W, H, seed=1, pockets=[(GOAL[0], GOAL[1], 6)])
 
 
+PLAN_SCENES = {
+    # BASELINE.json configs[0] and configs[1]: Hybrid A* on 400x400 (rect footprint) and 2048x2048 (box footprint)
+    "config1_400x400_rect": dict(W=400, seed=3, coverage=0.06, start=(2.0, 2.0, 0.3), goal=(17.5, 17.0, 1.2),
+                                 boundary=[0.64, 0.46], params={"motion_type": 2}),
+    "config2_2048x2048_box": dict(W=2048, seed=2, coverage=0.04, start=(5.0, 5.0, 0.5), goal=(60.0, 45.0, 0.0),
+                                  boundary=[-0.2, -0.25, 0.6, 0.25], params={"motion_type": 2, "max_iterations": 400000}),
+}
+
+
+def plan_scene(sc):
+    from path_planner_b200.synth import make_costmap
+    pockets = [(int(sc["start"][0] / RES), int(sc["start"][1] / RES), 25), (int(sc["goal"][0] / RES), int(sc["goal"][1] / RES), 25)]
+    return make_costmap(sc["W"], sc["W"], seed=sc["seed"], coverage=sc["coverage"], unknown_frac=0.0, pockets=pockets)
+
+
 def cpu_volume_sample(cost, target_seconds, threads):
     """Reference CPU volume on a row band sized for ~target_seconds; returns (cells/s, kind, sample)."""
     import oracle
@@ -410,6 +425,18 @@ def main():
         hms = h.timer_stop() / reps
         hs = h.heuristic_stats()
         line["heuristic"] = {"build_ms": hms, "rounds": hs["rounds"], "map": f"{W}x{H}", "unit": "ms"}
+        # plan ms: the library's own host Hybrid-A* over GPU tables (pp_plan), second call (buffers warm)
+        line["plan"] = {}
+        hp = capi.Handle(local_rank)
+        for name, sc in PLAN_SCENES.items():
+            pc = plan_scene(sc)
+            hp.costmap_upload(pc)
+            hp.footprint_from_boundary(RES, sc["boundary"], True)
+            hp.plan(RES, (0.0, 0.0), sc["start"], sc["goal"], sc["params"])
+            r = hp.plan(RES, (0.0, 0.0), sc["start"], sc["goal"], sc["params"])
+            line["plan"][name] = {"ms": r["tables_ms"] + r["search_ms"], "tables_ms": r["tables_ms"], "search_ms": r["search_ms"],
+                                  "iterations": r["iterations"], "path_poses": int(len(r["path"])), "found": bool(r["ok"])}
+        hp.close()
         from path_planner_b200.synth import make_teb_scene
         pts, poses = make_teb_scene(10000, 100, seed=0)
         h.radius_topk(pts, poses, 0.9574, 10)
@@ -434,6 +461,10 @@ def main():
                 pts, poses = make_teb_scene(10000, 100, seed=0)
                 ref.radius_topk(pts, poses, 0.9574, 10)
                 line["cpu_baseline"]["teb_us_per_round"] = 1e6 * (ref.last_build_seconds + ref.last_query_seconds)
+                line["cpu_baseline"]["plan"] = {}
+                for name, sc in PLAN_SCENES.items():  # the unmodified reference planner, 1 thread
+                    ok, path, it, ms = ref.plan(plan_scene(sc), RES, sc["boundary"], True, sc["start"], sc["goal"], sc["params"])
+                    line["cpu_baseline"]["plan"][name] = {"ms": ms, "iterations": it, "path_poses": int(len(path)), "found": bool(ok)}
         except Exception as e:  # the baseline is a report, never a reason to lose the GPU line
             line["cpu_baseline"]["note"] = f"heuristic/teb baseline failed: {e}"
 
