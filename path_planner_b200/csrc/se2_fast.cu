@@ -653,8 +653,14 @@ struct Se2Plan
     std::vector<uint32_t> h_work;
     std::vector<uint32_t> work_off;  // [n_theta+1] entry index
     uint32_t *d_work = nullptr;
+    // the part of the work list inside the last banded / dirty region (cached by region and bins)
+    std::vector<uint32_t> region_work;
+    uint32_t *d_region_work = nullptr;
+    size_t region_cap = 0;
+    uint64_t region_key[6] = {~0ull, 0, 0, 0, 0, 0};
     ~Se2Plan()
     {
+        cudaFree(d_region_work);
         cudaFree(d_xclass);
         cudaFree(d_yclass);
         cudaFree(d_work);
@@ -1000,9 +1006,44 @@ pp_status pp_se2_launch_fast(pp_handle h, uint32_t x0, uint32_t y0, uint32_t x1,
         const uint32_t w0 = pl->work_off[t], w1 = pl->work_off[t + n];
         if (w1 > w0)
         {
-            pp_status s = pp_se2_generic_worklist(h, pl->d_work + 2 * static_cast<size_t>(w0), w1 - w0);
-            if (s != PP_OK)
-                return s;
+            const bool whole_map = tx_lo == 0 && ty_lo == 0 && tx_hi >= pl->tiles_x && ty_hi >= pl->tiles_y;
+            if (whole_map)
+            {
+                pp_status s = pp_se2_generic_worklist(h, pl->d_work + 2 * static_cast<size_t>(w0), w1 - w0);
+                if (s != PP_OK)
+                    return s;
+            }
+            else
+            {
+                // a row band or a dirty region: only the listed (tile, bin) pairs inside it
+                const uint64_t key[6] = {tx_lo, tx_hi, ty_lo, ty_hi, t, n};
+                if (std::memcmp(key, pl->region_key, sizeof(key)) != 0)
+                {
+                    pl->region_work.clear();
+                    for (uint32_t e = w0; e < w1; ++e)
+                    {
+                        const uint32_t tile = pl->h_work[2 * e], wx = tile & 0xFFFFu, wy = tile >> 16;
+                        if (wx >= tx_lo && wx < tx_hi && wy >= ty_lo && wy < ty_hi)
+                        {
+                            pl->region_work.push_back(tile);
+                            pl->region_work.push_back(pl->h_work[2 * e + 1]);
+                        }
+                    }
+                    if (!pl->region_work.empty())
+                    {
+                        PP_CUDA(h, pp_reserve(pl->d_region_work, pl->region_cap, pl->region_work.size()));
+                        PP_CUDA(h, cudaMemcpyAsync(pl->d_region_work, pl->region_work.data(), pl->region_work.size() * sizeof(uint32_t),
+                                                   cudaMemcpyHostToDevice, h->stream));
+                    }
+                    std::memcpy(pl->region_key, key, sizeof(key));
+                }
+                if (!pl->region_work.empty())
+                {
+                    pp_status s = pp_se2_generic_worklist(h, pl->d_region_work, static_cast<uint32_t>(pl->region_work.size() / 2));
+                    if (s != PP_OK)
+                        return s;
+                }
+            }
         }
         t += n;
     }
