@@ -70,7 +70,9 @@ pp_status pp_launch_count(pp_handle h, uint64_t *count_out);
  * (Costmap2D::getCharMap(), row-major my*W+mx) is copied to the device once per update instead.
  * The reference takes no lock while costmap_2d mutates the grid on its own thread; callers
  * should copy under costmap->getMutex().
- *   pp_costmap_upload       whole grid; `host_is_pinned` != 0 skips the staging copy
+ *   pp_costmap_upload       whole grid; `host_is_pinned` != 0 skips the staging copy (the copy is
+ *                           then asynchronous: keep the buffer unchanged until pp_sync or a call
+ *                           that returns data)
  *   pp_costmap_update_rect  rows [y0,y0+h) x cols [x0,x0+w) from `src` (src_pitch bytes per row);
  *                           the rectangle is merged into the handle's dirty region
  *   pp_costmap_download     device grid back to the host (tests)

@@ -129,6 +129,8 @@ pp_status pp_se2_volume_reserve(pp_handle h, uint32_t n_theta)
     PP_REQUIRE(h, h->d_cost, PP_ERR_STATE, "pp_se2_volume_reserve: upload a costmap first (its size fixes the volume size)");
     PP_REQUIRE(h, n_theta > 0 && n_theta <= 4096, PP_ERR_RANGE, "n_theta %u outside 1..4096", n_theta);
     PP_CUDA(h, cudaSetDevice(h->device));
+    PP_REQUIRE(h, h->n_peer == 0 || static_cast<size_t>(h->W) * h->H * n_theta <= h->vol_cap, PP_ERR_STATE,
+               "pp_se2_volume_reserve: the volume is already mapped by peers and cannot grow");
     PP_CUDA(h, pp_reserve(h->d_vol, h->vol_cap, static_cast<size_t>(h->W) * h->H * n_theta));
     return PP_OK;
 }

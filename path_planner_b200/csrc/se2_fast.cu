@@ -633,6 +633,7 @@ struct Se2Plan
     uint32_t W = 0, H = 0, n_theta = 0;
     float ox = 0, oy = 0, ot = 0;
     std::vector<int32_t> fp;
+    bool few_bins = false;  // built for launches of at most FEW_BINS bins: fewer brick tables pay off
     // how hard the cover search tried (0 quick, 1 thorough) and how often the plan has been used
     int effort = 0;
     uint32_t uses = 0;
@@ -745,9 +746,10 @@ AxisClasses classify_axis(bool is_x, uint32_t n, float sample_off, const std::ve
     return out;
 }
 
+constexpr uint32_t FEW_BINS = 12;
 bool plan_matches(const Se2Plan *p, pp_handle h)
 {
-    return p && p->W == h->W && p->H == h->H && p->n_theta == h->n_theta && p->ox == h->ox && p->oy == h->oy &&
+    return p && p->few_bins == (h->t_end - h->t_begin <= FEW_BINS) && p->W == h->W && p->H == h->H && p->n_theta == h->n_theta && p->ox == h->ox && p->oy == h->oy &&
            p->ot == h->ot && p->fp == h->fp;
 }
 
@@ -800,6 +802,12 @@ pp_status build_plan(pp_handle h, int effort)
     pl->copy_words = pl->rows * pl->PW;
     const size_t table_bytes = static_cast<size_t>(4) * pl->copy_words * 4;
     int slots = static_cast<int>(std::min<size_t>(MAX_TABLES, (SMEM_LIMIT - 1024) / table_bytes));
+    // Every table costs a fixed amount per tile and saves samples per bin: with few bins per launch
+    // (a heading-sharded rank of an 8-GPU job builds 9) the costmap plus the two 2-runs is the optimum
+    // measured on B200 (tools/probe_tables.py).
+    pl->few_bins = h->t_end - h->t_begin <= FEW_BINS;
+    if (pl->few_bins)
+        slots = std::min(slots, 3);
     if (const char *cap = getenv("PP_SE2_MAX_TABLES"))  // tuning knob for experiments
         slots = std::max(1, std::min(slots, atoi(cap)));
     if (slots < 1)

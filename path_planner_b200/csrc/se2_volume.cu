@@ -270,6 +270,9 @@ pp_status pp_se2_volume_build(pp_handle h, uint32_t n_theta, float ox, float oy,
                "sample offsets must lie in [-1,1] (got %g, %g)", ox, oy);
     PP_CUDA(h, cudaSetDevice(h->device));
     const size_t plane = static_cast<size_t>(h->W) * h->H;
+    // peers may have this volume mapped (pp_se2_volume_ipc_open): it must not move under them
+    PP_REQUIRE(h, h->n_peer == 0 || plane * n_theta <= h->vol_cap, PP_ERR_STATE,
+               "pp_se2_volume_build: the volume is mapped by peers and too small for %u bins; reserve the final size before exporting it", n_theta);
     PP_CUDA(h, pp_reserve(h->d_vol, h->vol_cap, plane * n_theta));
     if (n_theta != h->n_theta || ox != h->ox || oy != h->oy || ot != h->ot)
         pp_se2_plan_free(h);
