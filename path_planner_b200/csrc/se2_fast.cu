@@ -37,20 +37,22 @@
 
 namespace
 {
-constexpr int FT_W = 64, FT_H = 32, FT_THREADS = 768;
+constexpr int FT_W = 64, FT_H = 16, FT_THREADS = 384;
+constexpr int CTAS_PER_SM = 2;
 constexpr int MAX_TABLES = 12;
 constexpr int MAX_T_PER_LAUNCH = 160;
 constexpr int MAX_LIST_WORDS = 6400;
 constexpr int MAX_R = 15;
-constexpr size_t SMEM_LIMIT = 227 * 1024;
+constexpr size_t SMEM_LIMIT = (227 * 1024 - 2048) / CTAS_PER_SM;  // per CTA; 1 KB per CTA is reserved by the system
 
 
 // ---------------------------------------------------------------------------------------------
 // Brick libraries. Table 0 is the costmap itself (the one-point brick); table k > 0 is
 // T_k = max(T_a, T_b shifted by (du, dv)). Tables are listed in dependency-level order. The
 // recipes are compile-time data so that the table build below unrolls completely.
-//   STAIRS  runs of 2/4/8 along x, 2/4 along y, the two diagonals, and four 4-cell "stair" bricks
-//           (two 2-runs offset by (2,+-1) or (+-1,2)) that follow rasterised oblique edges
+//   STAIRS  2-runs along x, y and the two diagonals, four 4-cell "stair" bricks (two 2-runs offset by
+//           (2,+-1) or (+-1,2)) that follow rasterised oblique edges, then runs of 4 along x and y
+//           and of 8 along x (the stairs come first so that a truncated library keeps them)
 //   RUNS3   runs of 2/3/6 along x and y, diagonals of 2/3/4
 //   BLOCKS  rectangles 2x2 .. 8x8 for solid footprints
 //   RUNS    runs of 2/4/8 along x and y, diagonals of 2/4
@@ -64,7 +66,7 @@ __host__ __device__ constexpr int lib_size(int lib) { return lib == 3 ? 11 : 12;
 __host__ __device__ constexpr Recipe lib_recipe(int lib, int k)
 {
     constexpr Recipe T[N_LIBS][MAX_TABLES] = {
-        {{0, 0, 0, 0}, {0, 0, 1, 0}, {0, 0, 0, 1}, {0, 0, 1, 1}, {0, 0, 1, -1}, {1, 1, 2, 0}, {2, 2, 0, 2}, {1, 1, 2, 1}, {1, 1, 2, -1}, {2, 2, 1, 2}, {2, 2, -1, 2}, {5, 5, 4, 0}},
+        {{0, 0, 0, 0}, {0, 0, 1, 0}, {0, 0, 0, 1}, {0, 0, 1, 1}, {0, 0, 1, -1}, {1, 1, 2, 1}, {1, 1, 2, -1}, {2, 2, 1, 2}, {2, 2, -1, 2}, {1, 1, 2, 0}, {2, 2, 0, 2}, {9, 9, 4, 0}},
         {{0, 0, 0, 0}, {0, 0, 1, 0}, {0, 0, 0, 1}, {0, 0, 1, 1}, {0, 0, 1, -1}, {1, 0, 2, 0}, {2, 0, 0, 2}, {3, 0, 2, 2}, {4, 0, 2, -2}, {3, 3, 2, 2}, {5, 5, 3, 0}, {6, 6, 0, 3}},
         {{0, 0, 0, 0}, {0, 0, 1, 0}, {0, 0, 0, 1}, {1, 1, 0, 1}, {1, 1, 2, 0}, {2, 2, 0, 2}, {3, 3, 2, 0}, {4, 4, 4, 0}, {5, 5, 0, 4}, {6, 6, 0, 2}, {9, 9, 4, 0}, {10, 10, 0, 4}},
         {{0, 0, 0, 0}, {0, 0, 1, 0}, {0, 0, 0, 1}, {0, 0, 1, 1}, {0, 0, 1, -1}, {1, 1, 2, 0}, {2, 2, 0, 2}, {3, 3, 2, 2}, {4, 4, 2, -2}, {5, 5, 4, 0}, {6, 6, 0, 4}, {0, 0, 0, 0}}};
@@ -112,10 +114,10 @@ __device__ __forceinline__ uint32_t bytemax4(uint32_t a, uint32_t b)
 }
 
 constexpr int QPT = 8;                                     // quads (4 cells along x) per thread and bin
-static_assert(FT_W / 4 * FT_H / QPT / 32 == 2, "a work unit is half the rows of a tile: one warp, QPT quads per thread");
+static_assert(FT_W / 4 * FT_H / QPT / 32 == 1, "a work unit is one bin of a tile: one warp, QPT quads per thread");
 
 // row of quad j of a thread, relative to the thread's first row
-__host__ __device__ constexpr int quad_row(int j) { return (j & 3) * 2 + (j >> 2) * 16; }
+__host__ __device__ constexpr int quad_row(int j) { return j; }
 
 template <int PW>
 __device__ __forceinline__ void load_pair(const uint8_t *smb, uint32_t d1, uint32_t d2, uint32_t (&u)[QPT], uint32_t (&v)[QPT])
@@ -157,7 +159,7 @@ __device__ __forceinline__ void run_units(const FastArgs &a, const uint32_t *sm,
     const bool in_x = gx < W;
     const size_t plane = static_cast<size_t>(a.W) * a.H;
     const size_t rs = a.W;
-    const uint32_t n_units = 2 * a.n_t;
+    const uint32_t n_units = a.n_t;
     while (true)
     {
         uint32_t unit = 0;
@@ -166,11 +168,11 @@ __device__ __forceinline__ void run_units(const FastArgs &a, const uint32_t *sm,
         unit = __shfl_sync(0xffffffffu, unit, 0);
         if (unit >= n_units)
             break;
-        const uint32_t t = unit >> 1;
+        const uint32_t t = unit;
         const uint32_t cls = s_cls[t];
         if (cls == 255u)
             continue;
-        const int row0 = static_cast<int>(unit & 1) + 8 * (lane >> 4);
+        const int row0 = 8 * (lane >> 4);
         const uint8_t *smb = reinterpret_cast<const uint8_t *>(sm + row0 * PW + q);
         const int gy = ty0 + row0;
         uint8_t *out = a.vol + plane * (a.t_first + t) + static_cast<size_t>(gy) * a.W + gx;
@@ -321,7 +323,7 @@ __device__ __forceinline__ void build_all_levels(uint32_t *sm, int CW, int rows,
 }
 
 template <int PW, int LIB>
-__global__ void __launch_bounds__(FT_THREADS, 1) se2_fast_kernel(const __grid_constant__ FastArgs a)
+__global__ void __launch_bounds__(FT_THREADS, CTAS_PER_SM) se2_fast_kernel(const __grid_constant__ FastArgs a)
 {
     extern __shared__ __align__(16) uint32_t sm[];
     __shared__ uint8_t s_cls[MAX_T_PER_LAUNCH];
