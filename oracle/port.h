@@ -38,6 +38,28 @@ int port_extract_obstacles(const uint8_t *cost, uint32_t W, uint32_t H, double r
 int port_radius_topk(const double *pts_xy, uint32_t N, const double *q_xy, uint32_t Q, double radius_arg, uint32_t K,
                      uint32_t *idx_out, double *d2_out, uint32_t *cnt_out, uint32_t *found_out);
 
+/* ---- ingestion before the hot path (oracle/ingest.c) ------------------ */
+typedef struct
+{
+    int track_unknown_space;    /* params.yaml:17 true */
+    int lethal_threshold;       /* costmap_2d default 100 */
+    int unknown_cost_value;     /* costmap_2d default -1 */
+    int trinary_costmap;        /* costmap_2d default true */
+    int inflate_unknown;        /* costmap_2d default false */
+    double resolution;          /* metres per cell */
+    double inscribed_radius;    /* metres, from the costmap footprint (params.yaml:6 -> 0.25) */
+    double inflation_radius;    /* params.yaml:22 0.5 */
+    double cost_scaling_factor; /* params.yaml:21 8.0 */
+} port_layer_params;
+
+int port_occupancy_from_image(const uint8_t *image, uint32_t W, uint32_t H, double occ_th, double free_th, int negate,
+                              int8_t *occ_out);
+int port_static_layer(const int8_t *occ, uint32_t W, uint32_t H, const port_layer_params *p, uint8_t *cost_out);
+uint32_t port_cell_inflation_radius(const port_layer_params *p);
+int port_inflation_cost_table(const port_layer_params *p, uint8_t *table);
+int port_inflate_propagate(uint8_t *master, uint32_t W, uint32_t H, const port_layer_params *p);
+int port_inflate_nearest(uint8_t *master, uint32_t W, uint32_t H, const port_layer_params *p);
+
 #ifdef __cplusplus
 }
 #endif
