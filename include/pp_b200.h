@@ -228,12 +228,55 @@ pp_status pp_se2_volume_ipc_export(pp_handle h, void *handle_out);
 pp_status pp_se2_volume_ipc_open(pp_handle h, const void *handles, int rank, int world);
 pp_status pp_se2_volume_set_push(pp_handle h, int enable);
 /* Row-band sharding (no counterpart in the reference): restrict pp_se2_volume_build to the map rows
- * [y_begin, y_end) (all columns, the bins given to the build). Whole 32-row tiles that overlap the
+ * [y_begin, y_end) (all columns, the bins given to the build). Whole 16-row tiles that overlap the
  * band are computed, so neighbouring bands may both write a few identical rows. y_end == 0 restores
  * the whole map. Together with pp_se2_volume_set_push this shards the volume spatially across GPUs:
  * every rank pays the per-tile table build only for its own band, which scales linearly, whereas
  * heading-bin sharding repeats that cost on every rank. */
 pp_status pp_se2_volume_set_rows(pp_handle h, uint32_t y_begin, uint32_t y_end);
+
+/* ---- N2: costmap ingestion (the step before the hot path) ----------------
+ * Today costmap_2d builds the grid on the CPU and the hot path only receives the result
+ * (pp_costmap_upload). These entry points build it on the GPU instead, so that a map change goes
+ * image/occupancy -> costmap -> SE2 volume refresh without leaving the device.
+ *
+ * pp_occupancy_from_image replaces the loop of MapManagerROS::loadMap
+ * (src/map_manager/src/map_manager_ros.cpp:93-108): `image` is the W x H 8-bit grayscale raster
+ * (row 0 at the top), thresholds are compared with the 0..255 pixel value as the reference does,
+ * the grid is stored bottom row first (map_manager_ros.h:15) as nav_msgs/OccupancyGrid data
+ * (0..100). pp_occupancy_upload / _update_rect take that data directly (the `/map` topic and its
+ * updates, path_planner/config/params.yaml:18); _download returns it.
+ *
+ * pp_costmap_from_occupancy replaces the two costmap_2d layers the reference configures
+ * (params.yaml:15-26; costmap_2d itself is not part of the reference tree): StaticLayer
+ * (interpretValue, written over the master grid) and InflationLayer (computeCost over the cell
+ * distance to the nearest lethal cell, out to ceil(inflation_radius / resolution) cells, with the
+ * NO_INFORMATION rule of its updateCosts). Distances are exact Euclidean nearest-obstacle
+ * distances; costmap_2d's queue hands sources over through four-neighbours and can settle on a
+ * farther obstacle in rare configurations, where this result is the higher (safer) cost -- see
+ * DESIGN.md. The result becomes the handle's costmap exactly as if it had been passed to
+ * pp_costmap_upload; after pp_occupancy_update_rect only the changed rectangle grown by the
+ * inflation radius is recomputed and recorded as the dirty region for pp_se2_volume_refresh.
+ * Limits: inflation radius <= 32 cells. */
+typedef struct pp_layer_params
+{
+    int track_unknown_space;    /* params.yaml:17 true */
+    int lethal_threshold;       /* costmap_2d default 100 */
+    int unknown_cost_value;     /* costmap_2d default -1 */
+    int trinary_costmap;        /* costmap_2d default 1 */
+    int inflate_unknown;        /* costmap_2d default 0 */
+    double resolution;          /* metres per cell */
+    double inscribed_radius;    /* metres; from the costmap footprint (params.yaml:6 gives 0.25) */
+    double inflation_radius;    /* params.yaml:22, 0.5 */
+    double cost_scaling_factor; /* params.yaml:21, 8.0 */
+} pp_layer_params;
+pp_status pp_occupancy_from_image(pp_handle h, const uint8_t *image, uint32_t W, uint32_t H, double occupied_thresh,
+                                  double free_thresh, int negate);
+pp_status pp_occupancy_upload(pp_handle h, const int8_t *occ, uint32_t W, uint32_t H);
+pp_status pp_occupancy_update_rect(pp_handle h, uint32_t x0, uint32_t y0, uint32_t w, uint32_t hgt, const int8_t *src,
+                                   size_t src_pitch);
+pp_status pp_occupancy_download(pp_handle h, int8_t *occ_out);
+pp_status pp_costmap_from_occupancy(pp_handle h, const pp_layer_params *params);
 
 #ifdef __cplusplus
 }

@@ -39,6 +39,21 @@ def plan_params(motion_type=2, n_theta=72, minimum_turning_radius=0.84, cost_pen
                       max_on_approach_iterations)
 
 
+class LayerParams(C.Structure):
+    """port_layer_params (oracle/port.h): costmap_2d static + inflation layer configuration."""
+    _fields_ = [("track_unknown_space", C.c_int), ("lethal_threshold", C.c_int), ("unknown_cost_value", C.c_int),
+                ("trinary_costmap", C.c_int), ("inflate_unknown", C.c_int), ("resolution", C.c_double),
+                ("inscribed_radius", C.c_double), ("inflation_radius", C.c_double), ("cost_scaling_factor", C.c_double)]
+
+
+def layer_params(track_unknown_space=1, lethal_threshold=100, unknown_cost_value=-1, trinary_costmap=1,
+                 inflate_unknown=0, resolution=0.05, inscribed_radius=0.25, inflation_radius=0.5,
+                 cost_scaling_factor=8.0):
+    """Defaults: src/path_planner/config/params.yaml:6,15-22 plus costmap_2d's own defaults."""
+    return LayerParams(track_unknown_space, lethal_threshold, unknown_cost_value, trinary_costmap, inflate_unknown,
+                       resolution, inscribed_radius, inflation_radius, cost_scaling_factor)
+
+
 class E2E:
     """oracle/_ref/libpp_e2e.so: the reference search over the drop-in CollisionChecker (see e2e_harness.cpp)."""
 
@@ -116,6 +131,15 @@ class Port:
         L.port_extract_obstacles.argtypes = [u8p, C.c_uint32, C.c_uint32] + [C.c_double] * 8 + [f64p, C.c_uint32]
         L.port_radius_topk.argtypes = [f64p, C.c_uint32, f64p, C.c_uint32, C.c_double, C.c_uint32, u32p, f64p, u32p,
                                        u32p]
+        i8p = np.ctypeslib.ndpointer(np.int8, flags="C_CONTIGUOUS")
+        lp = C.POINTER(LayerParams)
+        L.port_occupancy_from_image.argtypes = [u8p, C.c_uint32, C.c_uint32, C.c_double, C.c_double, C.c_int, i8p]
+        L.port_static_layer.argtypes = [i8p, C.c_uint32, C.c_uint32, lp, u8p]
+        L.port_cell_inflation_radius.argtypes = [lp]
+        L.port_cell_inflation_radius.restype = C.c_uint32
+        L.port_inflation_cost_table.argtypes = [lp, u8p]
+        L.port_inflate_propagate.argtypes = [u8p, C.c_uint32, C.c_uint32, lp]
+        L.port_inflate_nearest.argtypes = [u8p, C.c_uint32, C.c_uint32, lp]
 
     def footprint_points(self, resolution, boundary, hole):
         b = np.ascontiguousarray(boundary, np.float32)
@@ -180,6 +204,38 @@ class Port:
         found = np.zeros(Q, np.uint32)
         self.lib.port_radius_topk(pts, len(pts), queries, Q, radius_arg, K, idx, d2, cnt, found)
         return idx, d2, cnt, found
+
+    # ---- ingestion (oracle/ingest.c) ----
+    def occupancy_from_image(self, image, occ_th, free_th, negate):
+        image = np.ascontiguousarray(image, np.uint8)
+        H, W = image.shape
+        out = np.empty((H, W), np.int8)
+        self.lib.port_occupancy_from_image(image, W, H, occ_th, free_th, int(negate), out)
+        return out
+
+    def static_layer(self, occ, params):
+        occ = np.ascontiguousarray(occ, np.int8)
+        H, W = occ.shape
+        out = np.empty((H, W), np.uint8)
+        self.lib.port_static_layer(occ, W, H, C.byref(params), out)
+        return out
+
+    def inflation_cost_table(self, params):
+        R = int(self.lib.port_cell_inflation_radius(C.byref(params)))
+        tab = np.zeros((R + 2, R + 2), np.uint8)
+        self.lib.port_inflation_cost_table(C.byref(params), tab)
+        return R, tab
+
+    def inflate(self, static_cost, params, how="nearest"):
+        """how = "nearest" (the definition the GPU path is held to) or "propagate" (costmap_2d's queue)."""
+        m = np.ascontiguousarray(static_cost, np.uint8).copy()
+        H, W = m.shape
+        fn = self.lib.port_inflate_nearest if how == "nearest" else self.lib.port_inflate_propagate
+        fn(m, W, H, C.byref(params))
+        return m
+
+    def costmap_from_occupancy(self, occ, params, how="nearest"):
+        return self.inflate(self.static_layer(occ, params), params, how)
 
 
 class Ref:

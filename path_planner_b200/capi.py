@@ -21,6 +21,8 @@ SYMBOLS = [
     "pp_se2_volume_stats", "pp_footprint_cost_batch", "pp_heuristic_build", "pp_heuristic_ptr", "pp_heuristic_stats", "pp_heuristic_build_noalloc", "pp_plan",
     "pp_obstacles_extract", "pp_radius_topk", "pp_comm_unique_id", "pp_comm_init", "pp_se2_volume_allgather", "pp_se2_volume_reserve",
     "pp_se2_volume_ipc_export", "pp_se2_volume_ipc_open", "pp_se2_volume_set_push", "pp_se2_volume_set_rows",
+    "pp_occupancy_from_image", "pp_occupancy_upload", "pp_occupancy_update_rect", "pp_occupancy_download",
+    "pp_costmap_from_occupancy",
 ]
 
 _vp = C.c_void_p
@@ -43,6 +45,19 @@ class PlanParams(C.Structure):
         return cls(motion_type, n_theta, minimum_turning_radius, cost_penalty, change_penalty, non_straight_penalty,
                    reverse_penalty, analytic_expansion_ratio, analytic_expansion_tolerance, tolerance, max_iterations,
                    max_on_approach_iterations)
+
+
+class LayerParams(C.Structure):
+    """pp_layer_params; defaults from the reference's config/params.yaml:6,15-22 and costmap_2d's own."""
+    _fields_ = [("track_unknown_space", C.c_int), ("lethal_threshold", C.c_int), ("unknown_cost_value", C.c_int),
+                ("trinary_costmap", C.c_int), ("inflate_unknown", C.c_int), ("resolution", C.c_double),
+                ("inscribed_radius", C.c_double), ("inflation_radius", C.c_double), ("cost_scaling_factor", C.c_double)]
+
+    @classmethod
+    def make(cls, track_unknown_space=1, lethal_threshold=100, unknown_cost_value=-1, trinary_costmap=1,
+             inflate_unknown=0, resolution=0.05, inscribed_radius=0.25, inflation_radius=0.5, cost_scaling_factor=8.0):
+        return cls(track_unknown_space, lethal_threshold, unknown_cost_value, trinary_costmap, inflate_unknown,
+                   resolution, inscribed_radius, inflation_radius, cost_scaling_factor)
 
 
 class PPError(RuntimeError):
@@ -102,6 +117,11 @@ def load():
     L.pp_se2_volume_ipc_open.argtypes = [_vp, _vp, C.c_int, C.c_int]
     L.pp_se2_volume_set_push.argtypes = [_vp, C.c_int]
     L.pp_se2_volume_set_rows.argtypes = [_vp, _u32, _u32]
+    L.pp_occupancy_from_image.argtypes = [_vp, _vp, _u32, _u32, C.c_double, C.c_double, C.c_int]
+    L.pp_occupancy_upload.argtypes = [_vp, _vp, _u32, _u32]
+    L.pp_occupancy_update_rect.argtypes = [_vp, _u32, _u32, _u32, _u32, _vp, C.c_size_t]
+    L.pp_occupancy_download.argtypes = [_vp, _vp]
+    L.pp_costmap_from_occupancy.argtypes = [_vp, C.POINTER(LayerParams)]
     _lib = L
     return L
 
@@ -197,6 +217,34 @@ class Handle:
         out = np.empty((self.H, self.W), np.uint8)
         self._ck(self.L.pp_costmap_download(self.h, _ptr(out)))
         return out
+
+    # N2 ingestion
+    def occupancy_from_image(self, image, occupied_thresh, free_thresh, negate):
+        assert image.dtype == np.uint8 and image.ndim == 2 and image.flags.c_contiguous
+        self.occ_H, self.occ_W = image.shape
+        self._ck(self.L.pp_occupancy_from_image(self.h, _ptr(image), self.occ_W, self.occ_H, occupied_thresh,
+                                                free_thresh, int(negate)))
+
+    def occupancy_upload(self, occ):
+        assert occ.dtype == np.int8 and occ.ndim == 2 and occ.flags.c_contiguous
+        self.occ_H, self.occ_W = occ.shape
+        self._ck(self.L.pp_occupancy_upload(self.h, _ptr(occ), self.occ_W, self.occ_H))
+
+    def occupancy_update_rect(self, x0, y0, patch):
+        assert patch.dtype == np.int8 and patch.ndim == 2
+        patch = np.ascontiguousarray(patch)
+        hgt, w = patch.shape
+        self._ck(self.L.pp_occupancy_update_rect(self.h, x0, y0, w, hgt, _ptr(patch), w))
+
+    def occupancy_download(self):
+        out = np.empty((self.occ_H, self.occ_W), np.int8)
+        self._ck(self.L.pp_occupancy_download(self.h, _ptr(out)))
+        return out
+
+    def costmap_from_occupancy(self, params=None):
+        p = params if params is not None else LayerParams.make()
+        self._ck(self.L.pp_costmap_from_occupancy(self.h, C.byref(p)))
+        self.H, self.W = self.occ_H, self.occ_W
 
     # footprint
     def footprint_from_boundary(self, resolution, boundary, hole):

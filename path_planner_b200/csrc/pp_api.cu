@@ -21,6 +21,21 @@ pp_status pp_fail(pp_handle h, pp_status code, const char *fmt, ...)
     return code;
 }
 
+pp_status pp_ensure_stage(pp_handle h, size_t bytes)
+{
+    if (bytes <= h->stage_cap)
+        return PP_OK;
+    // the staging buffer may still be the source of an in-flight copy
+    PP_CUDA(h, cudaStreamSynchronize(h->stream));
+    if (h->h_stage)
+        PP_CUDA(h, cudaFreeHost(h->h_stage));
+    h->h_stage = nullptr;
+    h->stage_cap = 0;
+    PP_CUDA(h, cudaHostAlloc(reinterpret_cast<void **>(&h->h_stage), bytes, cudaHostAllocDefault));
+    h->stage_cap = bytes;
+    return PP_OK;
+}
+
 extern "C" {
 
 const char *pp_version(void) { return "pp_b200 0.1 (sm_100a)"; }
@@ -60,6 +75,9 @@ pp_status pp_destroy(pp_handle h)
     pp_se2_plan_free(h);
     pp_comm_destroy(h);
     cudaFree(h->d_cost);
+    cudaFree(h->d_occ);
+    cudaFree(h->d_infl);
+    cudaFree(h->d_img);
     cudaFree(h->d_flush);
     cudaFree(h->d_fp);
     cudaFree(h->d_vol);
@@ -149,21 +167,6 @@ pp_status pp_launch_count(pp_handle h, uint64_t *count_out)
 
 // ---- K0 ---------------------------------------------------------------------------------------
 
-static pp_status ensure_stage(pp_handle h, size_t bytes)
-{
-    if (bytes <= h->stage_cap)
-        return PP_OK;
-    // the staging buffer may still be the source of an in-flight copy
-    PP_CUDA(h, cudaStreamSynchronize(h->stream));
-    if (h->h_stage)
-        PP_CUDA(h, cudaFreeHost(h->h_stage));
-    h->h_stage = nullptr;
-    h->stage_cap = 0;
-    PP_CUDA(h, cudaHostAlloc(reinterpret_cast<void **>(&h->h_stage), bytes, cudaHostAllocDefault));
-    h->stage_cap = bytes;
-    return PP_OK;
-}
-
 pp_status pp_costmap_upload(pp_handle h, const uint8_t *host, uint32_t W, uint32_t H, int host_is_pinned)
 {
     if (!h)
@@ -183,7 +186,7 @@ pp_status pp_costmap_upload(pp_handle h, const uint8_t *host, uint32_t W, uint32
     const uint8_t *src = host;
     if (!host_is_pinned)
     {
-        pp_status s = ensure_stage(h, bytes);
+        pp_status s = pp_ensure_stage(h, bytes);
         if (s != PP_OK)
             return s;
         // the previous async copy out of the staging buffer must be done before it is overwritten
@@ -208,7 +211,7 @@ pp_status pp_costmap_update_rect(pp_handle h, uint32_t x0, uint32_t y0, uint32_t
                "pp_costmap_update_rect: rect (%u,%u)+(%u,%u) outside %ux%u", x0, y0, w, hgt, h->W, h->H);
     PP_CUDA(h, cudaSetDevice(h->device));
     const size_t bytes = static_cast<size_t>(w) * hgt;
-    pp_status s = ensure_stage(h, std::max(bytes, static_cast<size_t>(h->W) * h->H));
+    pp_status s = pp_ensure_stage(h, std::max(bytes, static_cast<size_t>(h->W) * h->H));
     if (s != PP_OK)
         return s;
     PP_CUDA(h, cudaStreamSynchronize(h->stream));

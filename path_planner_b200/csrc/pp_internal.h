@@ -77,6 +77,19 @@ struct pp_ctx
     uint32_t *d_topk_cnt = nullptr;
     size_t topk_cap = 0, topk_q_cap = 0;
 
+    // N2 ingestion
+    int8_t *d_occ = nullptr;
+    size_t occ_cap = 0;
+    uint32_t occ_W = 0, occ_H = 0;
+    bool occ_dirty = false, occ_all = false;  // a rectangle / the whole grid changed since the last costmap
+    uint32_t occ_x0 = 0, occ_y0 = 0, occ_x1 = 0, occ_y1 = 0;  // half-open
+    uint8_t *d_img = nullptr;  // map image as uploaded
+    size_t img_cap = 0;
+    uint8_t *d_infl = nullptr;  // inflation cost by squared cell distance, 0..R*R
+    size_t infl_cap = 0;
+    pp_layer_params layer = {};
+    bool layer_valid = false;
+
     // multi-GPU
     uint8_t *peer_vol[8] = {};  // peer_vol[r] = rank r's volume mapped here (own volume at [rank]); null if not opened
     int n_peer = 0;             // world size of the mapping
@@ -124,6 +137,8 @@ inline cudaError_t pp_reserve(T *&ptr, size_t &cap, size_t need)
     return e;
 }
 
+// pinned staging buffer of at least `bytes` (pp_api.cu)
+pp_status pp_ensure_stage(pp_handle h, size_t bytes);
 // implemented per kernel file
 pp_status pp_se2_launch(pp_handle h, uint32_t x0, uint32_t y0, uint32_t x1, uint32_t y1);
 void pp_se2_plan_free(pp_handle h);
