@@ -140,6 +140,14 @@ PLAN_SCENES = {
 }
 
 
+def occupancy_of(cost):
+    """nav_msgs/OccupancyGrid data whose static layer has the bench costmap's obstacles and unknown cells."""
+    occ = np.zeros(cost.shape, np.int8)
+    occ[cost == 254] = 100
+    occ[cost == 255] = -1
+    return occ
+
+
 def plan_scene(sc):
     from path_planner_b200.synth import make_costmap
     pockets = [(int(sc["start"][0] / RES), int(sc["start"][1] / RES), 25), (int(sc["goal"][0] / RES), int(sc["goal"][1] / RES), 25)]
@@ -437,6 +445,37 @@ def main():
             line["plan"][name] = {"ms": r["tables_ms"] + r["search_ms"], "tables_ms": r["tables_ms"], "search_ms": r["search_ms"],
                                   "iterations": r["iterations"], "path_poses": int(len(r["path"])), "found": bool(r["ok"])}
         hp.close()
+        # N2 ingestion on the same map: occupancy grid -> static layer + inflation -> costmap, on its own handle
+        hi = capi.Handle(local_rank)
+        occ = occupancy_of(cost)
+        lps = [capi.LayerParams.make(resolution=RES), capi.LayerParams.make(resolution=RES, cost_scaling_factor=8.0 + 1e-9)]
+        for k in range(3):
+            hi.occupancy_upload(occ)
+            hi.costmap_from_occupancy(lps[k % 2])
+        hi.sync()
+        t = time.perf_counter()
+        for k in range(5):
+            hi.occupancy_upload(occ)
+            hi.costmap_from_occupancy(lps[0])
+        hi.sync()
+        ing_e2e = 1e3 * (time.perf_counter() - t) / 5
+        hi.timer_start()
+        for k in range(10):  # a changed parameter forces the full recompute without a new upload
+            hi.costmap_from_occupancy(lps[(k + 1) % 2])
+        ing_ms = hi.timer_stop() / 10
+        patch = np.ascontiguousarray(occ[1000:1256, 2000:2256])
+        hi.costmap_from_occupancy(lps[0])
+        hi.sync()
+        t = time.perf_counter()
+        for k in range(20):
+            hi.occupancy_update_rect(2000, 1000, patch)
+            hi.costmap_from_occupancy(lps[0])
+        hi.sync()
+        line["ingest"] = {"full_recompute_ms": ing_ms, "e2e_ms_with_upload": ing_e2e,
+                          "rect_256x256_e2e_ms": 1e3 * (time.perf_counter() - t) / 20, "map": f"{W}x{H}",
+                          "inflation_cells": 10, "algorithmic_bytes": 2 * W * H,
+                          "note": "full_recompute_ms includes the 101-byte cost-table upload that a parameter change triggers"}
+        hi.close()
         from path_planner_b200.synth import make_teb_scene
         pts, poses = make_teb_scene(10000, 100, seed=0)
         h.radius_topk(pts, poses, 0.9574, 10)
@@ -461,6 +500,11 @@ def main():
                 pts, poses = make_teb_scene(10000, 100, seed=0)
                 ref.radius_topk(pts, poses, 0.9574, 10)
                 line["cpu_baseline"]["teb_us_per_round"] = 1e6 * (ref.last_build_seconds + ref.last_query_seconds)
+                port = oracle.load_port()
+                olp = oracle.layer_params(resolution=RES)
+                t = time.perf_counter()
+                port.costmap_from_occupancy(occupancy_of(cost), olp, "propagate")  # costmap_2d's algorithm restated, 1 thread
+                line["cpu_baseline"]["ingest_ms"] = 1e3 * (time.perf_counter() - t)
                 line["cpu_baseline"]["plan"] = {}
                 for name, sc in PLAN_SCENES.items():  # the unmodified reference planner, 1 thread
                     ok, path, it, ms = ref.plan(plan_scene(sc), RES, sc["boundary"], True, sc["start"], sc["goal"], sc["params"])
