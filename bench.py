@@ -485,6 +485,14 @@ def main():
             h.radius_topk(None, poses, 0.9574, 10)
         line["teb"] = {"us_per_round_e2e": 1e6 * (time.perf_counter() - t) / rounds,
                        "workload": "100 poses x 10000 points, K=10, host buffers in and out"}
+        # N3: errors + numeric Jacobians of all obstacle edges of one optimiser iteration (association on the device)
+        poses3 = np.ascontiguousarray(np.concatenate([poses, 0.6 * np.cos(poses[:, :1])], axis=1))
+        h.robot_model_set([0.72, 0.50])
+        h.obstacle_edges(poses3, 10)
+        t = time.perf_counter()
+        for _ in range(rounds):
+            h.obstacle_edges(poses3, 10)
+        line["teb"]["edges_us_per_iteration_e2e"] = 1e6 * (time.perf_counter() - t) / rounds
 
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         cores = os.cpu_count() or 1
@@ -500,6 +508,14 @@ def main():
                 pts, poses = make_teb_scene(10000, 100, seed=0)
                 ref.radius_topk(pts, poses, 0.9574, 10)
                 line["cpu_baseline"]["teb_us_per_round"] = 1e6 * (ref.last_build_seconds + ref.last_query_seconds)
+                teb_ref = oracle.load_teb_ref()
+                if teb_ref is not None:  # the reference's own EdgeObstacle + g2o-style numeric Jacobian, 1 thread
+                    idx, d2, cnt, found = ref.radius_topk(pts, poses, 0.9574, 10)
+                    poses3 = np.ascontiguousarray(np.concatenate([poses, 0.6 * np.cos(poses[:, :1])], axis=1))
+                    t = time.perf_counter()
+                    for _ in range(20):
+                        teb_ref.obstacle_edges(poses3, pts, idx, cnt, [0.72, 0.50], [0.1, 0.05, 0.2, 0.1])
+                    line["cpu_baseline"]["teb_edges_us_per_iteration"] = 1e6 * (time.perf_counter() - t) / 20
                 port = oracle.load_port()
                 olp = oracle.layer_params(resolution=RES)
                 t = time.perf_counter()

@@ -202,6 +202,33 @@ pp_status pp_obstacles_extract(pp_handle h, double resolution, double origin_x, 
 pp_status pp_radius_topk(pp_handle h, const double *pts_xy, uint32_t N, const double *queries_xy, uint32_t Q,
                          double radius_arg, uint32_t K, uint32_t *idx_out, double *d2_out, uint32_t *cnt_out);
 
+/* ---- N3: TEB obstacle edges, batched (the step after K3) ---------------------
+ * pp_robot_model_set replaces RobotModelHelper::createRobotModel
+ * (src/path_follower/src/teb_path_follower/robot_model.cpp:68-95): 1 number = circle radius, 2 =
+ * width and height of a rectangle, an even count >= 6 = polygon vertices x0,y0,x1,y1,...; the
+ * inscribed / circumscribed radii of PolygonRobotModel::computeRadius (:15-37) are returned.
+ * pp_obstacle_edges evaluates, for every (pose q, kept obstacle k) of the association that the last
+ * pp_radius_topk left on the device (same Q and K), what g2o evaluates per EdgeObstacle and
+ * Levenberg-Marquardt iteration (edges built at teb_optimizer.cpp:283-313): computeError()
+ * (g2o_edges/edge_obstacle.hpp:19-26 -> RobotModel::distanceToPoint, robot_model.cpp:3-6,39-66,
+ * and two penaltyBelow terms, commons.h:53-62) into error_out[Q][K][2], and the central-difference
+ * Jacobian g2o computes for an edge without an analytic one (step 1e-9 per pose dimension through
+ * Vertex2E::oplusImpl, commons.cpp:75-80) into jacobian_out[Q][K][2][3] (may be NULL). Slots
+ * k >= cnt[q] are zero. Poses are (x, y, theta) doubles. Floating point: agrees with the
+ * reference to 1e-12 (errors) and 1e-6 (Jacobians, whose step amplifies last-bit differences of
+ * hypot/sincos by 5e8); tests/test_gpu_teb_edges.py states the tolerances. */
+#define PP_ROBOT_MAX_VERTS 32
+typedef struct pp_obstacle_edge_params
+{
+    double obstacle_collision_dist;   /* commons.h:219, 0.1 */
+    double margin_obstacle_collision; /* commons.h:220, 0.05 */
+    double obstacle_inflation_dist;   /* commons.h:221, 0.2 */
+    double margin_obstacle_inflation; /* commons.h:222, 0.1 */
+} pp_obstacle_edge_params;
+pp_status pp_robot_model_set(pp_handle h, const double *numbers, uint32_t n, double *inscribed_out, double *circum_out);
+pp_status pp_obstacle_edges(pp_handle h, const double *poses_xyt, uint32_t Q, uint32_t K,
+                            const pp_obstacle_edge_params *params, double *error_out, double *jacobian_out);
+
 /* ---- multi-GPU: heading-sharded volume --------------------------------------------------------
  * No counterpart in the reference (single process, single thread). Rank g of `world` builds bins
  * [g*n_theta/world, (g+1)*n_theta/world) and pp_se2_volume_allgather exchanges the slabs in place

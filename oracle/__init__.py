@@ -140,6 +140,9 @@ class Port:
         L.port_inflation_cost_table.argtypes = [lp, u8p]
         L.port_inflate_propagate.argtypes = [u8p, C.c_uint32, C.c_uint32, lp]
         L.port_inflate_nearest.argtypes = [u8p, C.c_uint32, C.c_uint32, lp]
+        L.port_robot_model.argtypes = [f64p, C.c_int, f64p, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]
+        L.port_obstacle_edges.argtypes = [f64p, C.c_uint32, f64p, u32p, u32p, C.c_uint32, f64p, C.c_int, f64p, f64p,
+                                          C.c_void_p]
 
     def footprint_points(self, resolution, boundary, hole):
         b = np.ascontiguousarray(boundary, np.float32)
@@ -236,6 +239,65 @@ class Port:
 
     def costmap_from_occupancy(self, occ, params, how="nearest"):
         return self.inflate(self.static_layer(occ, params), params, how)
+
+    # ---- obstacle edges (oracle/teb_edges.c) ----
+    def robot_model(self, numbers):
+        """-> (vertices[nv,2] (empty for a circle), inscribed radius, circumscribed radius)"""
+        numbers = np.ascontiguousarray(numbers, np.float64)
+        verts = np.zeros((64, 2), np.float64)
+        ri, rc = C.c_double(0), C.c_double(0)
+        nv = self.lib.port_robot_model(numbers, len(numbers), verts, 64, C.byref(ri), C.byref(rc))
+        if nv < 0:
+            raise ValueError("bad robot model")
+        return verts[:nv].copy(), ri.value, rc.value
+
+    def obstacle_edges(self, poses, pts, idx, cnt, robot, info4, jacobian=True):
+        return _obstacle_edges(self.lib.port_obstacle_edges, poses, pts, idx, cnt, robot, info4, jacobian)
+
+
+def _obstacle_edges(fn, poses, pts, idx, cnt, robot, info4, jacobian):
+    poses = np.ascontiguousarray(poses, np.float64)
+    pts = np.ascontiguousarray(pts, np.float64)
+    idx = np.ascontiguousarray(idx, np.uint32)
+    cnt = np.ascontiguousarray(cnt, np.uint32)
+    robot = np.ascontiguousarray(robot, np.float64)
+    info4 = np.ascontiguousarray(info4, np.float64)
+    Q, K = idx.shape
+    err = np.zeros((Q, K, 2), np.float64)
+    jac = np.zeros((Q, K, 2, 3), np.float64) if jacobian else None
+    rc = fn(poses, Q, pts, idx, cnt, K, robot, len(robot), info4, err, _opt(jac, np.float64))
+    if rc != 0:
+        raise ValueError("bad robot model")
+    return err, jac
+
+
+class TebRef:
+    """oracle/_ref/libpp_teb_ref.so: the reference's own robot model and EdgeObstacle (teb_ref_harness.cpp)."""
+
+    def __init__(self):
+        path = os.path.join(_HERE, "_ref", "libpp_teb_ref.so")
+        if not os.path.exists(path):
+            raise FileNotFoundError(path)
+        self.lib = C.CDLL(path)
+        self.lib.teb_ref_robot_radii.argtypes = [f64p, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]
+        self.lib.teb_ref_obstacle_edges.argtypes = [f64p, C.c_uint32, f64p, u32p, u32p, C.c_uint32, f64p, C.c_int, f64p,
+                                                    f64p, C.c_void_p]
+
+    def robot_radii(self, numbers):
+        numbers = np.ascontiguousarray(numbers, np.float64)
+        ri, rc = C.c_double(0), C.c_double(0)
+        self.lib.teb_ref_robot_radii(numbers, len(numbers), C.byref(ri), C.byref(rc))
+        return ri.value, rc.value
+
+    def obstacle_edges(self, poses, pts, idx, cnt, robot, info4, jacobian=True):
+        return _obstacle_edges(self.lib.teb_ref_obstacle_edges, poses, pts, idx, cnt, robot, info4, jacobian)
+
+
+def load_teb_ref():
+    try:
+        return TebRef()
+    except (FileNotFoundError, OSError):
+        return None
 
 
 class Ref:

@@ -60,6 +60,12 @@ int port_inflation_cost_table(const port_layer_params *p, uint8_t *table);
 int port_inflate_propagate(uint8_t *master, uint32_t W, uint32_t H, const port_layer_params *p);
 int port_inflate_nearest(uint8_t *master, uint32_t W, uint32_t H, const port_layer_params *p);
 
+/* ---- obstacle edges after the TEB association (oracle/teb_edges.c) ---- */
+int port_robot_model(const double *numbers, int n, double *verts_xy, int max_verts, double *inscribed, double *circum);
+int port_obstacle_edges(const double *poses_xyt, uint32_t Q, const double *pts_xy, const uint32_t *idx,
+                        const uint32_t *cnt, uint32_t K, const double *robot_numbers, int n_robot, const double *info4,
+                        double *err_out, double *jac_out);
+
 #ifdef __cplusplus
 }
 #endif

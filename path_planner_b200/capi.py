@@ -22,7 +22,7 @@ SYMBOLS = [
     "pp_obstacles_extract", "pp_radius_topk", "pp_comm_unique_id", "pp_comm_init", "pp_se2_volume_allgather", "pp_se2_volume_reserve",
     "pp_se2_volume_ipc_export", "pp_se2_volume_ipc_open", "pp_se2_volume_set_push", "pp_se2_volume_set_rows",
     "pp_occupancy_from_image", "pp_occupancy_upload", "pp_occupancy_update_rect", "pp_occupancy_download",
-    "pp_costmap_from_occupancy",
+    "pp_costmap_from_occupancy", "pp_robot_model_set", "pp_obstacle_edges",
 ]
 
 _vp = C.c_void_p
@@ -58,6 +58,17 @@ class LayerParams(C.Structure):
              inflate_unknown=0, resolution=0.05, inscribed_radius=0.25, inflation_radius=0.5, cost_scaling_factor=8.0):
         return cls(track_unknown_space, lethal_threshold, unknown_cost_value, trinary_costmap, inflate_unknown,
                    resolution, inscribed_radius, inflation_radius, cost_scaling_factor)
+
+
+class ObstacleEdgeParams(C.Structure):
+    """pp_obstacle_edge_params; defaults from FollowerInfo (teb_path_follower/commons.h:219-222)."""
+    _fields_ = [("obstacle_collision_dist", C.c_double), ("margin_obstacle_collision", C.c_double),
+                ("obstacle_inflation_dist", C.c_double), ("margin_obstacle_inflation", C.c_double)]
+
+    @classmethod
+    def make(cls, obstacle_collision_dist=0.1, margin_obstacle_collision=0.05, obstacle_inflation_dist=0.2,
+             margin_obstacle_inflation=0.1):
+        return cls(obstacle_collision_dist, margin_obstacle_collision, obstacle_inflation_dist, margin_obstacle_inflation)
 
 
 class PPError(RuntimeError):
@@ -122,6 +133,8 @@ def load():
     L.pp_occupancy_update_rect.argtypes = [_vp, _u32, _u32, _u32, _u32, _vp, C.c_size_t]
     L.pp_occupancy_download.argtypes = [_vp, _vp]
     L.pp_costmap_from_occupancy.argtypes = [_vp, C.POINTER(LayerParams)]
+    L.pp_robot_model_set.argtypes = [_vp, _vp, _u32, C.POINTER(C.c_double), C.POINTER(C.c_double)]
+    L.pp_obstacle_edges.argtypes = [_vp, _vp, _u32, _u32, C.POINTER(ObstacleEdgeParams), _vp, _vp]
     _lib = L
     return L
 
@@ -352,6 +365,24 @@ class Handle:
         self._ck(self.L.pp_radius_topk(self.h, _ptr(pts), N, _ptr(queries), Q, radius_arg, K, _ptr(idx), _ptr(d2),
                                        _ptr(cnt)))
         return idx, d2, cnt
+
+    # N3
+    def robot_model_set(self, numbers):
+        """-> (inscribed radius, circumscribed radius)"""
+        numbers = np.ascontiguousarray(numbers, np.float64)
+        ri, rc = C.c_double(0), C.c_double(0)
+        self._ck(self.L.pp_robot_model_set(self.h, _ptr(numbers), len(numbers), C.byref(ri), C.byref(rc)))
+        return ri.value, rc.value
+
+    def obstacle_edges(self, poses_xyt, K, params=None, jacobian=True):
+        """Errors [Q,K,2] and Jacobians [Q,K,2,3] for the association of the last radius_topk."""
+        poses = np.ascontiguousarray(poses_xyt, np.float64)
+        Q = len(poses)
+        p = params if params is not None else ObstacleEdgeParams.make()
+        err = np.zeros((Q, K, 2), np.float64)
+        jac = np.zeros((Q, K, 2, 3), np.float64) if jacobian else None
+        self._ck(self.L.pp_obstacle_edges(self.h, _ptr(poses), Q, K, C.byref(p), _ptr(err), _ptr(jac)))
+        return err, jac
 
     # multi-GPU
     def comm_init(self, uid_bytes, rank, world):

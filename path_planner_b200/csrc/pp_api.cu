@@ -78,6 +78,8 @@ pp_status pp_destroy(pp_handle h)
     cudaFree(h->d_occ);
     cudaFree(h->d_infl);
     cudaFree(h->d_img);
+    cudaFree(h->d_poses);
+    cudaFree(h->d_edge_out);
     cudaFree(h->d_flush);
     cudaFree(h->d_fp);
     cudaFree(h->d_vol);

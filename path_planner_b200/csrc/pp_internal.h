@@ -90,6 +90,16 @@ struct pp_ctx
     pp_layer_params layer = {};
     bool layer_valid = false;
 
+    // N3 obstacle edges
+    int robot_nv = -1;  // -1 unset, 0 circle, else polygon vertex count
+    double robot_verts[2 * PP_ROBOT_MAX_VERTS] = {};
+    double robot_inscribed = 0.0, robot_circum = 0.0;
+    uint32_t topk_Q = 0, topk_K = 0;  // shape of the association left on the device by pp_radius_topk
+    double *d_poses = nullptr;
+    size_t poses_cap = 0;
+    double *d_edge_out = nullptr;
+    size_t edge_cap = 0;
+
     // multi-GPU
     uint8_t *peer_vol[8] = {};  // peer_vol[r] = rank r's volume mapped here (own volume at [rank]); null if not opened
     int n_peer = 0;             // world size of the mapping

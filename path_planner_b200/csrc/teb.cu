@@ -356,6 +356,8 @@ pp_status pp_radius_topk(pp_handle h, const double *pts_xy, uint32_t N, const do
                                                         h->d_topk_cnt);
     h->launches++;
     PP_CUDA(h, cudaGetLastError());
+    h->topk_Q = Q;
+    h->topk_K = K;
     PP_CUDA(h, cudaMemcpyAsync(idx_out, h->d_topk_idx, out_n * sizeof(uint32_t), cudaMemcpyDeviceToHost, h->stream));
     PP_CUDA(h, cudaMemcpyAsync(d2_out, h->d_topk_d2, out_n * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
     PP_CUDA(h, cudaMemcpyAsync(cnt_out, h->d_topk_cnt, Q * sizeof(uint32_t), cudaMemcpyDeviceToHost, h->stream));
