@@ -37,8 +37,17 @@
 
 namespace
 {
-constexpr int FT_W = 64, FT_H = 16, FT_THREADS = 384;
-constexpr int CTAS_PER_SM = 2;
+#ifndef PP_FT_THREADS
+#define PP_FT_THREADS 384
+#endif
+#ifndef PP_CTAS_PER_SM
+#define PP_CTAS_PER_SM 2
+#endif
+#ifndef PP_FT_H
+#define PP_FT_H 16
+#endif
+constexpr int FT_W = 64, FT_H = PP_FT_H, FT_THREADS = PP_FT_THREADS;
+constexpr int CTAS_PER_SM = PP_CTAS_PER_SM;
 constexpr int MAX_TABLES = 12;
 constexpr int MAX_T_PER_LAUNCH = 160;
 constexpr int MAX_LIST_WORDS = 6400;
@@ -102,9 +111,16 @@ struct FastArgs
     uint32_t t_first, n_t;
     uint16_t list_off[MAX_T_PER_LAUNCH][4];
     uint16_t list_len[MAX_T_PER_LAUNCH][4];
+    // (bin, class) pairs of this launch with the SAME offset set form a chain in bin order (for a
+    // centrally symmetric footprint bins t and t + n_theta/2 do): link = bin | class << 8, NO_LINK at the ends
+    uint16_t chain_prev[MAX_T_PER_LAUNCH][4];
+    uint16_t chain_next[MAX_T_PER_LAUNCH][4];
     alignas(16) uint32_t lists[MAX_LIST_WORDS];  // byte offsets into shared memory, relative to the thread's base
 };
+static_assert(MAX_T_PER_LAUNCH <= 255, "chain links keep the bin in 8 bits");
 static_assert(sizeof(FastArgs) < 32764, "kernel parameter block too large");
+
+constexpr uint32_t NO_LINK = 0xFFFFu;
 
 __device__ __forceinline__ uint32_t bytemax4(uint32_t a, uint32_t b)
 {
@@ -114,7 +130,8 @@ __device__ __forceinline__ uint32_t bytemax4(uint32_t a, uint32_t b)
 }
 
 constexpr int QPT = 8;                                     // quads (4 cells along x) per thread and bin
-static_assert(FT_W / 4 * FT_H / QPT / 32 == 1, "a work unit is one bin of a tile: one warp, QPT quads per thread");
+constexpr int UNITS_PER_BIN = FT_W / 4 * FT_H / QPT / 32;  // a work unit is 16 rows of one bin of a tile: one warp, QPT quads per thread
+static_assert(UNITS_PER_BIN * 16 == FT_H, "tile height must be a multiple of 16");
 
 // row of quad j of a thread, relative to the thread's first row
 __host__ __device__ constexpr int quad_row(int j) { return j; }
@@ -159,7 +176,7 @@ __device__ __forceinline__ void run_units(const FastArgs &a, const uint32_t *sm,
     const bool in_x = gx < W;
     const size_t plane = static_cast<size_t>(a.W) * a.H;
     const size_t rs = a.W;
-    const uint32_t n_units = a.n_t;
+    const uint32_t n_units = UNITS_PER_BIN * a.n_t;
     while (true)
     {
         uint32_t unit = 0;
@@ -168,11 +185,22 @@ __device__ __forceinline__ void run_units(const FastArgs &a, const uint32_t *sm,
         unit = __shfl_sync(0xffffffffu, unit, 0);
         if (unit >= n_units)
             break;
-        const uint32_t t = unit;
+        const uint32_t t = unit / UNITS_PER_BIN;
         const uint32_t cls = s_cls[t];
         if (cls == 255u)
             continue;
-        const int row0 = 8 * (lane >> 4);
+        // Bins whose offset sets coincide on this tile have identical outputs: the first of them
+        // evaluates, and stores to all (warp-uniform walks over the host-built chains).
+        bool evaluated_earlier = false;
+        for (uint32_t link = a.chain_prev[t][cls]; link != NO_LINK; link = a.chain_prev[link & 0xFFu][link >> 8])
+            if (s_cls[link & 0xFFu] == (link >> 8))
+            {
+                evaluated_earlier = true;
+                break;
+            }
+        if (evaluated_earlier)
+            continue;
+        const int row0 = 16 * static_cast<int>(unit % UNITS_PER_BIN) + 8 * (lane >> 4);
         const uint8_t *smb = reinterpret_cast<const uint8_t *>(sm + row0 * PW + q);
         const int gy = ty0 + row0;
         uint8_t *out = a.vol + plane * (a.t_first + t) + static_cast<size_t>(gy) * a.W + gx;
@@ -215,27 +243,61 @@ __device__ __forceinline__ void run_units(const FastArgs &a, const uint32_t *sm,
                 ua[j] = p1[quad_row(j) * PW];
             accumulate(odd, even, ua, ua);
         }
-        if (in_x)
-        {
 #pragma unroll
-            for (int j = 0; j < QPT; ++j)
-                if (gy + quad_row(j) < H)
-                {
-                    const uint32_t word = __byte_perm(even[j], odd[j], 0x7351);
-                    uint8_t *dst = out + quad_row(j) * rs;
-                    *reinterpret_cast<uint32_t *>(dst) = word;
-                    for (int p = 0; p < a.n_peers; ++p)  // peer volumes over NVLink
-                        *reinterpret_cast<uint32_t *>(dst + a.peer_delta[p]) = word;
-                }
+        for (int j = 0; j < QPT; ++j)
+            odd[j] = __byte_perm(even[j], odd[j], 0x7351);
+        uint32_t link = a.chain_next[t][cls];
+        while (true)
+        {
+            if (in_x)
+            {
+#pragma unroll
+                for (int j = 0; j < QPT; ++j)
+                    if (gy + quad_row(j) < H)
+                    {
+                        uint8_t *dst = out + quad_row(j) * rs;
+                        *reinterpret_cast<uint32_t *>(dst) = odd[j];
+                        for (int p = 0; p < a.n_peers; ++p)  // peer volumes over NVLink
+                            *reinterpret_cast<uint32_t *>(dst + a.peer_delta[p]) = odd[j];
+                    }
+            }
+            // next bin of the chain that is in the matching class on this tile
+            uint32_t t2 = NO_LINK;
+            while (link != NO_LINK && t2 == NO_LINK)
+            {
+                const uint32_t lt = link & 0xFFu, lc = link >> 8;
+                link = a.chain_next[lt][lc];
+                if (s_cls[lt] == lc)
+                    t2 = lt;
+            }
+            if (t2 == NO_LINK)
+                break;
+            out = a.vol + plane * (a.t_first + t2) + static_cast<size_t>(gy) * a.W + gx;
         }
     }
 }
 
-// Table build. Recipes and levels are compile-time constants (forced through template arguments),
-// so for every level both passes unroll over the tables of that level and all shared-memory loads
-// of a word are issued before the first dependent operation.
+// Shared-memory geometry, fixed by the row pitch so that every table address is an immediate:
+// PW = 22 words holds a halo of up to 10 cells, PW = 26 up to 15. The tables sit between two guard
+// regions, so a recipe may read a few rows before the first / after the last table without a bounds
+// test: such words only feed entries whose brick leaves the staged region, and those are never
+// sampled (a sample's brick lies inside the offset set, which lies inside the halo).
+template <int PW>
+struct Geo
+{
+    static constexpr int HALO = PW == 22 ? 10 : MAX_R;
+    static constexpr int ROWS = FT_H + 2 * HALO;
+    static constexpr int CW = ROWS * PW;     // words per table copy
+    static constexpr int GUARD = 4 * PW + 4;  // words; recipes reach at most 4 rows + 1 word away
+    static_assert(4 + FT_W + 2 * HALO <= 4 * PW, "row pitch too small for the halo");
+};
+
+// Table build. Recipes and levels are compile-time constants (forced through template arguments):
+// the tables of one level are consecutive in the library, the first M of them are built by
+// straight-line code (one uniform switch on M per level), and every shared-memory address is
+// base + immediate.
 //   pass 1: copy 0 of T_k = max(T_a, T_b shifted by (du, dv))
-//   pass 2: copies 1..3 = bytes s..s+3 of the word pair (i, i+1) of copy 0 (zero past the row end)
+//   pass 2: copies 1..3 = bytes s..s+3 of the word pair (i, i+1) of copy 0
 // Each thread owns the words tid, tid + FT_THREADS, ... of a table copy.
 template <int LIB, int K>
 struct TableInfo
@@ -243,6 +305,29 @@ struct TableInfo
     static constexpr Recipe rc = lib_recipe(LIB, K < lib_size(LIB) ? K : 0);
     static constexpr int level = K < lib_size(LIB) ? lib_level(LIB, K) : -1;
 };
+__host__ __device__ constexpr int level_first(int lib, int lvl)
+{
+    for (int k = 0; k < lib_size(lib); ++k)
+        if (lib_level(lib, k) == lvl)
+            return k;
+    return lib_size(lib);
+}
+__host__ __device__ constexpr int level_count(int lib, int lvl)
+{
+    int n = 0;
+    for (int k = 0; k < lib_size(lib); ++k)
+        n += lib_level(lib, k) == lvl;
+    return n;
+}
+__host__ __device__ constexpr bool levels_contiguous(int lib)
+{
+    for (int k = 1; k < lib_size(lib); ++k)
+        if (lib_level(lib, k) < lib_level(lib, k - 1))
+            return false;
+    return true;
+}
+static_assert(levels_contiguous(0) && levels_contiguous(1) && levels_contiguous(2) && levels_contiguous(3),
+              "libraries list their tables in level order");
 
 template <int... Ks, class F>
 __device__ __forceinline__ void for_each_index(std::integer_sequence<int, Ks...>, F &&f)
@@ -250,76 +335,78 @@ __device__ __forceinline__ void for_each_index(std::integer_sequence<int, Ks...>
     (f(std::integral_constant<int, Ks>{}), ...);
 }
 
-template <int PW, int LIB, int LVL>
-__device__ __forceinline__ void build_level(uint32_t *sm, int CW, int rows, int n_tables, int tid)
+// the first M tables of level LVL (M >= 1, LVL >= 1)
+template <int PW, int LIB, int LVL, int M>
+__device__ __forceinline__ void build_tables(uint32_t *tb, int tid)
 {
-    using AllTables = std::make_integer_sequence<int, MAX_TABLES>;
-    if constexpr (!level_in_use(LIB, LVL))
-        return;
-    if constexpr (LVL > 0)
+    constexpr int CW = Geo<PW>::CW;
+    constexpr int ITERS = (CW + FT_THREADS - 1) / FT_THREADS;
+    constexpr int K0 = level_first(LIB, LVL);
+    using Ms = std::make_integer_sequence<int, M>;
+#pragma unroll
+    for (int it = 0; it < ITERS; ++it)
     {
-#pragma unroll 1
-        for (int i = tid; i < CW; i += FT_THREADS)
-        {
-            const int sr = i / PW, sw = i % PW;
-            uint32_t va[MAX_TABLES], vb[MAX_TABLES];
-            for_each_index(AllTables{}, [&](auto kc) {
-                constexpr int k = decltype(kc)::value;
-                if constexpr (TableInfo<LIB, k>::level == LVL)
-                {
-                    constexpr Recipe rc = TableInfo<LIB, k>::rc;
-                    constexpr int dw = rc.du >> 2;  // floor
-                    if (k < n_tables)
-                    {
-                        const int r2 = sr + rc.dv, w2 = sw + dw;
-                        va[k] = sm[rc.a * 4 * CW + i];
-                        vb[k] = (r2 >= 0 && r2 < rows && w2 >= 0 && w2 < PW) ? sm[rc.b * 4 * CW + (rc.du & 3) * CW + i + rc.dv * PW + dw] : 0u;
-                    }
-                }
-            });
-            for_each_index(AllTables{}, [&](auto kc) {
-                constexpr int k = decltype(kc)::value;
-                if constexpr (TableInfo<LIB, k>::level == LVL)
-                    if (k < n_tables)
-                        sm[k * 4 * CW + i] = bytemax4(va[k], vb[k]);
-            });
-        }
-        __syncthreads();
+        const int i = tid + it * FT_THREADS;
+        if (it * FT_THREADS + FT_THREADS > CW && i >= CW)
+            break;
+        const uint32_t *src = tb + i;
+        uint32_t va[M], vb[M];
+        for_each_index(Ms{}, [&](auto mc) {
+            constexpr int m = decltype(mc)::value;
+            constexpr Recipe rc = TableInfo<LIB, K0 + m>::rc;
+            va[m] = src[rc.a * 4 * CW];
+            vb[m] = src[(rc.b * 4 + (rc.du & 3)) * CW + rc.dv * PW + (rc.du >> 2)];
+        });
+        for_each_index(Ms{}, [&](auto mc) {
+            constexpr int m = decltype(mc)::value;
+            tb[(K0 + m) * 4 * CW + i] = bytemax4(va[m], vb[m]);
+        });
     }
-#pragma unroll 1
-    for (int i = tid; i < CW; i += FT_THREADS)
+    __syncthreads();
+#pragma unroll
+    for (int it = 0; it < ITERS; ++it)
     {
-        const bool has_next = i % PW + 1 < PW;
-        uint32_t v[MAX_TABLES], nx[MAX_TABLES];
-        for_each_index(AllTables{}, [&](auto kc) {
-            constexpr int k = decltype(kc)::value;
-            if constexpr (TableInfo<LIB, k>::level == LVL)
-                if (k < n_tables)
-                {
-                    v[k] = sm[k * 4 * CW + i];
-                    nx[k] = has_next ? sm[k * 4 * CW + i + 1] : 0u;
-                }
-        });
-        for_each_index(AllTables{}, [&](auto kc) {
-            constexpr int k = decltype(kc)::value;
-            if constexpr (TableInfo<LIB, k>::level == LVL)
-                if (k < n_tables)
-                {
-                    uint32_t *T = sm + k * 4 * CW + i;
-                    T[CW] = __funnelshift_r(v[k], nx[k], 8);
-                    T[2 * CW] = __funnelshift_r(v[k], nx[k], 16);
-                    T[3 * CW] = __funnelshift_r(v[k], nx[k], 24);
-                }
-        });
+        const int i = tid + it * FT_THREADS;
+        if (it * FT_THREADS + FT_THREADS > CW && i >= CW)
+            break;
+        uint32_t *T = tb + K0 * 4 * CW + i;
+        uint32_t v[M], nx[M];
+#pragma unroll
+        for (int m = 0; m < M; ++m)
+        {
+            v[m] = T[m * 4 * CW];
+            nx[m] = T[m * 4 * CW + 1];
+        }
+#pragma unroll
+        for (int m = 0; m < M; ++m)
+        {
+            T[(m * 4 + 1) * CW] = __funnelshift_r(v[m], nx[m], 8);
+            T[(m * 4 + 2) * CW] = __funnelshift_r(v[m], nx[m], 16);
+            T[(m * 4 + 3) * CW] = __funnelshift_r(v[m], nx[m], 24);
+        }
     }
     __syncthreads();
 }
 
-template <int PW, int LIB, int... LVLs>
-__device__ __forceinline__ void build_all_levels(uint32_t *sm, int CW, int rows, int n_tables, int tid,
-                                                 std::integer_sequence<int, LVLs...>)
+template <int PW, int LIB, int LVL>
+__device__ __forceinline__ void build_level(uint32_t *tb, int n_tables, int tid)
 {
-    (build_level<PW, LIB, LVLs>(sm, CW, rows, n_tables, tid), ...);
+    if constexpr (LVL >= 1 && level_count(LIB, LVL) > 0)
+    {
+        constexpr int K0 = level_first(LIB, LVL), N = level_count(LIB, LVL);
+        const int m = min(n_tables - K0, N);  // uniform
+        for_each_index(std::make_integer_sequence<int, N>{}, [&](auto mc) {
+            constexpr int mm = decltype(mc)::value + 1;
+            if (m == mm)
+                build_tables<PW, LIB, LVL, mm>(tb, tid);
+        });
+    }
+}
+
+template <int PW, int LIB, int... LVLs>
+__device__ __forceinline__ void build_all_levels(uint32_t *tb, int n_tables, int tid, std::integer_sequence<int, LVLs...>)
+{
+    (build_level<PW, LIB, LVLs>(tb, n_tables, tid), ...);
 }
 
 template <int PW, int LIB>
@@ -328,12 +415,14 @@ __global__ void __launch_bounds__(FT_THREADS, CTAS_PER_SM) se2_fast_kernel(const
     extern __shared__ __align__(16) uint32_t sm[];
     __shared__ uint8_t s_cls[MAX_T_PER_LAUNCH];
     __shared__ uint32_t s_next;
+    using G = Geo<PW>;
+    uint32_t *tb = sm + G::GUARD;
     const int tid = threadIdx.x;
     const int warp = tid >> 5, lane = tid & 31;
     constexpr int NWARPS = FT_THREADS / 32;
-    constexpr int ROW_ITERS = (FT_H + 2 * MAX_R + NWARPS - 1) / NWARPS;
+    constexpr int ROW_ITERS = (G::ROWS + NWARPS - 1) / NWARPS;
+    constexpr int R = G::HALO, CW = G::CW;
     const uint32_t tile_x = a.tile_x0 + blockIdx.x, tile_y = a.tile_y0 + blockIdx.y;
-    const int R = a.R, rows = a.rows, CW = a.copy_words;
     const int tx0 = static_cast<int>(tile_x) * FT_W, ty0 = static_cast<int>(tile_y) * FT_H;
     const int W = static_cast<int>(a.W), H = static_cast<int>(a.H);
 
@@ -359,7 +448,7 @@ __global__ void __launch_bounds__(FT_THREADS, CTAS_PER_SM) se2_fast_kernel(const
     {
         const int r = warp + j * NWARPS;
         const int gy = ty0 - R + r;
-        const bool row_ok = r < rows && gy >= 0 && gy < H;
+        const bool row_ok = r < G::ROWS && gy >= 0 && gy < H;
         const uint8_t *rowp = a.cost + static_cast<size_t>(row_ok ? gy : 0) * a.W;
         lo[j] = (row_ok && lo_ok) ? __ldg(reinterpret_cast<const uint32_t *>(rowp + ga)) : 0u;
         hi[j] = (row_ok && hi_ok) ? __ldg(reinterpret_cast<const uint32_t *>(rowp + ga + 4)) : 0u;
@@ -370,22 +459,31 @@ __global__ void __launch_bounds__(FT_THREADS, CTAS_PER_SM) se2_fast_kernel(const
         s_cls[tid] = static_cast<uint8_t>(my_cls);
     if (tid == 0)
         s_next = 0;
+    // table 0 (the costmap itself) in its four byte-shifted copies, straight from the registers
 #pragma unroll
     for (int j = 0; j < ROW_ITERS; ++j)
     {
         const int r = warp + j * NWARPS;
-        if (wlane && r < rows)
-            sm[r * PW + lane] = __funnelshift_r(lo[j], hi[j], 8 * sh);
+        const uint32_t w0 = __funnelshift_r(lo[j], hi[j], 8 * sh);
+        const uint32_t w1 = __shfl_down_sync(0xffffffffu, w0, 1);  // the next word of the row
+        if (wlane && r < G::ROWS)
+        {
+            uint32_t *T = tb + r * PW + lane;
+            T[0] = w0;
+            T[CW] = __funnelshift_r(w0, w1, 8);
+            T[2 * CW] = __funnelshift_r(w0, w1, 16);
+            T[3 * CW] = __funnelshift_r(w0, w1, 24);
+        }
     }
     const int any_fast = __syncthreads_or(my_cls != 255u);
     if (!any_fast)
         return;  // every bin of this tile belongs to the generic work list
 
     // brick tables, level by level (tables of one level depend only on earlier levels)
-    build_all_levels<PW, LIB>(sm, CW, rows, a.n_tables, tid, std::make_integer_sequence<int, MAX_LEVEL + 1>{});
+    build_all_levels<PW, LIB>(tb, a.n_tables, tid, std::make_integer_sequence<int, MAX_LEVEL + 1>{});
 
-    // output phase: warps fetch (bin, row half) units until none are left
-    run_units<PW>(a, sm, s_cls, &s_next, lane, tx0, ty0);
+    // output phase: warps fetch (bin, 16 rows) units until none are left
+    run_units<PW>(a, tb, s_cls, &s_next, lane, tx0, ty0);
 }
 
 
@@ -652,6 +750,8 @@ struct Se2Plan
     std::vector<uint32_t> lists;
     std::vector<uint32_t> list_off;  // [n_theta*4]
     std::vector<uint16_t> list_len;  // [n_theta*4]
+    std::vector<uint32_t> list_id;   // [n_theta*4] number of the distinct offset set; NO_ID = class absent
+    static constexpr uint32_t NO_ID = 0xFFFFFFFFu;
     // generic work list, sorted by bin
     std::vector<uint32_t> h_work;
     std::vector<uint32_t> work_off;  // [n_theta+1] entry index
@@ -796,14 +896,17 @@ pp_status build_plan(pp_handle h, int effort)
     if (R > MAX_R)
         return PP_OK;
     // 2. geometry
-    pl->R = R;
-    pl->rows = FT_H + 2 * R;
     int pw = (4 + FT_W + 2 * R + 3) / 4;  // one margin word on the left
     pw = pw <= 22 ? 22 : 26;  // the two instantiated pitches (both 2 mod 4: conflict-free half-warps)
+    // the staged halo depends on the pitch only (Geo<PW>), so that table addresses are immediates
+    const int halo = pw == 22 ? Geo<22>::HALO : Geo<26>::HALO;
+    const size_t guard_bytes = static_cast<size_t>(2) * (pw == 22 ? Geo<22>::GUARD : Geo<26>::GUARD) * 4;
+    pl->R = halo;
+    pl->rows = FT_H + 2 * halo;
     pl->PW = pw;
     pl->copy_words = pl->rows * pl->PW;
     const size_t table_bytes = static_cast<size_t>(4) * pl->copy_words * 4;
-    int slots = static_cast<int>(std::min<size_t>(MAX_TABLES, (SMEM_LIMIT - 1024) / table_bytes));
+    int slots = static_cast<int>(std::min<size_t>(MAX_TABLES, (SMEM_LIMIT - 1024 - guard_bytes) / table_bytes));
     // Every table costs a fixed amount per tile and saves samples per bin: with few bins per launch
     // (a heading-sharded rank of an 8-GPU job builds 9) the costmap plus the two 2-runs is the optimum
     // measured on B200 (tools/probe_tables.py).
@@ -849,13 +952,15 @@ pp_status build_plan(pp_handle h, int effort)
         pl->n_tables = std::min<int>(slots, static_cast<int>(lib.size()));
         pl->lib.assign(lib.begin(), lib.begin() + pl->n_tables);
     }
-    pl->smem_bytes = table_bytes * pl->n_tables;
+    pl->smem_bytes = table_bytes * pl->n_tables + guard_bytes;
     auto bricks = brick_points(pl->lib, pl->n_tables);
 
     // 5. covers -> sample lists (byte offsets relative to the thread's base address)
     pl->list_off.assign(static_cast<size_t>(nt) * 4, 0);
     pl->list_len.assign(static_cast<size_t>(nt) * 4, 0);
+    pl->list_id.assign(static_cast<size_t>(nt) * 4, Se2Plan::NO_ID);
     std::map<Offsets, std::vector<uint32_t>> memo;
+    std::map<const std::vector<uint32_t> *, uint32_t> memo_id;  // map nodes do not move
     for (uint32_t t = 0; t < nt; ++t)
         for (int cx = 0; cx < xc[t].n_classes; ++cx)
             for (int cy = 0; cy < yc[t].n_classes; ++cy)
@@ -867,12 +972,13 @@ pp_status build_plan(pp_handle h, int effort)
                     std::vector<uint32_t> words;
                     for (const Placement &p : cover_set(S, bricks, R, node_budget))
                     {
-                        const int ax = R + 4 + p.ox, ay = R + p.oy;  // >= 0; +4: the margin word
+                        const int ax = halo + 4 + p.ox, ay = halo + p.oy;  // >= 0; +4: the margin word
                         const uint32_t word = static_cast<uint32_t>((p.brick * 4 + (ax & 3)) * pl->copy_words + ay * pl->PW + (ax >> 2));
                         words.push_back(word * 4);
                     }
                     it = memo.emplace(S, words).first;
                 }
+                pl->list_id[t * 4 + cx * 2 + cy] = memo_id.emplace(&it->second, static_cast<uint32_t>(memo_id.size())).first->second;
                 pl->list_off[t * 4 + cx * 2 + cy] = static_cast<uint32_t>(pl->lists.size());
                 pl->list_len[t * 4 + cx * 2 + cy] = static_cast<uint16_t>(it->second.size());
                 pl->lists.insert(pl->lists.end(), it->second.begin(), it->second.end());
@@ -982,20 +1088,44 @@ pp_status pp_se2_launch_fast(pp_handle h, uint32_t x0, uint32_t y0, uint32_t x1,
     {
         // as many bins as fit in the parameter block
         uint32_t n = 0, words = 0;
+        std::map<uint32_t, uint32_t> stored;           // offset-set id -> where its list sits in args.lists
+        std::map<uint32_t, uint32_t> last_with;        // offset-set id -> last (bin, class) link that has it
         while (t + n < h->t_end && n < MAX_T_PER_LAUNCH)
         {
             uint32_t need = 0;
             for (int c = 0; c < 4; ++c)
-                need += (pl->list_len[(t + n) * 4 + c] + 3u) & ~3u;
+                if (!stored.count(pl->list_id[(t + n) * 4 + c]))
+                    need += (pl->list_len[(t + n) * 4 + c] + 3u) & ~3u;
             if (words + need > MAX_LIST_WORDS)
                 break;
             for (int c = 0; c < 4; ++c)
             {
-                const uint32_t len = pl->list_len[(t + n) * 4 + c];
-                args.list_off[n][c] = static_cast<uint16_t>(words);
+                const uint32_t len = pl->list_len[(t + n) * 4 + c], id = pl->list_id[(t + n) * 4 + c];
                 args.list_len[n][c] = static_cast<uint16_t>(len);
-                std::memcpy(args.lists + words, pl->lists.data() + pl->list_off[(t + n) * 4 + c], len * sizeof(uint32_t));
-                words += (len + 3u) & ~3u;  // keep every list 16-byte aligned
+                args.chain_prev[n][c] = args.chain_next[n][c] = static_cast<uint16_t>(NO_LINK);
+                if (id == Se2Plan::NO_ID)
+                {
+                    args.list_off[n][c] = 0;
+                    continue;
+                }
+                auto st = stored.find(id);
+                if (st == stored.end())
+                {
+                    st = stored.emplace(id, words).first;
+                    std::memcpy(args.lists + words, pl->lists.data() + pl->list_off[(t + n) * 4 + c], len * sizeof(uint32_t));
+                    words += (len + 3u) & ~3u;  // keep every list 16-byte aligned
+                }
+                args.list_off[n][c] = static_cast<uint16_t>(st->second);
+                const uint32_t me = n | static_cast<uint32_t>(c) << 8;
+                auto lw = last_with.find(id);
+                if (lw != last_with.end())
+                {
+                    args.chain_prev[n][c] = static_cast<uint16_t>(lw->second);
+                    args.chain_next[lw->second & 0xFFu][lw->second >> 8] = static_cast<uint16_t>(me);
+                    lw->second = me;
+                }
+                else
+                    last_with.emplace(id, me);
             }
             ++n;
         }
@@ -1011,7 +1141,8 @@ pp_status pp_se2_launch_fast(pp_handle h, uint32_t x0, uint32_t y0, uint32_t x1,
             const uint32_t nw = pl->work_off[t + k + 1] - pl->work_off[t + k];
             generic_pairs += nw;
             fast_pairs += static_cast<uint64_t>(pl->tiles_x) * pl->tiles_y - nw;
-            sample_sum += pl->list_len[(t + k) * 4];
+            if (args.chain_prev[k][0] == NO_LINK)  // bins that share an earlier bin's evaluation load nothing
+                sample_sum += pl->list_len[(t + k) * 4];
         }
         const uint32_t w0 = pl->work_off[t], w1 = pl->work_off[t + n];
         if (w1 > w0)
