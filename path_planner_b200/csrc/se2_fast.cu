@@ -167,43 +167,38 @@ __device__ __forceinline__ void accumulate(uint32_t (&odd)[QPT], uint32_t (&even
 // lists balance out. The loads of the next sample pair are issued before the max operations of
 // the current one (software pipelining by hand).
 template <int PW>
-__device__ __forceinline__ void run_units(const FastArgs &a, const uint32_t *sm, const uint8_t *s_cls, uint32_t *s_next,
-                                          int lane, int tx0, int ty0)
+__device__ __forceinline__ void run_units(const FastArgs &a, const uint32_t *sm, const uint8_t *s_cls, const uint8_t *s_lead,
+                                          uint32_t n_lead, uint32_t *s_next, int lane, int tx0, int ty0)
 {
     const int q = lane & 15;
     const int W = static_cast<int>(a.W), H = static_cast<int>(a.H);
     const int gx = tx0 + 4 * q;
     const bool in_x = gx < W;
     const size_t plane = static_cast<size_t>(a.W) * a.H;
-    const size_t rs = a.W;
-    const uint32_t n_units = UNITS_PER_BIN * a.n_t;
+    const uint32_t n_units = UNITS_PER_BIN * n_lead;
+    // byte offsets of the thread's QPT rows inside a bin's plane (< 2^30): the same for every unit half
+    const uint32_t cell0 = static_cast<uint32_t>(ty0 + 8 * (lane >> 4)) * a.W + static_cast<uint32_t>(gx);
+    uint32_t row_off[QPT];
+#pragma unroll
+    for (int j = 0; j < QPT; ++j)
+        row_off[j] = cell0 + static_cast<uint32_t>(quad_row(j)) * a.W;
+    const bool tile_inside = tx0 + FT_W <= W && ty0 + FT_H <= H;
     while (true)
     {
         uint32_t unit = 0;
         if (lane == 0)
-            unit = atomicAdd(s_next, 1u);
+            asm volatile("atom.shared.add.u32 %0, [%1], 1;" : "=r"(unit) : "r"(static_cast<uint32_t>(__cvta_generic_to_shared(s_next))) : "memory");
         unit = __shfl_sync(0xffffffffu, unit, 0);
         if (unit >= n_units)
             break;
-        const uint32_t t = unit / UNITS_PER_BIN;
+        // s_lead lists the bins that evaluate on this tile (see the kernel prologue)
+        const uint32_t t = s_lead[unit / UNITS_PER_BIN];
         const uint32_t cls = s_cls[t];
-        if (cls == 255u)
-            continue;
-        // Bins whose offset sets coincide on this tile have identical outputs: the first of them
-        // evaluates, and stores to all (warp-uniform walks over the host-built chains).
-        bool evaluated_earlier = false;
-        for (uint32_t link = a.chain_prev[t][cls]; link != NO_LINK; link = a.chain_prev[link & 0xFFu][link >> 8])
-            if (s_cls[link & 0xFFu] == (link >> 8))
-            {
-                evaluated_earlier = true;
-                break;
-            }
-        if (evaluated_earlier)
-            continue;
         const int row0 = 16 * static_cast<int>(unit % UNITS_PER_BIN) + 8 * (lane >> 4);
         const uint8_t *smb = reinterpret_cast<const uint8_t *>(sm + row0 * PW + q);
         const int gy = ty0 + row0;
-        uint8_t *out = a.vol + plane * (a.t_first + t) + static_cast<size_t>(gy) * a.W + gx;
+        const uint32_t half_off = 16u * (unit % UNITS_PER_BIN) * a.W;
+        uint8_t *out = a.vol + plane * (a.t_first + t) + half_off;  // warp-uniform
         const uint32_t *list = a.lists + a.list_off[t][cls];
         const uint32_t n_samples = a.list_len[t][cls];  // >= 1; the stored list is padded to an even count
         const uint32_t len = n_samples & ~1u;            // samples consumed in pairs
@@ -249,13 +244,19 @@ __device__ __forceinline__ void run_units(const FastArgs &a, const uint32_t *sm,
         uint32_t link = a.chain_next[t][cls];
         while (true)
         {
-            if (in_x)
+            if (tile_inside && a.n_peers == 0)
+            {
+#pragma unroll
+                for (int j = 0; j < QPT; ++j)
+                    *reinterpret_cast<uint32_t *>(out + row_off[j]) = odd[j];
+            }
+            else if (in_x)
             {
 #pragma unroll
                 for (int j = 0; j < QPT; ++j)
                     if (gy + quad_row(j) < H)
                     {
-                        uint8_t *dst = out + quad_row(j) * rs;
+                        uint8_t *dst = out + row_off[j];
                         *reinterpret_cast<uint32_t *>(dst) = odd[j];
                         for (int p = 0; p < a.n_peers; ++p)  // peer volumes over NVLink
                             *reinterpret_cast<uint32_t *>(dst + a.peer_delta[p]) = odd[j];
@@ -272,7 +273,7 @@ __device__ __forceinline__ void run_units(const FastArgs &a, const uint32_t *sm,
             }
             if (t2 == NO_LINK)
                 break;
-            out = a.vol + plane * (a.t_first + t2) + static_cast<size_t>(gy) * a.W + gx;
+            out = a.vol + plane * (a.t_first + t2) + half_off;
         }
     }
 }
@@ -414,7 +415,8 @@ __global__ void __launch_bounds__(FT_THREADS, CTAS_PER_SM) se2_fast_kernel(const
 {
     extern __shared__ __align__(16) uint32_t sm[];
     __shared__ uint8_t s_cls[MAX_T_PER_LAUNCH];
-    __shared__ uint32_t s_next;
+    __shared__ uint8_t s_lead[MAX_T_PER_LAUNCH];  // bins that evaluate on this tile
+    __shared__ uint32_t s_next, s_nlead;
     using G = Geo<PW>;
     uint32_t *tb = sm + G::GUARD;
     const int tid = threadIdx.x;
@@ -458,7 +460,7 @@ __global__ void __launch_bounds__(FT_THREADS, CTAS_PER_SM) se2_fast_kernel(const
     if (static_cast<uint32_t>(tid) < a.n_t)
         s_cls[tid] = static_cast<uint8_t>(my_cls);
     if (tid == 0)
-        s_next = 0;
+        s_next = s_nlead = 0;
     // table 0 (the costmap itself) in its four byte-shifted copies, straight from the registers
 #pragma unroll
     for (int j = 0; j < ROW_ITERS; ++j)
@@ -479,11 +481,23 @@ __global__ void __launch_bounds__(FT_THREADS, CTAS_PER_SM) se2_fast_kernel(const
     if (!any_fast)
         return;  // every bin of this tile belongs to the generic work list
 
+    // Bins whose offset sets coincide on this tile have identical outputs: the first bin of such a
+    // chain (host-built, in bin order) evaluates and stores to all of them. One bin per thread.
+    if (my_cls != 255u)
+    {
+        bool evaluated_earlier = false;
+        for (uint32_t link = a.chain_prev[tid][my_cls]; link != NO_LINK && !evaluated_earlier; link = a.chain_prev[link & 0xFFu][link >> 8])
+            evaluated_earlier = s_cls[link & 0xFFu] == (link >> 8);
+        if (!evaluated_earlier)
+            s_lead[atomicAdd(&s_nlead, 1u)] = static_cast<uint8_t>(tid);
+    }
+
     // brick tables, level by level (tables of one level depend only on earlier levels)
     build_all_levels<PW, LIB>(tb, a.n_tables, tid, std::make_integer_sequence<int, MAX_LEVEL + 1>{});
+    __syncthreads();  // also orders s_lead / s_nlead when no table beyond the costmap is built
 
-    // output phase: warps fetch (bin, 16 rows) units until none are left
-    run_units<PW>(a, tb, s_cls, &s_next, lane, tx0, ty0);
+    // output phase: warps fetch (evaluating bin, 16 rows) units until none are left
+    run_units<PW>(a, tb, s_cls, s_lead, s_nlead, &s_next, lane, tx0, ty0);
 }
 
 
