@@ -5,9 +5,10 @@ TEB queries) at 4096x4096x72 (BASELINE.json configs[2]).
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
 
 One process per GPU (torchrun for N > 1). A step is one build of the whole SE2 volume from a costmap
-already resident in HBM; with N > 1 the 72 heading bins are split evenly across ranks (strong
-scaling, no data-path collective in `value`; the NCCL all-gather of the slabs is timed
-separately and reported under "gathered"). Rank 0 prints ONE JSON line.
+already resident in HBM; with N > 1 every rank builds all 72 heading bins of its band of map rows
+(strong scaling, independent units, no data-path collective in `value`; heading-bin sharding, its
+NCCL all-gather and the fused peer-store variants are timed separately and reported under
+"gathered"). Rank 0 prints ONE JSON line.
 
 `--impl reference` times the reference's own CPU code (oracle/_ref, compiled unmodified from the
 reference sources; falls back to the oracle port where that is absent) with all host threads on
@@ -271,8 +272,29 @@ def main():
         dist.broadcast_object_list(obj, src=0)
         h.comm_init(obj[0], rank, world)
 
+    # N > 1: every rank builds ALL heading bins of its band of map rows -- independent units, no
+    # exchange on the data path, and the per-tile table build is paid once per tile in the whole job
+    # (heading-bin sharding, SURVEY.md section 8e, repeats it on every rank and separates the bin pairs
+    # t / t + n/2 that share one evaluation; it is measured below for comparison).
+    from path_planner_b200.sharding import row_band
+    y0, y1 = row_band(H, rank, world) if world > 1 else (0, H)
+    if world > 1:
+        h.se2_volume_set_rows(y0, y1)
+
     def step():
-        h.se2_volume_build(N_THETA, 0.5, 0.5, 0.0, t0, t1)
+        h.se2_volume_build(N_THETA, 0.5, 0.5, 0.0, 0, N_THETA)
+
+    def timed(fn, steps):
+        """CUDA-event time per step of fn() on this rank's stream, L2 flushed before every step; max over ranks."""
+        barrier()
+        ms = 0.0
+        for _ in range(steps):
+            h.l2_flush()
+            h.timer_start()
+            fn()
+            ms += h.timer_stop()
+        barrier()
+        return max_over_ranks(ms / steps), ms / steps
 
     # ---- device-resident throughput (`value`) -------------------------------------------------
     for _ in range(args.warmup):
@@ -283,44 +305,30 @@ def main():
     barrier()
     sampler = ClockSampler(local_rank) if rank == 0 else None
     launches0 = h.launch_count()
-    total_ms = 0.0
     wall0 = time.perf_counter()
-    for _ in range(args.steps):
-        h.l2_flush()          # cold L2 for every step; the flush is outside the event pair
-        h.timer_start()
-        step()
-        total_ms += h.timer_stop()
-    barrier()
+    ms_per_step, my_ms = timed(step, args.steps)
     wall = time.perf_counter() - wall0
     launches = h.launch_count() - launches0
     clocks = sampler.stop() if sampler else None
-    ms_per_step = max_over_ranks(total_ms / args.steps)
     total_cells = W * H * N_THETA
     value = total_cells / (ms_per_step * 1e-3)
 
-    # ---- compute + NCCL all-gather of the slabs (N > 1) ----------------------------------------
+    # ---- N > 1: the other ways to split and exchange, for comparison ---------------------------------
     gathered = None
     if world > 1:
-        for _ in range(2):
-            step()
-            h.se2_volume_allgather()
-        h.sync()
-        barrier()
-        g_ms = 0.0
-        for _ in range(args.steps):
-            h.l2_flush()
-            h.timer_start()
-            step()
-            h.se2_volume_allgather()
-            g_ms += h.timer_stop()
-        barrier()
-        g_ms = max_over_ranks(g_ms / args.steps)
-        gathered = {"value": total_cells / (g_ms * 1e-3), "unit": UNIT, "ms_per_step": g_ms,
-                    "collective": "ncclAllGather of heading slabs, in place",
-                    "bytes_received_per_gpu": int(W * H * (N_THETA - per))}
+        def cells_per_s(ms):
+            return total_cells / (ms * 1e-3)
 
-    # ---- fused build + peer stores: slabs land in every GPU's volume while they are computed -----
-    if world > 1:
+        def theta_step():
+            h.se2_volume_build(N_THETA, 0.5, 0.5, 0.0, t0, t1)
+
+        def theta_gather_step():
+            theta_step()
+            h.se2_volume_allgather()
+
+        gathered = {}
+        # the row bands again, every output word also stored to all other ranks' volumes (NVLink peer
+        # mappings through CUDA IPC): the whole volume on every GPU without a separate collective
         h.se2_volume_reserve(N_THETA)
         handles = [None] * world
         dist.all_gather_object(handles, h.se2_volume_ipc_export())
@@ -329,51 +337,45 @@ def main():
         for _ in range(2):
             step()
         h.sync()
-        barrier()
-        p_ms = 0.0
-        for _ in range(args.steps):
-            h.l2_flush()
-            h.timer_start()
-            step()
-            p_ms += h.timer_stop()
-        barrier()
-        p_ms = max_over_ranks(p_ms / args.steps)
-        # spatial sharding: every rank builds ALL bins of its row band (per-tile table build paid once
-        # per tile in the whole job instead of once per rank) and pushes them to every volume
-        from path_planner_b200.sharding import row_band
-        y0, y1 = row_band(H, rank, world)
-        h.se2_volume_set_rows(y0, y1)
-        for push_on, key in ((False, "row_sharded"), (True, "row_sharded_fused_push")):
-            h.se2_volume_set_push(push_on)
-            for _ in range(2):
-                h.se2_volume_build(N_THETA, 0.5, 0.5, 0.0, 0, N_THETA)
-            h.sync()
-            barrier()
-            r_ms = 0.0
-            for _ in range(args.steps):
-                h.l2_flush()
-                h.timer_start()
-                h.se2_volume_build(N_THETA, 0.5, 0.5, 0.0, 0, N_THETA)
-                r_ms += h.timer_stop()
-            barrier()
-            r_ms = max_over_ranks(r_ms / args.steps)
-            gathered[key] = {"value": total_cells / (r_ms * 1e-3), "unit": UNIT, "ms_per_step": r_ms}
-        gathered["row_sharded"]["how"] = "rank g builds all 72 bins of map rows band g (no exchange); results identical"
-        gathered["row_sharded_fused_push"]["how"] = "same, every output word also stored to all other ranks' volumes"
-        h.se2_volume_set_rows(0, 0)
+        ms, _ = timed(step, args.steps)
+        gathered["row_sharded_fused_push"] = {"value": cells_per_s(ms), "unit": UNIT, "ms_per_step": ms,
+                                              "how": "row bands, every output word also stored to all other ranks' volumes"}
         h.se2_volume_set_push(False)
-        gathered["fused_push"] = {"value": total_cells / (p_ms * 1e-3), "unit": UNIT, "ms_per_step": p_ms,
-                                  "how": "build kernels store every output word to all ranks' volumes over NVLink peer mappings (CUDA IPC); no separate collective"}
+        # heading-bin sharding: rank g builds bins [g*n/N, (g+1)*n/N) of the whole map
+        h.se2_volume_set_rows(0, 0)
+        for _ in range(2):
+            theta_gather_step()
+        h.sync()
+        ms, _ = timed(theta_step, args.steps)
+        gathered["theta_sharded"] = {"value": cells_per_s(ms), "unit": UNIT, "ms_per_step": ms,
+                                     "how": "rank g builds its slab of heading bins of the whole map (no exchange)"}
+        ms, _ = timed(theta_gather_step, args.steps)
+        gathered["theta_sharded_allgather"] = {"value": cells_per_s(ms), "unit": UNIT, "ms_per_step": ms,
+                                               "collective": "ncclAllGather of heading slabs, in place",
+                                               "bytes_received_per_gpu": int(W * H * (N_THETA - per))}
+        h.se2_volume_set_push(True)
+        for _ in range(2):
+            theta_step()
+        h.sync()
+        ms, _ = timed(theta_step, args.steps)
+        gathered["theta_sharded_fused_push"] = {"value": cells_per_s(ms), "unit": UNIT, "ms_per_step": ms,
+                                                "how": "slab build kernels store every output word to all ranks' volumes; no separate collective"}
+        h.se2_volume_set_push(False)
+        h.se2_volume_set_rows(y0, y1)
 
     # ---- end to end through the C ABI with host buffers (`e2e`) ----------------------------------
-    out_pinned = capi.PinnedBuffer(W * H * per)
-    out_view = out_pinned.array.reshape(per, H, W)
+    band = y1 - y0
+    out_pinned = capi.PinnedBuffer(W * band * N_THETA)
+    out_view = out_pinned.array.reshape(N_THETA, band, W)
     e2e_steps = max(3, min(args.steps, 5))
 
     def e2e_step():
         h.costmap_upload(cost_pinned, pinned=True)
         step()
-        h.se2_volume_download(t0, t1, out=out_view, pinned=True)
+        if world > 1:
+            h.se2_volume_download_rows(y0, y1, 0, N_THETA, out=out_view)
+        else:
+            h.se2_volume_download(0, N_THETA, out=out_view, pinned=True)
 
     e2e_step()
     barrier()
@@ -387,12 +389,12 @@ def main():
     e_ms = max_over_ranks(max(e_ms, 0.0) / e2e_steps)
     e2e = {"value": total_cells / (e_ms * 1e-3), "unit": UNIT, "ms_per_step": e_ms, "wall_ms_per_step": e_wall / e2e_steps,
            "h2d_bytes_per_step": int(W * H * world), "d2h_bytes_per_step": int(W * H * N_THETA),
-           "path": "pp_costmap_upload(pinned host) + pp_se2_volume_build + pp_se2_volume_download(pinned host)"}
+           "path": "pp_costmap_upload(pinned host) + pp_se2_volume_build + pp_se2_volume_download"
+                   + ("_rows(this rank's band; pinned host)" if world > 1 else "(pinned host)")}
 
     # ---- roofline of the dominant kernel ---------------------------------------------------------
     peak, peak_src = measured_peak_gbs()
-    alg_bytes = W * H * (1 + per)            # read the costmap once, write every output byte once
-    my_ms = total_ms / args.steps
+    alg_bytes = W * (y1 - y0) * (1 + N_THETA)   # read the costmap once, write every output byte once (this rank's rows)
     achieved = alg_bytes / (my_ms * 1e-3) / 1e9
     traffic = None
     tpath = os.path.join(ROOT, "profiles", "se2_traffic.json")
@@ -410,9 +412,9 @@ def main():
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "u8",
         "data": "synthetic",
-        "config": {"workload": WORKLOAD, "W": W, "H": H, "n_theta": N_THETA, "bins_per_gpu": per,
+        "config": {"workload": WORKLOAD, "W": W, "H": H, "n_theta": N_THETA, "rows_per_gpu": int(y1 - y0),
                    "footprint_points": int(len(h.footprint_get())), "sample_offset": [0.5, 0.5, 0.0],
-                   "sharding": f"theta x{world}", "l2": "flushed between steps (256 MiB memset, outside the timed events)",
+                   "sharding": f"row bands x{world}", "l2": "flushed between steps (256 MiB memset, outside the timed events)",
                    "kernel_mode": "auto" if args.mode == 0 else "generic", "fast_tiles": stats["fast_tiles"],
                    "generic_tiles": stats["generic_tiles"], "samples_per_cell": stats["samples_per_cell"]},
         "roofline": roofline, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,

@@ -105,6 +105,9 @@ pp_status pp_footprint_get(pp_handle h, int32_t *offsets_xy_out, uint32_t max_po
  *   pp_se2_volume_refresh  recompute only the dirty region (grown by the footprint reach) for
  *                          the bins of the last build, then clear the dirty region
  *   pp_se2_volume_download copy bins [t_begin, t_end) to `host_out` ((t_end-t_begin)*H*W bytes)
+ *   pp_se2_volume_download_rows  the same for map rows [y_begin, y_end) only: host_out receives
+ *                          (t_end-t_begin) bands of (y_end-y_begin)*W bytes, one after the other
+ *                          (what a row-band-sharded rank hands to its host; see pp_se2_volume_set_rows)
  *   pp_se2_volume_ptr      device address of bin 0 (for zero-copy consumers and NCCL)
  */
 pp_status pp_se2_volume_build(pp_handle h, uint32_t n_theta, float ox, float oy, float ot, uint32_t t_begin,
@@ -112,6 +115,8 @@ pp_status pp_se2_volume_build(pp_handle h, uint32_t n_theta, float ox, float oy,
 pp_status pp_se2_volume_refresh(pp_handle h);
 pp_status pp_se2_volume_download(pp_handle h, uint32_t t_begin, uint32_t t_end, uint8_t *host_out,
                                  int host_is_pinned);
+pp_status pp_se2_volume_download_rows(pp_handle h, uint32_t t_begin, uint32_t t_end, uint32_t y_begin, uint32_t y_end,
+                                      uint8_t *host_out);
 pp_status pp_se2_volume_ptr(pp_handle h, const uint8_t **device_ptr_out, uint64_t *bytes_out);
 /* Which kernel variant pp_se2_volume_build uses: 0 = automatic, 1 = force the generic exact
  * gather everywhere (used by tests to cross-check the tiled fast path against it). */

@@ -17,7 +17,7 @@ SYMBOLS = [
     "pp_version", "pp_create", "pp_destroy", "pp_last_error", "pp_sync", "pp_host_alloc", "pp_host_free",
     "pp_timer_start", "pp_timer_stop", "pp_l2_flush", "pp_launch_count", "pp_costmap_upload", "pp_costmap_update_rect", "pp_costmap_download",
     "pp_footprint_from_boundary", "pp_footprint_set", "pp_footprint_get", "pp_se2_volume_build",
-    "pp_se2_volume_refresh", "pp_se2_volume_download", "pp_se2_volume_ptr", "pp_se2_volume_set_mode",
+    "pp_se2_volume_refresh", "pp_se2_volume_download", "pp_se2_volume_download_rows", "pp_se2_volume_ptr", "pp_se2_volume_set_mode",
     "pp_se2_volume_stats", "pp_footprint_cost_batch", "pp_heuristic_build", "pp_heuristic_ptr", "pp_heuristic_stats", "pp_heuristic_build_noalloc", "pp_plan",
     "pp_obstacles_extract", "pp_radius_topk", "pp_comm_unique_id", "pp_comm_init", "pp_se2_volume_allgather", "pp_se2_volume_reserve",
     "pp_se2_volume_ipc_export", "pp_se2_volume_ipc_open", "pp_se2_volume_set_push", "pp_se2_volume_set_rows",
@@ -107,6 +107,7 @@ def load():
     L.pp_se2_volume_build.argtypes = [_vp, _u32, C.c_float, C.c_float, C.c_float, _u32, _u32]
     L.pp_se2_volume_refresh.argtypes = [_vp]
     L.pp_se2_volume_download.argtypes = [_vp, _u32, _u32, _vp, C.c_int]
+    L.pp_se2_volume_download_rows.argtypes = [_vp, _u32, _u32, _u32, _u32, _vp]
     L.pp_se2_volume_ptr.argtypes = [_vp, C.POINTER(_vp), C.POINTER(C.c_uint64)]
     L.pp_se2_volume_set_mode.argtypes = [_vp, C.c_int]
     L.pp_se2_volume_stats.argtypes = [_vp, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), C.POINTER(C.c_double)]
@@ -289,6 +290,13 @@ class Handle:
         if out is None:
             out = np.empty((t_end - t_begin, self.H, self.W), np.uint8)
         self._ck(self.L.pp_se2_volume_download(self.h, t_begin, t_end, _ptr(out), int(pinned)))
+        return out
+
+    def se2_volume_download_rows(self, y_begin, y_end, t_begin=0, t_end=None, out=None):
+        t_end = self.n_theta if t_end is None else t_end
+        if out is None:
+            out = np.empty((t_end - t_begin, y_end - y_begin, self.W), np.uint8)
+        self._ck(self.L.pp_se2_volume_download_rows(self.h, t_begin, t_end, y_begin, y_end, _ptr(out)))
         return out
 
     def se2_volume_ptr(self):

@@ -358,6 +358,25 @@ pp_status pp_se2_volume_download(pp_handle h, uint32_t t_begin, uint32_t t_end, 
     return PP_OK;
 }
 
+pp_status pp_se2_volume_download_rows(pp_handle h, uint32_t t_begin, uint32_t t_end, uint32_t y_begin, uint32_t y_end,
+                                      uint8_t *host_out)
+{
+    if (!h)
+        return PP_ERR_INVALID;
+    PP_REQUIRE(h, h->d_vol && host_out, PP_ERR_STATE, "pp_se2_volume_download_rows: no volume or null output");
+    PP_REQUIRE(h, t_begin <= t_end && t_end <= h->n_theta, PP_ERR_INVALID, "bins [%u,%u) outside [0,%u)", t_begin, t_end, h->n_theta);
+    PP_REQUIRE(h, y_begin <= y_end && y_end <= h->H, PP_ERR_INVALID, "rows [%u,%u) outside [0,%u)", y_begin, y_end, h->H);
+    if (t_begin == t_end || y_begin == y_end)
+        return PP_OK;
+    PP_CUDA(h, cudaSetDevice(h->device));
+    const size_t plane = static_cast<size_t>(h->W) * h->H, band = static_cast<size_t>(h->W) * (y_end - y_begin);
+    // one strided copy: a "row" of it is the band of one bin
+    PP_CUDA(h, cudaMemcpy2DAsync(host_out, band, h->d_vol + plane * t_begin + static_cast<size_t>(y_begin) * h->W, plane, band,
+                                 t_end - t_begin, cudaMemcpyDeviceToHost, h->stream));
+    PP_CUDA(h, cudaStreamSynchronize(h->stream));
+    return PP_OK;
+}
+
 pp_status pp_se2_volume_ptr(pp_handle h, const uint8_t **device_ptr_out, uint64_t *bytes_out)
 {
     if (!h || !device_ptr_out)

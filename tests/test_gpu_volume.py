@@ -194,3 +194,32 @@ def test_large_footprint_and_coarse_resolution(handle, port):
         handle.se2_volume_build(72, t_begin=30, t_end=40)
         got = handle.se2_volume_download(30, 40)
         assert np.array_equal(got, port.se2_volume(cost, pts, 72, t0=30, t1=40)), (res, b)
+
+
+def test_download_rows_is_a_slice_of_the_volume(handle):
+    cost = make_costmap(200, 150, seed=8)
+    handle.costmap_upload(cost)
+    handle.footprint_from_boundary(RES, [0.64, 0.46], True)
+    handle.se2_volume_build(72)
+    vol = handle.se2_volume_download()
+    for (y0, y1, t0, t1) in ((0, 150, 0, 72), (32, 96, 0, 72), (149, 150, 10, 11), (16, 48, 36, 72)):
+        assert np.array_equal(handle.se2_volume_download_rows(y0, y1, t0, t1), vol[t0:t1, y0:y1])
+    from path_planner_b200.capi import PPError
+    with pytest.raises(PPError):
+        handle.se2_volume_download_rows(100, 151)
+
+
+def test_twin_bins_equal_their_own_evaluation(handle, port):
+    """Bins t and t + n/2 of a centrally symmetric footprint share one evaluation in the fast kernel; a build
+    of the upper half alone (no twin in the launch) must give the same bytes, and both must match the oracle."""
+    cost = make_costmap(448, 200, seed=12)
+    pts = port.footprint_points(RES, [0.64, 0.46], True)
+    handle.costmap_upload(cost)
+    handle.footprint_from_boundary(RES, [0.64, 0.46], True)
+    handle.se2_volume_build(72)
+    whole = handle.se2_volume_download()
+    handle.se2_volume_build(72, t_begin=36, t_end=72)
+    upper = handle.se2_volume_download(36, 72)
+    assert np.array_equal(whole[36:], upper)
+    want = port.se2_volume(cost, pts, 72, t0=30, t1=42)
+    assert np.array_equal(whole[30:42], want)
