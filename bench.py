@@ -343,7 +343,7 @@ def main():
         h.se2_volume_set_push(False)
         # heading-bin sharding: rank g builds bins [g*n/N, (g+1)*n/N) of the whole map
         h.se2_volume_set_rows(0, 0)
-        for _ in range(2):
+        for _ in range(4):  # a handle re-plans thoroughly on its third build of a configuration: keep that out of the timing
             theta_gather_step()
         h.sync()
         ms, _ = timed(theta_step, args.steps)
@@ -362,6 +362,9 @@ def main():
                                                 "how": "slab build kernels store every output word to all ranks' volumes; no separate collective"}
         h.se2_volume_set_push(False)
         h.se2_volume_set_rows(y0, y1)
+        for _ in range(4):  # back to the primary configuration (its plan may have been replaced above)
+            step()
+        h.sync()
 
     # ---- end to end through the C ABI with host buffers (`e2e`) ----------------------------------
     band = y1 - y0
