@@ -6,12 +6,15 @@
 // max over uint8 is exact, idempotent and order-free, so S_t may be covered by translated copies
 // of small "bricks" B (S_t = U_i (B_i + o_i), overlaps allowed, no point outside S_t), and
 //   V[t][y][x] = max_i T_{B_i}[y + o_i.y][x + o_i.x],   T_B = dilation of the costmap tile by B.
-// The brick tables are heading-independent: a CTA stages one 64x32 tile (+ halo) of the costmap in
-// shared memory, derives up to 11 brick tables from it by doubling (each table is the max of two
-// shifted earlier tables; recipes are compile-time data), and then serves ALL heading bins of the
-// launch from them, turning the P = 48 gathers per cell of the reference into ~15.5 aligned 32-bit
-// shared-memory loads per four cells. Every table is stored in four byte-shifted copies so that
-// the word for any x offset is an aligned LDS.32.
+// The brick tables are heading-independent: a CTA stages one 64x16 tile (+ halo) of the costmap in
+// shared memory, derives the brick tables from it by doubling (each table is the max of two
+// shifted earlier tables; recipes are compile-time data; as many tables as fit twice per SM, 8 for
+// the shipped footprint), and then serves ALL heading bins of the launch from them, turning the
+// P = 48 gathers per cell of the reference into ~19 aligned 32-bit shared-memory loads per four
+// cells. Every table is stored in four byte-shifted copies so that the word for any x offset is an
+// aligned LDS.32. Bins whose offset sets coincide (t and t + n_theta/2 for a centrally symmetric
+// footprint -- verified by the planner on the exact offsets, not assumed) are evaluated once per
+// tile and stored to all of them.
 //
 // sm_100a has no native per-byte max (__vmaxu4 is emulated with ~7 instructions). It does have the
 // 3-input VIMNMX3.U16x2. A u16 max is decided by the high byte, so on a raw word (b0,b1,b2,b3) it
@@ -160,12 +163,13 @@ __device__ __forceinline__ void accumulate(uint32_t (&odd)[QPT], uint32_t (&even
     }
 }
 
-// Output phase. A work unit is (bin, half of the tile's rows): one warp computes 16 quad columns x
-// 16 rows of one bin, 8 quads per thread. Thread -> quad column (lane & 15) and rows
-// 8*(lane >> 4) + half + quad_row(j): half-warps sit 8 rows apart, which is bank-conflict free for
-// PW = 2 (mod 4). Warps fetch units from a shared counter, so bins with long and short sample
-// lists balance out. The loads of the next sample pair are issued before the max operations of
-// the current one (software pipelining by hand).
+// Output phase. A work unit is 16 rows of one evaluating bin: one warp computes 16 quad columns x
+// 16 rows, 8 quads per thread. Thread -> quad column (lane & 15) and rows 8*(lane >> 4) + j:
+// half-warps sit 8 rows apart, which is bank-conflict free for PW = 2 (mod 4). Warps fetch units
+// from a shared counter, so bins with long and short sample lists balance out. The loads of the
+// next sample pair are issued before the max operations of the current one (software pipelining
+// by hand). The result is stored to every bin of the evaluating bin's chain that is in the matching
+// class on this tile.
 template <int PW>
 __device__ __forceinline__ void run_units(const FastArgs &a, const uint32_t *sm, const uint8_t *s_cls, const uint8_t *s_lead,
                                           uint32_t n_lead, uint32_t *s_next, int lane, int tx0, int ty0)
