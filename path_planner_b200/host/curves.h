@@ -186,19 +186,25 @@ private:
 
     // ---------------- Reeds-Shepp ----------------
     static constexpr double kRsZero = 10.0 * std::numeric_limits<double>::epsilon();
+    // fmod(x, 2 pi) without the library call where the result is known exactly: |x| < 2 pi leaves x,
+    // 2 pi <= |x| <= 4 pi is one exact subtraction (Sterbenz); fmod itself is exact, so this is bit-identical
+    static double fmod_two_pi(double x)
+    {
+        const double a = fabs(x);
+        if (a < kTwoPi)
+            return x;
+        if (a <= 2.0 * kTwoPi)
+            return x < 0 ? x + kTwoPi : x - kTwoPi;
+        return fmod(x, kTwoPi);
+    }
     static double rs_mod(double x)
     {
-        double v = fmod(x, kTwoPi);
+        double v = fmod_two_pi(x);
         if (v < -kPi)
             v += kTwoPi;
         else if (v > kPi)
             v -= kTwoPi;
         return v;
-    }
-    static void polar(double x, double y, double &r, double &theta)
-    {
-        r = sqrt(x * x + y * y);
-        theta = atan2(y, x);
     }
     static void tau_omega(double u, double v, double xi, double eta, double phi, double &tau, double &omega)
     {
@@ -207,9 +213,17 @@ private:
         tau = (t2 < 0) ? rs_mod(t1 + kPi) : rs_mod(t1);
         omega = rs_mod(tau - u + v - phi);
     }
-    static bool f81(double x, double y, double phi, double &t, double &u, double &v)  // L+S+L+
+    // Every formula receives sin(phi) and cos(phi) (computed once per query; sin is odd and cos even
+    // bit for bit in the host libm, checked in tests/test_curves.py) and the incumbent bound Lmin: a
+    // candidate replaces the incumbent only if |t| + w|u| + |v| < Lmin, so once a partial sum reaches
+    // Lmin the remaining inverse trigonometry is skipped -- the outcome is the same.
+    static bool f81(double x, double y, double phi, double sp, double cp, double Lmin, double &t, double &u, double &v)  // L+S+L+
     {
-        polar(x - sin(phi), y - 1.0 + cos(phi), u, t);
+        const double xi = x - sp, eta = y - 1.0 + cp;
+        u = sqrt(xi * xi + eta * eta);
+        if (!(u < Lmin))
+            return false;
+        t = atan2(eta, xi);
         if (t >= -kRsZero)
         {
             v = rs_mod(phi - t);
@@ -218,14 +232,17 @@ private:
         }
         return false;
     }
-    static bool f82(double x, double y, double phi, double &t, double &u, double &v)  // L+S+R+
+    static bool f82(double x, double y, double phi, double sp, double cp, double Lmin, double &t, double &u, double &v)  // L+S+R+
     {
-        double t1, u1;
-        polar(x + sin(phi), y - 1.0 - cos(phi), u1, t1);
+        const double xi = x + sp, eta = y - 1.0 - cp;
+        double u1 = sqrt(xi * xi + eta * eta);
         u1 = u1 * u1;
         if (u1 >= 4.0)
         {
             u = sqrt(u1 - 4.0);
+            if (!(u < Lmin))
+                return false;
+            const double t1 = atan2(eta, xi);
             const double theta = atan2(2.0, u);
             t = rs_mod(t1 + theta);
             v = rs_mod(t - phi);
@@ -233,34 +250,36 @@ private:
         }
         return false;
     }
-    static bool f83(double x, double y, double phi, double &t, double &u, double &v)  // L+R-L
+    static bool f83(double x, double y, double phi, double sp, double cp, double Lmin, double &t, double &u, double &v)  // L+R-L
     {
-        const double xi = x - sin(phi), eta = y - 1.0 + cos(phi);
-        double u1, theta;
-        polar(xi, eta, u1, theta);
+        const double xi = x - sp, eta = y - 1.0 + cp;
+        const double u1 = sqrt(xi * xi + eta * eta);
         if (u1 <= 4.0)
         {
+            const double theta = atan2(eta, xi);
             u = -2.0 * asin(0.25 * u1);
             t = rs_mod(theta + 0.5 * u + kPi);
             v = rs_mod(phi - t + u);
             return t >= -kRsZero && u <= kRsZero;
         }
+        (void)Lmin;
         return false;
     }
-    static bool f87(double x, double y, double phi, double &t, double &u, double &v)  // L+R+uL-uR-
+    static bool f87(double x, double y, double phi, double sp, double cp, double Lmin, double &t, double &u, double &v)  // L+R+uL-uR-
     {
-        const double xi = x + sin(phi), eta = y - 1.0 - cos(phi), rho = 0.25 * (2.0 + sqrt(xi * xi + eta * eta));
+        const double xi = x + sp, eta = y - 1.0 - cp, rho = 0.25 * (2.0 + sqrt(xi * xi + eta * eta));
         if (rho <= 1.0)
         {
             u = acos(rho);
             tau_omega(u, -u, xi, eta, phi, t, v);
             return t >= -kRsZero && v <= kRsZero;
         }
+        (void)Lmin;
         return false;
     }
-    static bool f88(double x, double y, double phi, double &t, double &u, double &v)  // L+R-uL-uR+
+    static bool f88(double x, double y, double phi, double sp, double cp, double Lmin, double &t, double &u, double &v)  // L+R-uL-uR+
     {
-        const double xi = x + sin(phi), eta = y - 1.0 - cos(phi), rho = (20.0 - xi * xi - eta * eta) / 16.0;
+        const double xi = x + sp, eta = y - 1.0 - cp, rho = (20.0 - xi * xi - eta * eta) / 16.0;
         if (rho >= 0 && rho <= 1)
         {
             u = -acos(rho);
@@ -270,47 +289,52 @@ private:
                 return t >= -kRsZero && v >= -kRsZero;
             }
         }
+        (void)Lmin;
         return false;
     }
-    static bool f89(double x, double y, double phi, double &t, double &u, double &v)  // L+R-S-L-
+    static bool f89(double x, double y, double phi, double sp, double cp, double Lmin, double &t, double &u, double &v)  // L+R-S-L-
     {
-        const double xi = x - sin(phi), eta = y - 1.0 + cos(phi);
-        double rho, theta;
-        polar(xi, eta, rho, theta);
+        const double xi = x - sp, eta = y - 1.0 + cp;
+        const double rho = sqrt(xi * xi + eta * eta);
         if (rho >= 2.0)
         {
             const double r = sqrt(rho * rho - 4.0);
             u = 2.0 - r;
+            if (!(u <= kRsZero) || !(fabs(u) < Lmin))
+                return false;
+            const double theta = atan2(eta, xi);
             t = rs_mod(theta + atan2(r, -2.0));
             v = rs_mod(phi - 0.5 * kPi - t);
             return t >= -kRsZero && u <= kRsZero && v <= kRsZero;
         }
         return false;
     }
-    static bool f810(double x, double y, double phi, double &t, double &u, double &v)  // L+R-S-R-
+    static bool f810(double x, double y, double phi, double sp, double cp, double Lmin, double &t, double &u, double &v)  // L+R-S-R-
     {
-        const double xi = x + sin(phi), eta = y - 1.0 - cos(phi);
-        double rho, theta;
-        polar(-eta, xi, rho, theta);
+        const double xi = x + sp, eta = y - 1.0 - cp;
+        const double rho = sqrt(eta * eta + xi * xi);
         if (rho >= 2.0)
         {
-            t = theta;
             u = 2.0 - rho;
+            if (!(u <= kRsZero) || !(fabs(u) < Lmin))
+                return false;
+            t = atan2(xi, -eta);
             v = rs_mod(t + 0.5 * kPi - phi);
             return t >= -kRsZero && u <= kRsZero && v <= kRsZero;
         }
         return false;
     }
-    static bool f811(double x, double y, double phi, double &t, double &u, double &v)  // L+R-S-L-R+
+    static bool f811(double x, double y, double phi, double sp, double cp, double Lmin, double &t, double &u, double &v)  // L+R-S-L-R+
     {
-        const double xi = x + sin(phi), eta = y - 1.0 - cos(phi);
-        double rho, theta;
-        polar(xi, eta, rho, theta);
+        const double xi = x + sp, eta = y - 1.0 - cp;
+        const double rho = sqrt(xi * xi + eta * eta);
         if (rho >= 2.0)
         {
             u = 4.0 - sqrt(rho * rho - 4.0);
             if (u <= kRsZero)
             {
+                if (!(fabs(u) < Lmin))
+                    return false;
                 t = rs_mod(atan2((4.0 - u) * xi - 2.0 * eta, -2.0 * xi + (u - 4.0) * eta));
                 v = rs_mod(t - phi);
                 return t >= -kRsZero && v >= -kRsZero;
@@ -319,7 +343,7 @@ private:
         return false;
     }
 
-    typedef bool (*Formula)(double, double, double, double &, double &, double &);
+    typedef bool (*Formula)(double, double, double, double, double, double, double &, double &, double &);
     // layout of (t, u, v) over the five segments: 0 tuv, 1 vut, 2 t,u,-u,v, 3 t,u,u,v,
     // 4 t,-pi/2,u,v, 5 v,u,-pi/2,t, 6 t,-pi/2,u,-pi/2,v
     static void lay(Word &w, const char *segs, int layout, double s, double t, double u, double v)
@@ -345,14 +369,16 @@ private:
         }
     }
     // one formula under the four symmetries; plain / mirrored give the segment letters
-    static void four_ways(Formula f, double x, double y, double phi, const char *plain, const char *mirrored, int layout,
-                          double u_weight, double &Lmin, Word &best)
+    static void four_ways(Formula f, double x, double y, double phi, double sphi, double cphi, const char *plain,
+                          const char *mirrored, int layout, double u_weight, double &Lmin, Word &best)
     {
         const double sx[4] = {1, -1, 1, -1}, sy[4] = {1, 1, -1, -1}, sp[4] = {1, -1, -1, 1}, sg[4] = {1, -1, 1, -1};
         for (int k = 0; k < 4; ++k)
         {
             double t, u, v, L;
-            if (f(sx[k] * x, sy[k] * y, sp[k] * phi, t, u, v) && Lmin > (L = fabs(t) + u_weight * fabs(u) + fabs(v)))
+            // bound on |u| alone: w|u| >= |u| for w >= 1
+            if (f(sx[k] * x, sy[k] * y, sp[k] * phi, sp[k] * sphi, cphi, Lmin, t, u, v) &&
+                Lmin > (L = fabs(t) + u_weight * fabs(u) + fabs(v)))
             {
                 lay(best, k >= 2 ? mirrored : plain, layout, sg[k], t, u, v);
                 Lmin = L;
@@ -364,22 +390,23 @@ private:
         Word best;
         best.seg[0] = 'L'; best.seg[1] = 'R'; best.seg[2] = 'L';
         double Lmin = best.total;
-        four_ways(f81, x, y, phi, "LSL--", "RSR--", 0, 1.0, Lmin, best);
-        four_ways(f82, x, y, phi, "LSR--", "RSL--", 0, 1.0, Lmin, best);
+        const double sphi = sin(phi), cphi = cos(phi);
+        four_ways(f81, x, y, phi, sphi, cphi, "LSL--", "RSR--", 0, 1.0, Lmin, best);
+        four_ways(f82, x, y, phi, sphi, cphi, "LSR--", "RSL--", 0, 1.0, Lmin, best);
         Lmin = best.total;
-        four_ways(f83, x, y, phi, "LRL--", "RLR--", 0, 1.0, Lmin, best);
-        const double xb = x * cos(phi) + y * sin(phi), yb = x * sin(phi) - y * cos(phi);
-        four_ways(f83, xb, yb, phi, "LRL--", "RLR--", 1, 1.0, Lmin, best);
+        four_ways(f83, x, y, phi, sphi, cphi, "LRL--", "RLR--", 0, 1.0, Lmin, best);
+        const double xb = x * cphi + y * sphi, yb = x * sphi - y * cphi;
+        four_ways(f83, xb, yb, phi, sphi, cphi, "LRL--", "RLR--", 1, 1.0, Lmin, best);
         Lmin = best.total;
-        four_ways(f87, x, y, phi, "LRLR-", "RLRL-", 2, 2.0, Lmin, best);
-        four_ways(f88, x, y, phi, "LRLR-", "RLRL-", 3, 2.0, Lmin, best);
+        four_ways(f87, x, y, phi, sphi, cphi, "LRLR-", "RLRL-", 2, 2.0, Lmin, best);
+        four_ways(f88, x, y, phi, sphi, cphi, "LRLR-", "RLRL-", 3, 2.0, Lmin, best);
         Lmin = best.total - 0.5 * kPi;
-        four_ways(f89, x, y, phi, "LRSL-", "RLSR-", 4, 1.0, Lmin, best);
-        four_ways(f810, x, y, phi, "LRSR-", "RLSL-", 4, 1.0, Lmin, best);
-        four_ways(f89, xb, yb, phi, "LSRL-", "RSLR-", 5, 1.0, Lmin, best);
-        four_ways(f810, xb, yb, phi, "RSRL-", "LSLR-", 5, 1.0, Lmin, best);
+        four_ways(f89, x, y, phi, sphi, cphi, "LRSL-", "RLSR-", 4, 1.0, Lmin, best);
+        four_ways(f810, x, y, phi, sphi, cphi, "LRSR-", "RLSL-", 4, 1.0, Lmin, best);
+        four_ways(f89, xb, yb, phi, sphi, cphi, "LSRL-", "RSLR-", 5, 1.0, Lmin, best);
+        four_ways(f810, xb, yb, phi, sphi, cphi, "RSRL-", "LSLR-", 5, 1.0, Lmin, best);
         Lmin = best.total - kPi;
-        four_ways(f811, x, y, phi, "LRSLR", "RLSRL", 6, 1.0, Lmin, best);
+        four_ways(f811, x, y, phi, sphi, cphi, "LRSLR", "RLSRL", 6, 1.0, Lmin, best);
         return best;
     }
 

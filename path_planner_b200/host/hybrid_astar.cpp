@@ -18,7 +18,10 @@ float wrap_angle_f(float a)
 }
 double wrap_angle_d(double a)
 {
-    const double r = std::fmod(a + M_PI, 2.0 * M_PI);
+    // fmod(s, 2 pi) is s itself for |s| < 2 pi and one exact subtraction (Sterbenz) for 2 pi <= |s| <= 4 pi;
+    // fmod is exact, so skipping the library call there gives the same bits
+    const double two_pi = 2.0 * M_PI, s = a + M_PI, m = std::fabs(s);
+    const double r = m < two_pi ? s : (m <= 2.0 * two_pi ? (s < 0.0 ? s + two_pi : s - two_pi) : std::fmod(s, two_pi));
     return r <= 0.0 ? r + M_PI : r - M_PI;
 }
 }  // namespace
@@ -119,8 +122,7 @@ float HybridAStar::heuristic(const Tables &tb, const Pose &at) const
 {
     const Pose &goal = _goal->at;
     const SE2 from{static_cast<double>(at.x), static_cast<double>(at.y), wrap_angle_d(static_cast<double>(at.theta * _bin))};
-    const SE2 to{static_cast<double>(goal.x), static_cast<double>(goal.y), wrap_angle_d(static_cast<double>(goal.theta * _bin))};
-    const float motion_h = static_cast<float>(_curves->distance(from, to));
+    const float motion_h = static_cast<float>(_curves->distance(from, _goal_se2));
 
     const unsigned int sx = static_cast<unsigned int>(at.x), sy = static_cast<unsigned int>(at.y);
     const float field = tb.field[static_cast<size_t>(sy) * _W + sx];
@@ -274,6 +276,8 @@ bool HybridAStar::plan(const Tables &tb, const Pose &start_world, const Pose &go
     };
     _start = place(start_world);
     _goal = place(goal_world);
+    _goal_se2 = {static_cast<double>(_goal->at.x), static_cast<double>(_goal->at.y),
+                 wrap_angle_d(static_cast<double>(_goal->at.theta * _bin))};  // the same for every heuristic call
 
     // cacheObstacleHeuristic() succeeds iff the start cell is reached from the goal (:161-164)
     const unsigned int scx = static_cast<unsigned int>(_start->at.x), scy = static_cast<unsigned int>(_start->at.y);

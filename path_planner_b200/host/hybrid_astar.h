@@ -97,5 +97,6 @@ private:
     std::unique_ptr<CurveSpace> _curves;
     std::unordered_map<unsigned int, Node> _graph;
     Node *_start = nullptr, *_goal = nullptr;
+    SE2 _goal_se2{0.0, 0.0, 0.0};
 };
 }  // namespace ppb
