@@ -55,7 +55,10 @@ pp_status pp_create(pp_handle *out, int device)
     pp_ctx *h = new pp_ctx();
     h->device = device;
     if ((e = cudaSetDevice(device)) != cudaSuccess || (e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking)) != cudaSuccess ||
+        (e = cudaStreamCreateWithFlags(&h->aux, cudaStreamNonBlocking)) != cudaSuccess ||
         (e = cudaEventCreate(&h->ev_start)) != cudaSuccess || (e = cudaEventCreate(&h->ev_stop)) != cudaSuccess ||
+        (e = cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming)) != cudaSuccess ||
+        (e = cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming)) != cudaSuccess ||
         (e = cudaHostAlloc(reinterpret_cast<void **>(&h->h_counter), 64, cudaHostAllocDefault)) != cudaSuccess)
     {
         pp_fail(nullptr, PP_ERR_CUDA, "pp_create: %s", cudaGetErrorString(e));
@@ -72,6 +75,8 @@ pp_status pp_destroy(pp_handle h)
         return PP_OK;
     cudaSetDevice(h->device);
     cudaStreamSynchronize(h->stream);
+    if (h->aux)
+        cudaStreamSynchronize(h->aux);
     pp_se2_plan_free(h);
     pp_comm_destroy(h);
     cudaFree(h->d_cost);
@@ -97,6 +102,9 @@ pp_status pp_destroy(pp_handle h)
     cudaFreeHost(h->h_vol_mirror);
     cudaFreeHost(h->h_field_mirror);
     cudaFreeHost(h->h_counter);
+    cudaEventDestroy(h->ev_fork);
+    cudaEventDestroy(h->ev_join);
+    cudaStreamDestroy(h->aux);
     cudaEventDestroy(h->ev_start);
     cudaEventDestroy(h->ev_stop);
     cudaStreamDestroy(h->stream);

@@ -13,6 +13,8 @@ struct pp_ctx
 {
     int device = 0;
     cudaStream_t stream = nullptr;
+    cudaStream_t aux = nullptr;  // side stream: the exact work-list kernel runs beside the tiled kernel
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     cudaEvent_t ev_start = nullptr, ev_stop = nullptr;
     std::string err;
     uint64_t launches = 0;  // kernels launched by this library on this handle

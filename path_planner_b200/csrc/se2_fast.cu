@@ -1150,10 +1150,9 @@ pp_status pp_se2_launch_fast(pp_handle h, uint32_t x0, uint32_t y0, uint32_t x1,
         PP_REQUIRE(h, n > 0, PP_ERR_RANGE, "a single heading bin needs more than %d sample words", MAX_LIST_WORDS);
         args.t_first = t;
         args.n_t = n;
-        launch_fast(pl->PW, pl->lib_id, grid, pl->smem_bytes, h->stream, args);
-        h->launches++;
-        PP_CUDA(h, cudaGetLastError());
-        // bookkeeping + the exact path for the (tile, bin) pairs outside uniform ranges
+        // bookkeeping + the exact path for the (tile, bin) pairs outside uniform ranges: queued first, on the
+        // side stream, so that its CTAs share the SMs with the tiled kernel instead of running after it
+        bool forked = false;
         for (uint32_t k = 0; k < n; ++k)
         {
             const uint32_t nw = pl->work_off[t + k + 1] - pl->work_off[t + k];
@@ -1171,6 +1170,7 @@ pp_status pp_se2_launch_fast(pp_handle h, uint32_t x0, uint32_t y0, uint32_t x1,
                 pp_status s = pp_se2_generic_worklist(h, pl->d_work + 2 * static_cast<size_t>(w0), w1 - w0);
                 if (s != PP_OK)
                     return s;
+                forked = true;
             }
             else
             {
@@ -1201,8 +1201,18 @@ pp_status pp_se2_launch_fast(pp_handle h, uint32_t x0, uint32_t y0, uint32_t x1,
                     pp_status s = pp_se2_generic_worklist(h, pl->d_region_work, static_cast<uint32_t>(pl->region_work.size() / 2));
                     if (s != PP_OK)
                         return s;
+                    forked = true;
                 }
             }
+        }
+        launch_fast(pl->PW, pl->lib_id, grid, pl->smem_bytes, h->stream, args);
+        h->launches++;
+        PP_CUDA(h, cudaGetLastError());
+        if (forked)
+        {
+            pp_status s = pp_se2_join_aux(h);
+            if (s != PP_OK)
+                return s;
         }
         t += n;
     }

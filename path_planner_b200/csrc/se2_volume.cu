@@ -162,7 +162,7 @@ size_t generic_smem_bytes(int R)
 
 // Launch the generic kernel over region [x0,x1) x [y0,y1) for the handle's bins.
 static pp_status launch_generic(pp_handle h, uint32_t x0, uint32_t y0, uint32_t x1, uint32_t y1, const uint32_t *d_worklist,
-                                uint32_t n_work)
+                                uint32_t n_work, cudaStream_t stream)
 {
     GenericArgs a;
     a.cost = h->d_cost;
@@ -206,7 +206,7 @@ static pp_status launch_generic(pp_handle h, uint32_t x0, uint32_t y0, uint32_t 
         grid = dim3(tiles_x, tiles_y, chunks);
         h->stat_generic_tiles += tiles * n_t;
     }
-    se2_generic_kernel<<<grid, GT_THREADS, smem, h->stream>>>(a);
+    se2_generic_kernel<<<grid, GT_THREADS, smem, stream>>>(a);
     h->launches++;
     PP_CUDA(h, cudaGetLastError());
     return PP_OK;
@@ -225,7 +225,7 @@ pp_status pp_se2_launch(pp_handle h, uint32_t x0, uint32_t y0, uint32_t x1, uint
         if (s != PP_INTERNAL_DECLINED)
             return s;
     }
-    return launch_generic(h, x0, y0, x1, y1, nullptr, 0);
+    return launch_generic(h, x0, y0, x1, y1, nullptr, 0, h->stream);
 }
 
 pp_status pp_se2_generic_worklist(pp_handle h, const uint32_t *d_worklist, uint32_t n_work)
@@ -233,7 +233,17 @@ pp_status pp_se2_generic_worklist(pp_handle h, const uint32_t *d_worklist, uint3
     if (n_work == 0)
         return PP_OK;
     h->stat_generic_tiles += n_work;
-    return launch_generic(h, 0, 0, h->W, h->H, d_worklist, n_work);
+    // fork: the side stream waits for what is already queued (costmap / work-list uploads, earlier builds)
+    PP_CUDA(h, cudaEventRecord(h->ev_fork, h->stream));
+    PP_CUDA(h, cudaStreamWaitEvent(h->aux, h->ev_fork, 0));
+    return launch_generic(h, 0, 0, h->W, h->H, d_worklist, n_work, h->aux);
+}
+
+pp_status pp_se2_join_aux(pp_handle h)
+{
+    PP_CUDA(h, cudaEventRecord(h->ev_join, h->aux));
+    PP_CUDA(h, cudaStreamWaitEvent(h->stream, h->ev_join, 0));
+    return PP_OK;
 }
 
 extern "C" {
