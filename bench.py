@@ -184,7 +184,7 @@ def run_reference(args, rank):
         return
     cores = os.cpu_count() or 1
     cost = make_inputs()
-    per_step = max(2.0, min(20.0, 120.0 / max(1, args.steps + args.warmup)))
+    per_step = max(0.5, min(20.0, 90.0 / max(1, args.steps + args.warmup)))  # the whole arm stays within a few minutes
     vals = []
     kind = sample = None
     for i in range(args.warmup + args.steps):

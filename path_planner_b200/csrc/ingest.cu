@@ -65,15 +65,32 @@ __global__ void __launch_bounds__(IT_THREADS) ingest_kernel(const IngestArgs a)
     for (int i = threadIdx.x; i <= R * R; i += IT_THREADS)
         s_tab[i] = a.infl[i];
     int any_lethal = 0;
-    for (int i = threadIdx.x; i < cols * rows; i += IT_THREADS)
+    constexpr int BATCH = 8;  // global loads in flight per thread: the staging loop is latency-bound otherwise
+    for (int i0 = threadIdx.x; i0 < cols * rows; i0 += BATCH * IT_THREADS)
     {
-        const int r = i / cols, c = i - r * cols;
-        const int x = x_base + c, y = y_base + r;
-        uint8_t v = FREE_SPACE;  // cells outside the grid hold no obstacle
-        if (x >= 0 && y >= 0 && x < static_cast<int>(a.W) && y < static_cast<int>(a.H))
-            v = interpret(static_cast<uint8_t>(a.occ[static_cast<size_t>(y) * a.W + x]), a);
-        s_stat[r * PITCH + c] = v;
-        any_lethal |= (v == LETHAL);
+        int8_t raw[BATCH];
+        bool inside[BATCH];
+#pragma unroll
+        for (int b = 0; b < BATCH; ++b)
+        {
+            const int i = i0 + b * IT_THREADS;
+            const int r = i / cols, c = i - r * cols;
+            const int x = x_base + c, y = y_base + r;
+            inside[b] = i < cols * rows && x >= 0 && y >= 0 && x < static_cast<int>(a.W) && y < static_cast<int>(a.H);
+            raw[b] = inside[b] ? __ldg(a.occ + static_cast<size_t>(y) * a.W + x) : static_cast<int8_t>(0);
+        }
+#pragma unroll
+        for (int b = 0; b < BATCH; ++b)
+        {
+            const int i = i0 + b * IT_THREADS;
+            if (i >= cols * rows)
+                break;
+            const int r = i / cols, c = i - r * cols;
+            // cells outside the grid hold no obstacle
+            const uint8_t v = inside[b] ? interpret(static_cast<uint8_t>(raw[b]), a) : FREE_SPACE;
+            s_stat[r * PITCH + c] = v;
+            any_lethal |= (v == LETHAL);
+        }
     }
     any_lethal = __syncthreads_or(any_lethal);
 

@@ -92,10 +92,50 @@ bool HybridAStar::goalCell(const Pose &goal_world, unsigned int &gx, unsigned in
 
 HybridAStar::Node *HybridAStar::node(unsigned int index)
 {
-    auto it = _graph.find(index);
-    if (it != _graph.end())
-        return &it->second;
-    return &_graph.emplace(index, Node(index)).first->second;
+    const unsigned int key = index + 1;
+    unsigned int slot = (index * 2654435761u) & _slot_mask;  // Fibonacci hashing; linear probing
+    while (_slot_key[slot] != 0)
+    {
+        if (_slot_key[slot] == key)
+            return &_nodes[_slot_node[slot]];
+        slot = (slot + 1) & _slot_mask;
+    }
+    if ((_nodes.size() + 1) * 2 > _slot_key.size())
+    {
+        growGraph();
+        return node(index);
+    }
+    _slot_key[slot] = key;
+    _slot_node[slot] = static_cast<unsigned int>(_nodes.size());
+    _nodes.emplace_back(index);
+    return &_nodes.back();
+}
+
+void HybridAStar::resetGraph(unsigned int expected_nodes)
+{
+    unsigned int slots = 1024;
+    while (slots < 2 * expected_nodes)
+        slots *= 2;
+    _nodes.clear();
+    _slot_key.assign(slots, 0u);
+    _slot_node.assign(slots, 0u);
+    _slot_mask = slots - 1;
+}
+
+void HybridAStar::growGraph()
+{
+    const unsigned int slots = static_cast<unsigned int>(_slot_key.size()) * 2;
+    _slot_key.assign(slots, 0u);
+    _slot_node.assign(slots, 0u);
+    _slot_mask = slots - 1;
+    for (unsigned int i = 0; i < _nodes.size(); ++i)
+    {
+        unsigned int slot = (_nodes[i].index * 2654435761u) & _slot_mask;
+        while (_slot_key[slot] != 0)
+            slot = (slot + 1) & _slot_mask;
+        _slot_key[slot] = _nodes[i].index + 1;
+        _slot_node[slot] = i;
+    }
 }
 
 // Volume lookup in place of collision_checker.cpp:126-172: cell of the pose, nearest heading bin.
@@ -263,8 +303,7 @@ bool HybridAStar::plan(const Tables &tb, const Pose &start_world, const Pose &go
     if (!inside(start_world) || !inside(goal_world))
         return false;
     const float ox = static_cast<float>(_ox), oy = static_cast<float>(_oy), res = static_cast<float>(_res);
-    _graph.clear();
-    _graph.reserve(100000);
+    resetGraph(32768);
     auto place = [&](const Pose &w) {  // setStart / setGoal, :45-66
         const float x = (w.x - ox) / res, y = (w.y - oy) / res;
         float h = w.theta / _bin + _n_theta_f;
@@ -335,7 +374,7 @@ bool HybridAStar::plan(const Tables &tb, const Pose &start_world, const Pose &go
             if (approach_iterations > static_cast<int>(_p.max_on_approach_iterations) ||
                 iterations + 1 > static_cast<int>(_p.max_iterations))
             {
-                _goal->parent = &_graph.at(best.second);
+                _goal->parent = node(best.second);  // exists: it was queued
                 found = backtrace(_goal, path);
                 break;
             }

@@ -17,9 +17,9 @@
 #include "curves.h"
 
 #include <cstdint>
+#include <deque>
 #include <memory>
 #include <queue>
-#include <unordered_map>
 #include <vector>
 
 namespace ppb
@@ -95,7 +95,16 @@ private:
     float _n_theta_f, _bin, _turn_cells, _tol_cells, _ae_ratio_cells, _ae_tol_cells, _neutral;
     std::vector<Pose> _motions;
     std::unique_ptr<CurveSpace> _curves;
-    std::unordered_map<unsigned int, Node> _graph;
+    // The graph (the reference's std::unordered_map<unsigned, NodeHybrid>, astar_hybrid.h): nodes live in a
+    // deque (stable addresses: the queue and the parent links hold pointers) and are found through an
+    // open-addressing table of node numbers, which costs one probe where the node-based map costs an
+    // allocation per insert and a pointer chase per lookup.
+    std::deque<Node> _nodes;
+    std::vector<unsigned int> _slot_key;  // node index + 1, 0 = empty
+    std::vector<unsigned int> _slot_node; // position in _nodes
+    unsigned int _slot_mask = 0;
+    void resetGraph(unsigned int expected_nodes);
+    void growGraph();
     Node *_start = nullptr, *_goal = nullptr;
     SE2 _goal_se2{0.0, 0.0, 0.0};
 };
