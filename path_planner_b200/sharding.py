@@ -1,6 +1,8 @@
-"""Heading-bin sharding of the SE2 volume over the GPUs of one box: rank g of
-`world` owns bins [g*n/world, (g+1)*n/world). Host-side helpers shared by bench.py and the tests;
-the data path itself (pp_se2_volume_build per rank, pp_se2_volume_allgather) is in the library."""
+"""Sharding of the SE2 volume over the GPUs of one box. Two partitions of the same
+independent units: heading bins -- rank g of `world` owns bins [g*n/world, (g+1)*n/world) -- and map-row
+bands (row_band below; what bench.py --gpus N times as `value`). Host-side helpers shared by bench.py and
+the tests; the data path itself (pp_se2_volume_build per rank, pp_se2_volume_set_rows,
+pp_se2_volume_allgather) is in the library."""
 
 
 def bin_range(n_theta, rank, world):
@@ -36,8 +38,9 @@ def gather_slabs(local_slab, dist):
 
 
 def row_band(height, rank, world, tile_rows=32):
-    """Half-open range of map rows of `rank` for spatial sharding: bands are whole 32-row tiles
-    (the kernel's tile height), as equal as the tile count allows; together they cover [0, height)."""
+    """Half-open range of map rows of `rank` for spatial sharding: bands are whole multiples of 32 rows
+    (a multiple of the kernel's 16-row tile height, also of the optional 32-row build), as equal as the
+    count allows; together they cover [0, height)."""
     if world < 1 or not 0 <= rank < world:
         raise ValueError(f"rank {rank} of {world}")
     tiles = (height + tile_rows - 1) // tile_rows
