@@ -25,8 +25,18 @@ namespace
 constexpr int HT = 32;            // tile edge
 constexpr int HT_THREADS = 256;   // 4 cells per thread
 constexpr int HT_PITCH = HT + 2 + 1;
-constexpr int ROUNDS_PER_CHECK = 16;
-constexpr uint32_t ROUND_GRID = 148 * 8;  // CTAs per relaxation round: they walk the round's work list
+#ifndef PP_HT_CHECK
+#define PP_HT_CHECK 32
+#endif
+#ifndef PP_HT_GRID
+#define PP_HT_GRID 4
+#endif
+constexpr int ROUNDS_PER_CHECK = PP_HT_CHECK;
+#ifndef PP_HT_LOCAL
+#define PP_HT_LOCAL 4
+#endif
+constexpr int HT_LOCAL = PP_HT_LOCAL;  // warp-local relaxations of a band between two block-wide votes
+constexpr uint32_t ROUND_GRID = 148 * PP_HT_GRID;  // CTAs per relaxation round: they walk the round's work list
 
 constexpr uint32_t INACTIVE = 0xFFFFFFFFu;  // tile key: bit pattern of the smallest pending value, or this
 constexpr int N_COUNTERS = 16;              // [0..3] tiles flagged per round, [4] visits, [5] sweeps, [8..11] min key per round
@@ -86,23 +96,42 @@ __global__ void __launch_bounds__(HT_THREADS) heur_round_kernel(float *__restric
     __shared__ float WS[HT][HT];
     __shared__ float WD[HT][HT];
     __shared__ uint32_t edge_min[8];  // smallest new value on each border / corner (bit pattern), INACTIVE if unchanged
-    for (uint32_t entry = blockIdx.x; entry < n_active; entry += gridDim.x)
+    __shared__ float s_travel[512];
+    for (int i = threadIdx.x; i < 512; i += HT_THREADS)
+        s_travel[i] = travel[i];
+    // Pass 1, one list entry per thread: entries outside this round's bucket carry their key over to
+    // the next generation (their chains of dependent atomics run side by side instead of one after the
+    // other), entries inside it are collected for pass 2.
+    __shared__ uint32_t s_mine[HT_THREADS];
+    __shared__ uint32_t s_n_mine;
+    for (uint32_t base = blockIdx.x; base < n_active; base += gridDim.x * HT_THREADS)
     {
-    const uint32_t tile = list_cur[entry];
-    const uint32_t key = cur[tile];
-    __syncthreads();  // every thread has read the key (and is done with the previous tile's shared memory)
-    if (__uint_as_float(key) > threshold)
+    __syncthreads();  // the previous batch's tiles are done with s_mine / the tile arrays
+    if (threadIdx.x == 0)
+        s_n_mine = 0;
+    __syncthreads();
+    const uint32_t entry = base + threadIdx.x * gridDim.x;
+    if (entry < n_active)
     {
-        // not in this round's bucket: carry the key over
-        if (threadIdx.x == 0)
+        const uint32_t tile = list_cur[entry];
+        const uint32_t key = cur[tile];
+        if (__uint_as_float(key) > threshold)
         {
             cur[tile] = INACTIVE;
             if (atomicMin(&nxt[tile], key) == INACTIVE)
                 list_nxt[atomicAdd(&counters[(round + 1) & 3], 1u)] = tile;
             atomicMin(&counters[8 + ((round + 1) & 3)], key);
         }
-        continue;
+        else
+            s_mine[atomicAdd(&s_n_mine, 1u)] = tile;
     }
+    __syncthreads();
+    const uint32_t n_mine = s_n_mine;
+    // Pass 2: relax the collected tiles, one after the other
+    for (uint32_t m = 0; m < n_mine; ++m)
+    {
+    const uint32_t tile = s_mine[m];
+    __syncthreads();  // every thread is done with the previous tile's shared memory
 
     const uint32_t tx = tile % tiles_x, ty = tile / tiles_x;
     const int x0 = static_cast<int>(tx * HT), y0 = static_cast<int>(ty * HT);
@@ -110,57 +139,120 @@ __global__ void __launch_bounds__(HT_THREADS) heur_round_kernel(float *__restric
     const float INF = __int_as_float(0x7f800000);
     if (tid < 8)
         edge_min[tid] = INACTIVE;
-    for (int i = tid; i < (HT + 2) * (HT + 2); i += HT_THREADS)
+    // A tile visit is a chain of latencies, not of bandwidth (a round with a single tile takes as long as
+    // one with hundreds): every global load of the visit -- 34 x 34 field values, 32 x 32 costs -- is
+    // issued before the first one is used, and the travel weights come from the shared-memory copy.
+    constexpr int F_LOADS = ((HT + 2) * (HT + 2) + HT_THREADS - 1) / HT_THREADS;  // 5
+    constexpr int C_LOADS = HT * HT / HT_THREADS;                                 // 4
+    float fv[F_LOADS];
+    uint32_t cv[C_LOADS];
+#pragma unroll
+    for (int j = 0; j < F_LOADS; ++j)
     {
+        const int i = tid + j * HT_THREADS;
         const int r = i / (HT + 2), c = i - r * (HT + 2);
         const int gy = y0 + r - 1, gx = x0 + c - 1;
-        float v = INF;
-        if (gy >= 0 && gy < static_cast<int>(H) && gx >= 0 && gx < static_cast<int>(W))
-            v = field[static_cast<size_t>(gy) * W + gx];
-        F[r][c] = v;
+        fv[j] = INF;
+        if (i < (HT + 2) * (HT + 2) && gy >= 0 && gy < static_cast<int>(H) && gx >= 0 && gx < static_cast<int>(W))
+            fv[j] = field[static_cast<size_t>(gy) * W + gx];
     }
-    for (int i = tid; i < HT * HT; i += HT_THREADS)
+#pragma unroll
+    for (int j = 0; j < C_LOADS; ++j)
     {
+        const int i = tid + j * HT_THREADS;
         const int r = i / HT, c = i - r * HT;
         const int gy = y0 + r, gx = x0 + c;
-        float ws = INF, wd = INF;
-        // border cells are never entered (astar_hybrid.cpp:141), nor cells with cost >= 253 (:143)
+        // border cells are never entered (astar_hybrid.cpp:141), nor cells with cost >= 253 (:143): weight INF
+        cv[j] = 256u;
         if (gy > 0 && gy < static_cast<int>(H) - 1 && gx > 0 && gx < static_cast<int>(W) - 1)
-        {
-            const uint32_t cst = cost[static_cast<size_t>(gy) * W + gx];
-            ws = travel[cst];
-            wd = travel[256 + cst];
-        }
-        WS[r][c] = ws;
-        WD[r][c] = wd;
+            cv[j] = cost[static_cast<size_t>(gy) * W + gx];
+    }
+#pragma unroll
+    for (int j = 0; j < F_LOADS; ++j)
+    {
+        const int i = tid + j * HT_THREADS;
+        const int r = i / (HT + 2), c = i - r * (HT + 2);
+        if (i < (HT + 2) * (HT + 2))
+            F[r][c] = fv[j];
+    }
+#pragma unroll
+    for (int j = 0; j < C_LOADS; ++j)
+    {
+        const int i = tid + j * HT_THREADS;
+        const int r = i / HT, c = i - r * HT;
+        WS[r][c] = cv[j] < 256u ? s_travel[cv[j]] : INF;
+        WD[r][c] = cv[j] < 256u ? s_travel[256 + cv[j]] : INF;
     }
     __syncthreads();
 
-    // thread owns cells (rowq + 8*k, col): a warp works on one row at a time, lane = column, so every
-    // shared-memory access of the relaxation is bank-conflict free (row pitch 35 words)
-    const int col = tid & 31, rowq = tid >> 5;
-    float init[4];
+    // A warp owns a band of 4 consecutive tile rows, lane = column, and keeps its 4 x 32 values and their
+    // travel weights in registers. Left / right neighbours come from the neighbouring lanes by shuffle
+    // (the tile's halo columns, constant during a visit, for lanes 0 and 31), the rows above and below
+    // the band from shared memory, re-read after every block-wide vote. Between two votes a warp relaxes
+    // its band HT_LOCAL times on its own (Jacobi inside the band); stale values across bands are
+    // harmless: values only decrease, towards the same fixed point.
+    const int lane = tid & 31, band = (tid >> 5) * 4, c = lane + 1;
+    float v[4], ws[4], wd[4], edge_l[4], edge_r[4], init[4];
 #pragma unroll
     for (int k = 0; k < 4; ++k)
-        init[k] = F[rowq + 8 * k + 1][col + 1];
+    {
+        const int r = band + k + 1;
+        v[k] = init[k] = F[r][c];
+        ws[k] = WS[r - 1][c - 1];
+        wd[k] = WD[r - 1][c - 1];
+        edge_l[k] = F[r][0];
+        edge_r[k] = F[r][HT + 1];
+    }
     uint32_t iters = 0;
 
     int changed;
     do
     {
         int local = 0;
+        float up[3], dn[3];  // the rows just outside the band: columns c-1, c, c+1
 #pragma unroll
-        for (int k = 0; k < 4; ++k)
+        for (int d = 0; d < 3; ++d)
         {
-            const int r = rowq + 8 * k + 1, c = col + 1;
-            const float ms = fminf(fminf(F[r - 1][c], F[r + 1][c]), fminf(F[r][c - 1], F[r][c + 1]));
-            const float md = fminf(fminf(F[r - 1][c - 1], F[r + 1][c + 1]), fminf(F[r - 1][c + 1], F[r + 1][c - 1]));
-            const float cand = fminf(__fadd_rn(ms, WS[r - 1][c - 1]), __fadd_rn(md, WD[r - 1][c - 1]));
-            if (cand < F[r][c])
+            up[d] = F[band][c - 1 + d];
+            dn[d] = F[band + 5][c - 1 + d];
+        }
+#pragma unroll 1
+        for (int it = 0; it < HT_LOCAL; ++it)
+        {
+            float l[4], r[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
             {
-                F[r][c] = cand;
-                local = 1;
+                l[k] = __shfl_up_sync(0xffffffffu, v[k], 1);
+                r[k] = __shfl_down_sync(0xffffffffu, v[k], 1);
+                if (lane == 0)
+                    l[k] = edge_l[k];
+                if (lane == 31)
+                    r[k] = edge_r[k];
             }
+            float nv[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+            {
+                const float a0 = k == 0 ? up[0] : l[k - 1], a1 = k == 0 ? up[1] : v[k - 1], a2 = k == 0 ? up[2] : r[k - 1];
+                const float b0 = k == 3 ? dn[0] : l[k + 1], b1 = k == 3 ? dn[1] : v[k + 1], b2 = k == 3 ? dn[2] : r[k + 1];
+                const float ms = fminf(fminf(a1, b1), fminf(l[k], r[k]));
+                const float md = fminf(fminf(a0, b2), fminf(a2, b0));
+                nv[k] = fminf(__fadd_rn(ms, ws[k]), __fadd_rn(md, wd[k]));
+            }
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+                if (nv[k] < v[k])
+                {
+                    v[k] = nv[k];
+                    local = 1;
+                }
+        }
+        if (local)
+        {
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+                F[band + k + 1][c] = v[k];
         }
         changed = __syncthreads_or(local);
         ++iters;
@@ -177,14 +269,14 @@ __global__ void __launch_bounds__(HT_THREADS) heur_round_kernel(float *__restric
 #pragma unroll
     for (int k = 0; k < 4; ++k)
     {
-        const int r = rowq + 8 * k, c = col;
-        const float v = F[r + 1][c + 1];
-        if (v < init[k])
+        const int r = band + k, c = lane;
+        const float val = v[k];
+        if (val < init[k])
         {
             const int gy = y0 + r, gx = x0 + c;
             if (gy < static_cast<int>(H) && gx < static_cast<int>(W))
-                field[static_cast<size_t>(gy) * W + gx] = v;
-            const uint32_t vb = __float_as_uint(v);
+                field[static_cast<size_t>(gy) * W + gx] = val;
+            const uint32_t vb = __float_as_uint(val);
             if (r == 0) atomicMin(&edge_min[0], vb);                       // N
             if (r == HT - 1) atomicMin(&edge_min[1], vb);                  // S
             if (c == 0) atomicMin(&edge_min[2], vb);                       // W
@@ -210,7 +302,8 @@ __global__ void __launch_bounds__(HT_THREADS) heur_round_kernel(float *__restric
             atomicMin(&counters[8 + ((round + 1) & 3)], k);
         }
     }
-    }  // work list
+    }  // pass 2
+    }  // batches of the work list
 }
 
 __global__ void heur_finalize_kernel(float *field, size_t n)
