@@ -34,6 +34,9 @@ extern "C" pp_status pp_plan(pp_handle h, const pp_plan_params *params, double r
     PP_REQUIRE(h, !h->fp.empty(), PP_ERR_STATE, "pp_plan: set a footprint first");
     PP_REQUIRE(h, params->motion_type == 1 || params->motion_type == 2, PP_ERR_INVALID, "pp_plan: motion_type must be 1 (Dubins) or 2 (Reeds-Shepp)");
     PP_REQUIRE(h, params->n_theta > 0 && resolution > 0.0, PP_ERR_INVALID, "pp_plan: n_theta and resolution must be positive");
+    // search nodes are numbered in 32 bits, like the reference's (node_hybrid.h: unsigned int index)
+    PP_REQUIRE(h, static_cast<uint64_t>(h->W) * h->H * params->n_theta < 0xFFFFFFFFull, PP_ERR_RANGE,
+               "pp_plan: %ux%ux%u search nodes do not fit the 32-bit node numbering", h->W, h->H, params->n_theta);
     *n_points_out = 0;
     *iterations_out = 0;
     *found_out = 0;
