@@ -99,6 +99,7 @@ pp_status pp_destroy(pp_handle h)
     cudaFree(h->d_topk_d2);
     cudaFree(h->d_topk_cnt);
     cudaFreeHost(h->h_stage);
+    cudaFreeHost(h->h_teb);
     cudaFreeHost(h->h_vol_mirror);
     cudaFreeHost(h->h_field_mirror);
     cudaFreeHost(h->h_counter);

@@ -78,6 +78,8 @@ struct pp_ctx
     double *d_topk_d2 = nullptr;
     uint32_t *d_topk_cnt = nullptr;
     size_t topk_cap = 0, topk_q_cap = 0;
+    uint8_t *h_teb = nullptr;  // pinned landing buffer of the TEB results (every TEB call synchronises before it returns)
+    size_t teb_host_cap = 0;
 
     // N2 ingestion
     int8_t *d_occ = nullptr;

@@ -14,6 +14,8 @@
 //      than the scan it saves; the kernel is launch-latency bound.
 #include "pp_internal.h"
 
+#include <cstring>
+
 #include <cmath>
 #include <algorithm>
 
@@ -125,6 +127,7 @@ __global__ void extract_emit_kernel(ExtractArgs a, const uint32_t *col_offsets, 
 constexpr int RK_THREADS = 256;
 constexpr int RK_CAP = 3072;  // hits buffered per query before a reduction to the K best
 constexpr int RK_MAXK = 64;
+constexpr int RK_BATCH = 4;   // points per thread between two block barriers of the scan
 
 struct Key
 {
@@ -141,8 +144,6 @@ __global__ void __launch_bounds__(RK_THREADS) radius_topk_kernel(const double *_
     __shared__ unsigned long long s_d2[RK_CAP + RK_MAXK];
     __shared__ uint32_t s_idx[RK_CAP + RK_MAXK];
     __shared__ uint32_t s_count;
-    __shared__ Key s_warp[RK_THREADS / 32];
-    __shared__ uint32_t s_warp_slot[RK_THREADS / 32];
     __shared__ unsigned long long s_best_d2[RK_MAXK];
     __shared__ uint32_t s_best_idx[RK_MAXK];
     __shared__ uint32_t s_nbest;
@@ -171,54 +172,44 @@ __global__ void __launch_bounds__(RK_THREADS) radius_topk_kernel(const double *_
         __syncthreads();
         n += s_nbest;
         const uint32_t want = min(K, n);
-        for (uint32_t r = 0; r < want; ++r)
+        // K rounds of arg-min by warp 0 alone: shuffles instead of block barriers (a few hundred candidates)
+        if (warp == 0)
         {
-            Key best = {EMPTY, 0xFFFFFFFFu};
-            uint32_t slot = 0xFFFFFFFFu;
-            for (uint32_t i = tid; i < n; i += RK_THREADS)
+            for (uint32_t r = 0; r < want; ++r)
             {
-                const Key k = {s_d2[i], s_idx[i]};
-                if (key_less(k, best))
+                Key best = {EMPTY, 0xFFFFFFFFu};
+                uint32_t slot = 0xFFFFFFFFu;
+                for (uint32_t i = lane; i < n; i += 32)
                 {
-                    best = k;
-                    slot = i;
-                }
-            }
-#pragma unroll
-            for (int d = 16; d > 0; d >>= 1)
-            {
-                Key o;
-                o.d2 = __shfl_down_sync(0xffffffffu, best.d2, d);
-                o.idx = __shfl_down_sync(0xffffffffu, best.idx, d);
-                const uint32_t oslot = __shfl_down_sync(0xffffffffu, slot, d);
-                if (key_less(o, best))
-                {
-                    best = o;
-                    slot = oslot;
-                }
-            }
-            if (lane == 0)
-            {
-                s_warp[warp] = best;
-                s_warp_slot[warp] = slot;
-            }
-            __syncthreads();
-            if (tid == 0)
-            {
-                Key b = s_warp[0];
-                uint32_t bs = s_warp_slot[0];
-                for (int w = 1; w < RK_THREADS / 32; ++w)
-                    if (key_less(s_warp[w], b))
+                    const Key k = {s_d2[i], s_idx[i]};
+                    if (key_less(k, best))
                     {
-                        b = s_warp[w];
-                        bs = s_warp_slot[w];
+                        best = k;
+                        slot = i;
                     }
-                s_best_d2[r] = b.d2;
-                s_best_idx[r] = b.idx;
-                s_d2[bs] = EMPTY;  // taken
-                s_idx[bs] = 0xFFFFFFFFu;
+                }
+#pragma unroll
+                for (int d = 16; d > 0; d >>= 1)
+                {
+                    Key o;
+                    o.d2 = __shfl_xor_sync(0xffffffffu, best.d2, d);
+                    o.idx = __shfl_xor_sync(0xffffffffu, best.idx, d);
+                    const uint32_t oslot = __shfl_xor_sync(0xffffffffu, slot, d);
+                    if (key_less(o, best))
+                    {
+                        best = o;
+                        slot = oslot;
+                    }
+                }
+                if (lane == 0)
+                {
+                    s_best_d2[r] = best.d2;
+                    s_best_idx[r] = best.idx;
+                    s_d2[slot] = EMPTY;  // taken
+                    s_idx[slot] = 0xFFFFFFFFu;
+                }
+                __syncwarp();
             }
-            __syncthreads();
         }
         if (tid == 0)
         {
@@ -228,31 +219,41 @@ __global__ void __launch_bounds__(RK_THREADS) radius_topk_kernel(const double *_
         __syncthreads();
     };
 
-    for (uint32_t base = 0; base < N; base += RK_THREADS)
+    for (uint32_t base = 0; base < N; base += RK_BATCH * RK_THREADS)
     {
-        if (s_count + RK_THREADS > RK_CAP)  // uniform across the block (read after a barrier)
+        if (s_count + RK_BATCH * RK_THREADS > RK_CAP)  // uniform across the block (read after a barrier)
             select_best();
-        const uint32_t i = base + tid;
-        bool hit = false;
-        double d2 = 0.0;
-        if (i < N)
+        // RK_BATCH points per thread between two barriers, all loads issued first
+        double px[RK_BATCH], py[RK_BATCH];
+#pragma unroll
+        for (int b = 0; b < RK_BATCH; ++b)
         {
-            const double dx = __dsub_rn(qx, pts[2 * static_cast<size_t>(i)]);
-            d2 = __dadd_rn(d2, __dmul_rn(dx, dx));
-            const double dy = __dsub_rn(qy, pts[2 * static_cast<size_t>(i) + 1]);
-            d2 = __dadd_rn(d2, __dmul_rn(dy, dy));
-            hit = d2 < radius_arg;
+            const uint32_t i = base + b * RK_THREADS + tid;
+            px[b] = i < N ? pts[2 * static_cast<size_t>(i)] : 0.0;
+            py[b] = i < N ? pts[2 * static_cast<size_t>(i) + 1] : 0.0;
         }
-        const unsigned ballot = __ballot_sync(0xffffffffu, hit);
-        uint32_t warp_base = 0;
-        if (lane == 0 && ballot)
-            warp_base = atomicAdd(&s_count, __popc(ballot));
-        warp_base = __shfl_sync(0xffffffffu, warp_base, 0);
-        if (hit)
+#pragma unroll
+        for (int b = 0; b < RK_BATCH; ++b)
         {
-            const uint32_t slot = warp_base + __popc(ballot & ((1u << lane) - 1u));
-            s_d2[slot] = static_cast<unsigned long long>(__double_as_longlong(d2));
-            s_idx[slot] = i;
+            const uint32_t i = base + b * RK_THREADS + tid;
+            // L2_Simple_Adaptor::evalMetric (nanoflann.hpp:627-638): (0 + dx*dx) + dy*dy in double, no contraction
+            double d2 = 0.0;
+            const double dx = __dsub_rn(qx, px[b]);
+            d2 = __dadd_rn(d2, __dmul_rn(dx, dx));
+            const double dy = __dsub_rn(qy, py[b]);
+            d2 = __dadd_rn(d2, __dmul_rn(dy, dy));
+            const bool hit = i < N && d2 < radius_arg;
+            const unsigned ballot = __ballot_sync(0xffffffffu, hit);
+            uint32_t warp_base = 0;
+            if (lane == 0 && ballot)
+                warp_base = atomicAdd(&s_count, __popc(ballot));
+            warp_base = __shfl_sync(0xffffffffu, warp_base, 0);
+            if (hit)
+            {
+                const uint32_t slot = warp_base + __popc(ballot & ((1u << lane) - 1u));
+                s_d2[slot] = static_cast<unsigned long long>(__double_as_longlong(d2));
+                s_idx[slot] = i;
+            }
         }
         __syncthreads();
     }
@@ -351,6 +352,19 @@ pp_status pp_radius_topk(pp_handle h, const double *pts_xy, uint32_t N, const do
         h->topk_cap = out_n;
     }
     PP_CUDA(h, pp_reserve(h->d_topk_cnt, h->topk_q_cap, static_cast<size_t>(Q)));
+    // Results land in a pinned buffer of their own and are copied out on the host: three device-to-host
+    // copies into pageable memory are staged and synchronised by the driver one by one, which costs more
+    // than the kernel. (The few KB of queries go down inline with the copy command.)
+    const size_t d2_bytes = out_n * sizeof(double), idx_bytes = out_n * sizeof(uint32_t), cnt_bytes = Q * sizeof(uint32_t);
+    if (d2_bytes + idx_bytes + cnt_bytes > h->teb_host_cap)
+    {
+        if (h->h_teb)
+            PP_CUDA(h, cudaFreeHost(h->h_teb));
+        h->h_teb = nullptr;
+        h->teb_host_cap = 0;
+        PP_CUDA(h, cudaHostAlloc(reinterpret_cast<void **>(&h->h_teb), d2_bytes + idx_bytes + cnt_bytes, cudaHostAllocDefault));
+        h->teb_host_cap = d2_bytes + idx_bytes + cnt_bytes;
+    }
     PP_CUDA(h, cudaMemcpyAsync(h->d_queries, queries_xy, sizeof(double) * 2 * Q, cudaMemcpyHostToDevice, h->stream));
     radius_topk_kernel<<<Q, RK_THREADS, 0, h->stream>>>(d_pts, N, h->d_queries, radius_arg, K, h->d_topk_idx, h->d_topk_d2,
                                                         h->d_topk_cnt);
@@ -358,10 +372,14 @@ pp_status pp_radius_topk(pp_handle h, const double *pts_xy, uint32_t N, const do
     PP_CUDA(h, cudaGetLastError());
     h->topk_Q = Q;
     h->topk_K = K;
-    PP_CUDA(h, cudaMemcpyAsync(idx_out, h->d_topk_idx, out_n * sizeof(uint32_t), cudaMemcpyDeviceToHost, h->stream));
-    PP_CUDA(h, cudaMemcpyAsync(d2_out, h->d_topk_d2, out_n * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
-    PP_CUDA(h, cudaMemcpyAsync(cnt_out, h->d_topk_cnt, Q * sizeof(uint32_t), cudaMemcpyDeviceToHost, h->stream));
+    uint8_t *s_d2 = h->h_teb, *s_idx = s_d2 + d2_bytes, *s_cnt = s_idx + idx_bytes;
+    PP_CUDA(h, cudaMemcpyAsync(s_d2, h->d_topk_d2, d2_bytes, cudaMemcpyDeviceToHost, h->stream));
+    PP_CUDA(h, cudaMemcpyAsync(s_idx, h->d_topk_idx, idx_bytes, cudaMemcpyDeviceToHost, h->stream));
+    PP_CUDA(h, cudaMemcpyAsync(s_cnt, h->d_topk_cnt, cnt_bytes, cudaMemcpyDeviceToHost, h->stream));
     PP_CUDA(h, cudaStreamSynchronize(h->stream));
+    std::memcpy(d2_out, s_d2, d2_bytes);
+    std::memcpy(idx_out, s_idx, idx_bytes);
+    std::memcpy(cnt_out, s_cnt, cnt_bytes);
     return PP_OK;
 }
 
