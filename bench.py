@@ -450,6 +450,30 @@ def main():
             line["plan"][name] = {"ms": r["tables_ms"] + r["search_ms"], "tables_ms": r["tables_ms"], "search_ms": r["search_ms"],
                                   "iterations": r["iterations"], "path_poses": int(len(r["path"])), "found": bool(r["ok"])}
         hp.close()
+        # K0: costmap upload over the host link: pinned, pageable (staged), one dirty rectangle
+        hu = capi.Handle(local_rank)
+        pageable = np.ascontiguousarray(cost)
+        up = {}
+        for key, src, pinned in (("h2d_pinned_GBps", cost_pinned, True), ("h2d_pageable_staged_GBps", pageable, False)):
+            hu.costmap_upload(src, pinned=pinned)
+            hu.sync()
+            t = time.perf_counter()
+            for _ in range(10):
+                hu.costmap_upload(src, pinned=pinned)
+            hu.sync()
+            up[key] = W * H * 10 / (time.perf_counter() - t) / 1e9
+        patch = np.ascontiguousarray(cost[1000:1256, 2000:2256])
+        hu.costmap_update_rect(2000, 1000, patch)
+        hu.sync()
+        t = time.perf_counter()
+        for _ in range(50):
+            hu.costmap_update_rect(2000, 1000, patch)
+        hu.sync()
+        up["rect_256x256_us"] = 1e6 * (time.perf_counter() - t) / 50
+        up["d2h_pinned_GBps_volume_download"] = W * H * N_THETA / (e2e["ms_per_step"] * 1e-3) / 1e9 if world == 1 else None
+        up["bytes"] = W * H
+        line["upload"] = up
+        hu.close()
         # N2 ingestion on the same map: occupancy grid -> static layer + inflation -> costmap, on its own handle
         hi = capi.Handle(local_rank)
         occ = occupancy_of(cost)
