@@ -930,7 +930,10 @@ pp_status build_plan(pp_handle h, int effort)
     // measured on B200 (tools/probe_tables.py).
     pl->few_bins = h->t_end - h->t_begin <= FEW_BINS;
     if (pl->few_bins)
-        slots = std::min(slots, 3);
+    {
+        const char *few = getenv("PP_SE2_FEW_TABLES");  // tuning knob for experiments
+        slots = std::min(slots, few ? std::max(1, atoi(few)) : 3);
+    }
     if (const char *cap = getenv("PP_SE2_MAX_TABLES"))  // tuning knob for experiments
         slots = std::max(1, std::min(slots, atoi(cap)));
     if (slots < 1)

@@ -8,7 +8,7 @@ if len(sys.argv) > 1:
     cost = make_costmap(4096, 4096, seed=1)
     h = capi.Handle(0); h.costmap_upload(cost); h.footprint_from_boundary(0.05, [0.64, 0.46], True)
     out = {}
-    for nb in (72, 36, 18, 9):
+    for nb in (72, 18, 12, 9):
         for _ in range(3): h.se2_volume_build(72, 0.5, 0.5, 0.0, 0, nb)
         h.sync(); ts = []
         for _ in range(5):
@@ -16,6 +16,6 @@ if len(sys.argv) > 1:
         out[nb] = (round(float(np.mean(ts)), 3), round(h.se2_volume_stats()["samples_per_cell"], 1))
     print(sys.argv[1], out)
 else:
-    for n in (1, 2, 3, 5, 7, 9, 11, 12):
-        env = dict(os.environ, PP_SE2_MAX_TABLES=str(n))
+    for n in (2, 3, 4, 5, 6, 8):
+        env = dict(os.environ, PP_SE2_MAX_TABLES=str(n), PP_SE2_FEW_TABLES=str(n))
         subprocess.run([sys.executable, __file__, str(n)], env=env)
