@@ -64,6 +64,7 @@ class ClockSampler:
             self.nv = pynvml
             self.dev = pynvml.nvmlDeviceGetHandleByIndex(gpu_index)
             self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self.dev, pynvml.NVML_CLOCK_SM))
+            sys.setswitchinterval(5e-4)  # the timed loop is a tight run of short ctypes calls: let the poller in often
             self.thread = threading.Thread(target=self._poll, daemon=True)
             self.thread.start()
         except Exception:
