@@ -282,20 +282,22 @@ __device__ __forceinline__ void run_units(const FastArgs &a, const uint32_t *sm,
     }
 }
 
-// Shared-memory geometry, fixed by the row pitch so that every table address is an immediate:
-// PW = 22 words holds a halo of up to 10 cells, PW = 26 up to 15. The tables sit between two guard
+// Shared-memory geometry, compile-time (row pitch and halo are template parameters) so that every table
+// address is an immediate: PW = 22 words holds a halo of up to 10 cells, PW = 26 up to 15. The tables sit between two guard
 // regions, so a recipe may read a few rows before the first / after the last table without a bounds
 // test: such words only feed entries whose brick leaves the staged region, and those are never
 // sampled (a sample's brick lies inside the offset set, which lies inside the halo).
-template <int PW>
+template <int PW, int HALO_>
 struct Geo
 {
-    static constexpr int HALO = PW == 22 ? 10 : MAX_R;
+    static constexpr int HALO = HALO_;
     static constexpr int ROWS = FT_H + 2 * HALO;
     static constexpr int CW = ROWS * PW;     // words per table copy
     static constexpr int GUARD = 4 * PW + 4;  // words; recipes reach at most 4 rows + 1 word away
     static_assert(4 + FT_W + 2 * HALO <= 4 * PW, "row pitch too small for the halo");
 };
+// halos with an instantiation: 7..10 cells at 22 words per row, 11..15 at 26
+constexpr int halo_for(int pw, int reach) { return pw == 22 ? (reach < 7 ? 7 : reach) : (reach < 11 ? 11 : reach); }
 
 // Table build. Recipes and levels are compile-time constants (forced through template arguments):
 // the tables of one level are consecutive in the library, the first M of them are built by
@@ -341,10 +343,10 @@ __device__ __forceinline__ void for_each_index(std::integer_sequence<int, Ks...>
 }
 
 // the first M tables of level LVL (M >= 1, LVL >= 1)
-template <int PW, int LIB, int LVL, int M>
+template <int PW, int HALO, int LIB, int LVL, int M>
 __device__ __forceinline__ void build_tables(uint32_t *tb, int tid)
 {
-    constexpr int CW = Geo<PW>::CW;
+    constexpr int CW = Geo<PW, HALO>::CW;
     constexpr int ITERS = (CW + FT_THREADS - 1) / FT_THREADS;
     constexpr int K0 = level_first(LIB, LVL);
     using Ms = std::make_integer_sequence<int, M>;
@@ -393,7 +395,7 @@ __device__ __forceinline__ void build_tables(uint32_t *tb, int tid)
     __syncthreads();
 }
 
-template <int PW, int LIB, int LVL>
+template <int PW, int HALO, int LIB, int LVL>
 __device__ __forceinline__ void build_level(uint32_t *tb, int n_tables, int tid)
 {
     if constexpr (LVL >= 1 && level_count(LIB, LVL) > 0)
@@ -403,25 +405,25 @@ __device__ __forceinline__ void build_level(uint32_t *tb, int n_tables, int tid)
         for_each_index(std::make_integer_sequence<int, N>{}, [&](auto mc) {
             constexpr int mm = decltype(mc)::value + 1;
             if (m == mm)
-                build_tables<PW, LIB, LVL, mm>(tb, tid);
+                build_tables<PW, HALO, LIB, LVL, mm>(tb, tid);
         });
     }
 }
 
-template <int PW, int LIB, int... LVLs>
+template <int PW, int HALO, int LIB, int... LVLs>
 __device__ __forceinline__ void build_all_levels(uint32_t *tb, int n_tables, int tid, std::integer_sequence<int, LVLs...>)
 {
-    (build_level<PW, LIB, LVLs>(tb, n_tables, tid), ...);
+    (build_level<PW, HALO, LIB, LVLs>(tb, n_tables, tid), ...);
 }
 
-template <int PW, int LIB>
+template <int PW, int HALO, int LIB>
 __global__ void __launch_bounds__(FT_THREADS, CTAS_PER_SM) se2_fast_kernel(const __grid_constant__ FastArgs a)
 {
     extern __shared__ __align__(16) uint32_t sm[];
     __shared__ uint8_t s_cls[MAX_T_PER_LAUNCH];
     __shared__ uint8_t s_lead[MAX_T_PER_LAUNCH];  // bins that evaluate on this tile
     __shared__ uint32_t s_next, s_nlead;
-    using G = Geo<PW>;
+    using G = Geo<PW, HALO>;
     uint32_t *tb = sm + G::GUARD;
     const int tid = threadIdx.x;
     const int warp = tid >> 5, lane = tid & 31;
@@ -497,7 +499,7 @@ __global__ void __launch_bounds__(FT_THREADS, CTAS_PER_SM) se2_fast_kernel(const
     }
 
     // brick tables, level by level (tables of one level depend only on earlier levels)
-    build_all_levels<PW, LIB>(tb, a.n_tables, tid, std::make_integer_sequence<int, MAX_LEVEL + 1>{});
+    build_all_levels<PW, HALO, LIB>(tb, a.n_tables, tid, std::make_integer_sequence<int, MAX_LEVEL + 1>{});
     __syncthreads();  // also orders s_lead / s_nlead when no table beyond the costmap is built
 
     // output phase: warps fetch (evaluating bin, 16 rows) units until none are left
@@ -505,24 +507,27 @@ __global__ void __launch_bounds__(FT_THREADS, CTAS_PER_SM) se2_fast_kernel(const
 }
 
 
-// one instantiation per (pitch, library)
+// one instantiation per (pitch, halo, library)
 template <class F>
-auto dispatch_fast(int pw, int lib, F f)
+auto dispatch_fast(int pw, int halo, int lib, F f)
 {
-#define PP_CASE(P, L) \
-    if (pw == P && lib == L) return f(se2_fast_kernel<P, L>);
-    PP_CASE(22, 0) PP_CASE(22, 1) PP_CASE(22, 2) PP_CASE(22, 3)
-    PP_CASE(26, 0) PP_CASE(26, 1) PP_CASE(26, 2)
+#define PP_CASE(P, HL, L) \
+    if (pw == P && halo == HL && lib == L) return f(se2_fast_kernel<P, HL, L>);
+#define PP_LIBS(P, HL) PP_CASE(P, HL, 0) PP_CASE(P, HL, 1) PP_CASE(P, HL, 2) PP_CASE(P, HL, 3)
+    PP_LIBS(22, 7) PP_LIBS(22, 8) PP_LIBS(22, 9) PP_LIBS(22, 10)
+    PP_LIBS(26, 11) PP_LIBS(26, 12) PP_LIBS(26, 13) PP_LIBS(26, 14)
+    PP_CASE(26, 15, 0) PP_CASE(26, 15, 1) PP_CASE(26, 15, 2)
+#undef PP_LIBS
 #undef PP_CASE
-    return f(se2_fast_kernel<26, 3>);
+    return f(se2_fast_kernel<26, 15, 3>);
 }
-cudaError_t set_fast_smem(int pw, int lib, size_t bytes)
+cudaError_t set_fast_smem(int pw, int halo, int lib, size_t bytes)
 {
-    return dispatch_fast(pw, lib, [&](auto kernel) { return cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(bytes)); });
+    return dispatch_fast(pw, halo, lib, [&](auto kernel) { return cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(bytes)); });
 }
-void launch_fast(int pw, int lib, dim3 grid, size_t smem, cudaStream_t stream, const FastArgs &args)
+void launch_fast(int pw, int halo, int lib, dim3 grid, size_t smem, cudaStream_t stream, const FastArgs &args)
 {
-    dispatch_fast(pw, lib, [&](auto kernel) { kernel<<<grid, FT_THREADS, smem, stream>>>(args); return cudaSuccess; });
+    dispatch_fast(pw, halo, lib, [&](auto kernel) { kernel<<<grid, FT_THREADS, smem, stream>>>(args); return cudaSuccess; });
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -916,9 +921,9 @@ pp_status build_plan(pp_handle h, int effort)
     // 2. geometry
     int pw = (4 + FT_W + 2 * R + 3) / 4;  // one margin word on the left
     pw = pw <= 22 ? 22 : 26;  // the two instantiated pitches (both 2 mod 4: conflict-free half-warps)
-    // the staged halo depends on the pitch only (Geo<PW>), so that table addresses are immediates
-    const int halo = pw == 22 ? Geo<22>::HALO : Geo<26>::HALO;
-    const size_t guard_bytes = static_cast<size_t>(2) * (pw == 22 ? Geo<22>::GUARD : Geo<26>::GUARD) * 4;
+    // the staged halo is a template parameter of the kernel (table addresses are immediates)
+    const int halo = halo_for(pw, R);
+    const size_t guard_bytes = static_cast<size_t>(2) * (4 * pw + 4) * 4;  // Geo::GUARD on both sides of the tables
     pl->R = halo;
     pl->rows = FT_H + 2 * halo;
     pl->PW = pw;
@@ -1047,7 +1052,7 @@ pp_status build_plan(pp_handle h, int effort)
         PP_CUDA(h, cudaMemcpyAsync(pl->d_work, pl->h_work.data(), pl->h_work.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, h->stream));
     }
     PP_CUDA(h, cudaStreamSynchronize(h->stream));
-    PP_CUDA(h, set_fast_smem(pl->PW, pl->lib_id, pl->smem_bytes));
+    PP_CUDA(h, set_fast_smem(pl->PW, pl->R, pl->lib_id, pl->smem_bytes));
     pl->usable = true;
     return PP_OK;
 }
@@ -1208,7 +1213,7 @@ pp_status pp_se2_launch_fast(pp_handle h, uint32_t x0, uint32_t y0, uint32_t x1,
                 }
             }
         }
-        launch_fast(pl->PW, pl->lib_id, grid, pl->smem_bytes, h->stream, args);
+        launch_fast(pl->PW, pl->R, pl->lib_id, grid, pl->smem_bytes, h->stream, args);
         h->launches++;
         PP_CUDA(h, cudaGetLastError());
         if (forked)
