@@ -223,3 +223,17 @@ def test_twin_bins_equal_their_own_evaluation(handle, port):
     assert np.array_equal(whole[36:], upper)
     want = port.se2_volume(cost, pts, 72, t0=30, t1=42)
     assert np.array_equal(whole[30:42], want)
+
+
+@pytest.mark.parametrize("boundary", [[0.5, 0.4], [0.6, 0.5], [0.64, 0.46], [0.8, 0.6], [0.9, 0.6], [1.0, 0.6], [1.1, 0.6],
+                                      [1.2, 0.7], [1.3, 0.7]])
+def test_every_halo_instantiation(handle, port, boundary):
+    """Footprint reaches 7 ... 15 cells: one per compiled (pitch, halo) variant of the tiled kernel."""
+    cost = make_costmap(320, 208, seed=int(boundary[0] * 100))
+    pts = port.footprint_points(RES, boundary, True)
+    handle.costmap_upload(cost)
+    handle.footprint_from_boundary(RES, boundary, True)
+    handle.se2_volume_build(72)
+    stats = handle.se2_volume_stats()
+    assert stats["fast_tiles"] > 0  # the tiled kernel did take part
+    assert np.array_equal(handle.se2_volume_download(), port.se2_volume(cost, pts, 72))
