@@ -110,7 +110,7 @@ struct FastArgs
     const uint8_t *xclass;  // [n_theta][tiles_x]: 0/1 = column range class, 255 = not uniform
     const uint8_t *yclass;  // [n_theta][tiles_y]
     uint32_t W, H, tiles_x, tiles_y, tile_x0, tile_y0;
-    int32_t R, PW, rows, copy_words, n_tables;
+    int32_t n_tables;  // pitch, halo and library are template parameters of the kernel
     uint32_t t_first, n_t;
     uint16_t list_off[MAX_T_PER_LAUNCH][4];
     uint16_t list_len[MAX_T_PER_LAUNCH][4];
@@ -1099,10 +1099,6 @@ pp_status pp_se2_launch_fast(pp_handle h, uint32_t x0, uint32_t y0, uint32_t x1,
     args.tiles_y = pl->tiles_y;
     args.tile_x0 = tx_lo;
     args.tile_y0 = ty_lo;
-    args.R = pl->R;
-    args.PW = pl->PW;
-    args.rows = pl->rows;
-    args.copy_words = pl->copy_words;
     args.n_tables = pl->n_tables;
     const dim3 grid(tx_hi - tx_lo, ty_hi - ty_lo, 1);
     const uint64_t n_tiles = static_cast<uint64_t>(grid.x) * grid.y;
