@@ -213,6 +213,19 @@ private:
         tau = (t2 < 0) ? rs_mod(t1 + kPi) : rs_mod(t1);
         omega = rs_mod(tau - u + v - phi);
     }
+    // Sign pre-tests. A formula is rejected when its first arc t is negative beyond the tolerance; whether
+    // it is can often be seen from the sign of a sine that costs two multiplications instead of two
+    // atan2. Only clear cases are decided here (margins far above the rounding error of the test itself
+    // and far above kRsZero); everything else takes the full evaluation, so the outcome is unchanged.
+    static bool clearly_negative_atan2(double y, double x)  // atan2(y, x) < -kRsZero for certain
+    {
+        return y < 0.0 && !(x > 0.0 && -y <= 1e-14 * x);
+    }
+    static bool clearly_negative_sine(double a, double b)  // a + b < 0 for certain, a and b products of the inputs
+    {
+        return a + b < -1e-12 * (fabs(a) + fabs(b));
+    }
+
     // Every formula receives sin(phi) and cos(phi) (computed once per query; sin is odd and cos even
     // bit for bit in the host libm, checked in tests/test_curves.py) and the incumbent bound Lmin: a
     // candidate replaces the incumbent only if |t| + w|u| + |v| < Lmin, so once a partial sum reaches
@@ -221,7 +234,7 @@ private:
     {
         const double xi = x - sp, eta = y - 1.0 + cp;
         u = sqrt(xi * xi + eta * eta);
-        if (!(u < Lmin))
+        if (!(u < Lmin) || clearly_negative_atan2(eta, xi))
             return false;
         t = atan2(eta, xi);
         if (t >= -kRsZero)
@@ -240,7 +253,7 @@ private:
         if (u1 >= 4.0)
         {
             u = sqrt(u1 - 4.0);
-            if (!(u < Lmin))
+            if (!(u < Lmin) || clearly_negative_sine(eta * u, xi * 2.0))  // sin(t1 + theta) up to a positive factor
                 return false;
             const double t1 = atan2(eta, xi);
             const double theta = atan2(2.0, u);
@@ -300,7 +313,7 @@ private:
         {
             const double r = sqrt(rho * rho - 4.0);
             u = 2.0 - r;
-            if (!(u <= kRsZero) || !(fabs(u) < Lmin))
+            if (!(u <= kRsZero) || !(fabs(u) < Lmin) || clearly_negative_sine(eta * -2.0, xi * r))
                 return false;
             const double theta = atan2(eta, xi);
             t = rs_mod(theta + atan2(r, -2.0));
@@ -316,7 +329,7 @@ private:
         if (rho >= 2.0)
         {
             u = 2.0 - rho;
-            if (!(u <= kRsZero) || !(fabs(u) < Lmin))
+            if (!(u <= kRsZero) || !(fabs(u) < Lmin) || clearly_negative_atan2(xi, -eta))
                 return false;
             t = atan2(xi, -eta);
             v = rs_mod(t + 0.5 * kPi - phi);
@@ -335,7 +348,10 @@ private:
             {
                 if (!(fabs(u) < Lmin))
                     return false;
-                t = rs_mod(atan2((4.0 - u) * xi - 2.0 * eta, -2.0 * xi + (u - 4.0) * eta));
+                const double ty = (4.0 - u) * xi - 2.0 * eta, tx = -2.0 * xi + (u - 4.0) * eta;
+                if (clearly_negative_atan2(ty, tx))
+                    return false;
+                t = rs_mod(atan2(ty, tx));
                 v = rs_mod(t - phi);
                 return t >= -kRsZero && v >= -kRsZero;
             }
