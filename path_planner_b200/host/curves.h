@@ -27,6 +27,28 @@ public:
 
     double distance(const SE2 &a, const SE2 &b) const { return rho_ * solve(a, b).total; }
 
+    // The four trigonometric values a Reeds-Shepp query starts with, for callers that ask about the same
+    // pair of headings again and again (a search has one goal heading and a few dozen node headings):
+    // values of exactly the calls distance() makes, so the result is the same bits.
+    struct HeadingTrig
+    {
+        double cos_a, sin_a;      // of a.yaw
+        double sin_phi, cos_phi;  // of b.yaw - a.yaw
+    };
+    static HeadingTrig headingTrig(double a_yaw, double b_yaw)
+    {
+        const double phi = b_yaw - a_yaw;
+        return {cos(a_yaw), sin(a_yaw), sin(phi), cos(phi)};
+    }
+    double distance(const SE2 &a, const SE2 &b, const HeadingTrig &h) const
+    {
+        if (kind_ == DUBINS)
+            return distance(a, b);
+        const double dx = b.x - a.x, dy = b.y - a.y;
+        return rho_ * reeds_shepp((h.cos_a * dx + h.sin_a * dy) / rho_, (-h.sin_a * dx + h.cos_a * dy) / rho_, b.yaw - a.yaw,
+                                  h.sin_phi, h.cos_phi).total;
+    }
+
     SE2 interpolate(const SE2 &from, const SE2 &to, double t) const
     {
         if (t >= 1.0)
@@ -401,12 +423,12 @@ private:
             }
         }
     }
-    static Word reeds_shepp(double x, double y, double phi)
+    static Word reeds_shepp(double x, double y, double phi) { return reeds_shepp(x, y, phi, sin(phi), cos(phi)); }
+    static Word reeds_shepp(double x, double y, double phi, double sphi, double cphi)
     {
         Word best;
         best.seg[0] = 'L'; best.seg[1] = 'R'; best.seg[2] = 'L';
         double Lmin = best.total;
-        const double sphi = sin(phi), cphi = cos(phi);
         four_ways(f81, x, y, phi, sphi, cphi, "LSL--", "RSR--", 0, 1.0, Lmin, best);
         four_ways(f82, x, y, phi, sphi, cphi, "LSR--", "RSL--", 0, 1.0, Lmin, best);
         Lmin = best.total;

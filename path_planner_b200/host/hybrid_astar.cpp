@@ -3,6 +3,7 @@
 
 #include <algorithm>
 #include <climits>
+#include <cstring>
 #include <cmath>
 #include <limits>
 
@@ -161,8 +162,19 @@ bool HybridAStar::footprint(const Tables &tb, float x, float y, float theta_rad,
 float HybridAStar::heuristic(const Tables &tb, const Pose &at) const
 {
     const Pose &goal = _goal->at;
-    const SE2 from{static_cast<double>(at.x), static_cast<double>(at.y), wrap_angle_d(static_cast<double>(at.theta * _bin))};
-    const float motion_h = static_cast<float>(_curves->distance(from, _goal_se2));
+    // every node heading of a search is start fraction + whole bins: a few dozen distinct floats, so the
+    // wrapped yaw and the trigonometry of (node heading, goal heading) are remembered per heading value
+    uint32_t bits;
+    std::memcpy(&bits, &at.theta, sizeof bits);
+    HeadingEntry &e = _heading_cache[static_cast<unsigned int>(at.theta) % _heading_cache.size()];
+    if (e.bits != bits)
+    {
+        e.bits = bits;
+        e.yaw = wrap_angle_d(static_cast<double>(at.theta * _bin));
+        e.trig = CurveSpace::headingTrig(e.yaw, _goal_se2.yaw);
+    }
+    const SE2 from{static_cast<double>(at.x), static_cast<double>(at.y), e.yaw};
+    const float motion_h = static_cast<float>(_curves->distance(from, _goal_se2, e.trig));
 
     const unsigned int sx = static_cast<unsigned int>(at.x), sy = static_cast<unsigned int>(at.y);
     const float field = tb.field[static_cast<size_t>(sy) * _W + sx];
@@ -315,6 +327,7 @@ bool HybridAStar::plan(const Tables &tb, const Pose &start_world, const Pose &go
     };
     _start = place(start_world);
     _goal = place(goal_world);
+    _heading_cache.assign(_n_theta + 1, HeadingEntry());  // keyed to this goal's heading
     _goal_se2 = {static_cast<double>(_goal->at.x), static_cast<double>(_goal->at.y),
                  wrap_angle_d(static_cast<double>(_goal->at.theta * _bin))};  // the same for every heuristic call
 

@@ -107,5 +107,12 @@ private:
     void growGraph();
     Node *_start = nullptr, *_goal = nullptr;
     SE2 _goal_se2{0.0, 0.0, 0.0};
+    struct HeadingEntry
+    {
+        uint32_t bits = 0xFFFFFFFFu;  // bit pattern of the heading coordinate this entry was computed for (NaN: none yet)
+        double yaw = 0.0;
+        CurveSpace::HeadingTrig trig{1.0, 0.0, 0.0, 1.0};
+    };
+    mutable std::vector<HeadingEntry> _heading_cache;
 };
 }  // namespace ppb
