@@ -6,6 +6,8 @@
 //   idx.setPoints(points_xy, n);            // or idx.extractFromCostmap(...) (teb_follower.cpp:140-169)
 //   idx.query(poses_xy, q, radius_arg, K);   // one launch for all poses of a buildGraph round
 //   idx.count(i), idx.index(i, j), idx.dist2(i, j)  -> what results[j].first / .second were
+//   idx.setRobotModel(...); idx.evaluateEdges(poses_xyt, params);   // per optimiser iteration (N3)
+//   idx.edgeError(i, j), idx.edgeJacobian(i, j)
 //
 // radius_arg is passed through exactly as the reference passes it to nanoflann (compared against
 // squared distances, strict <).
@@ -58,6 +60,27 @@ public:
         _resident = s == PP_OK;
         return s == PP_OK;
     }
+    // N3: what EdgeObstacle::computeError (g2o_edges/edge_obstacle.hpp:19-26) and g2o's numeric
+    // linearizeOplus give for every edge (pose i, kept obstacle j) of the last query(), in one launch.
+    // robot_numbers as RobotModelHelper::createRobotModel takes them (robot_model.cpp:68-95).
+    bool setRobotModel(const double *robot_numbers, uint32_t n)
+    {
+        return pp_robot_model_set(_h, robot_numbers, n, &_inscribed, &_circum) == PP_OK;
+    }
+    double inscribedRadius() const { return _inscribed; }
+    double circumRadius() const { return _circum; }
+    bool evaluateEdges(const double *poses_xyt, const pp_obstacle_edge_params &params, bool jacobians = true)
+    {
+        _err.assign(static_cast<size_t>(_q) * _k * 2, 0.0);
+        _jac.assign(jacobians ? static_cast<size_t>(_q) * _k * 6 : 0, 0.0);
+        if (_n == 0 || _q == 0)
+            return true;
+        return pp_obstacle_edges(_h, poses_xyt, _q, _k, &params, _err.data(), jacobians ? _jac.data() : nullptr) == PP_OK;
+    }
+    // _error[0..1] of the edge and its 2x3 row-major Jacobian with respect to (x, y, theta)
+    const double *edgeError(uint32_t pose, uint32_t j) const { return &_err[(static_cast<size_t>(pose) * _k + j) * 2]; }
+    const double *edgeJacobian(uint32_t pose, uint32_t j) const { return &_jac[(static_cast<size_t>(pose) * _k + j) * 6]; }
+
     uint32_t size() const { return _n; }
     const std::vector<double> &points() const { return _points; }
     uint32_t count(uint32_t pose) const { return _cnt[pose]; }
@@ -70,5 +93,6 @@ private:
     uint32_t _n, _q, _k;
     bool _resident = false;
     std::vector<uint32_t> _idx, _cnt;
-    std::vector<double> _d2;
+    std::vector<double> _d2, _err, _jac;
+    double _inscribed = 0.0, _circum = 0.0;
 };
