@@ -68,12 +68,19 @@ extern "C" pp_status pp_plan(pp_handle h, const pp_plan_params *params, double r
     const size_t cells = static_cast<size_t>(h->W) * h->H;
     PP_CUDA(h, reserve_pinned(h->h_vol_mirror, h->vol_mirror_cap, cells * params->n_theta));
     PP_CUDA(h, reserve_pinned(h->h_field_mirror, h->field_mirror_cap, cells));
-    PP_CUDA(h, cudaMemcpyAsync(h->h_vol_mirror, h->d_vol, cells * params->n_theta, cudaMemcpyDeviceToHost, h->stream));
+    // the volume travels to the host on the side stream while the heuristic field is built on the main one
+    PP_CUDA(h, cudaEventRecord(h->ev_fork, h->stream));
+    PP_CUDA(h, cudaStreamWaitEvent(h->aux, h->ev_fork, 0));
+    PP_CUDA(h, cudaMemcpyAsync(h->h_vol_mirror, h->d_vol, cells * params->n_theta, cudaMemcpyDeviceToHost, h->aux));
     st = pp_heuristic_build(h, gx, gy, params->cost_penalty, nullptr);
     if (st != PP_OK)
+    {
+        cudaStreamSynchronize(h->aux);
         return st;
+    }
     PP_CUDA(h, cudaMemcpyAsync(h->h_field_mirror, h->d_field, cells * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
     PP_CUDA(h, cudaStreamSynchronize(h->stream));
+    PP_CUDA(h, cudaStreamSynchronize(h->aux));
     const auto mid = std::chrono::steady_clock::now();
 
     ppb::Tables tb;
