@@ -2,7 +2,9 @@
 #include "pp_internal.h"
 #include "../host/hybrid_astar.h"
 
+#include <algorithm>
 #include <chrono>
+#include <vector>
 
 namespace
 {
@@ -20,6 +22,32 @@ cudaError_t reserve_pinned(T *&ptr, size_t &cap, size_t need)
         cap = need;
     return e;
 }
+// on-demand mirror of the SE2 volume for the host search (see pp_plan)
+struct BandPager
+{
+    static constexpr unsigned int SHIFT = 6, ROWS = 1u << SHIFT;
+    pp_handle h;
+    uint32_t n_theta;
+    std::vector<uint8_t> ready;
+    cudaError_t error;
+
+    static void fetch(void *ctx, unsigned int band)
+    {
+        BandPager *p = static_cast<BandPager *>(ctx);
+        pp_handle h = p->h;
+        const size_t plane = static_cast<size_t>(h->W) * h->H;
+        const uint32_t y0 = band * ROWS, y1 = std::min<uint32_t>(h->H, y0 + ROWS);
+        const size_t offset = static_cast<size_t>(y0) * h->W, bytes = static_cast<size_t>(y1 - y0) * h->W;
+        // one strided copy: a "row" of it is this band inside one heading bin
+        cudaError_t e = cudaMemcpy2DAsync(h->h_vol_mirror + offset, plane, h->d_vol + offset, plane, bytes, p->n_theta,
+                                          cudaMemcpyDeviceToHost, h->aux);
+        if (e == cudaSuccess)
+            e = cudaStreamSynchronize(h->aux);
+        if (e != cudaSuccess && p->error == cudaSuccess)
+            p->error = e;
+        p->ready[band] = 1;  // also after an error: the search must not spin on it; pp_plan reports the error
+    }
+};
 }  // namespace
 
 extern "C" pp_status pp_plan(pp_handle h, const pp_plan_params *params, double resolution, double origin_x, double origin_y,
@@ -68,10 +96,18 @@ extern "C" pp_status pp_plan(pp_handle h, const pp_plan_params *params, double r
     const size_t cells = static_cast<size_t>(h->W) * h->H;
     PP_CUDA(h, reserve_pinned(h->h_vol_mirror, h->vol_mirror_cap, cells * params->n_theta));
     PP_CUDA(h, reserve_pinned(h->h_field_mirror, h->field_mirror_cap, cells));
-    // the volume travels to the host on the side stream while the heuristic field is built on the main one
+    // The volume travels to the host on the side stream while the heuristic field is built on the main
+    // one. A small volume goes as a whole; a large one is paged in during the search, by bands of 64 map
+    // rows (all heading bins of a band in one strided copy), because a search only touches the rows of
+    // its corridor and the host link, not the GPU, is what a 300 MB .. 1.2 GB mirror waits for.
     PP_CUDA(h, cudaEventRecord(h->ev_fork, h->stream));
     PP_CUDA(h, cudaStreamWaitEvent(h->aux, h->ev_fork, 0));
-    PP_CUDA(h, cudaMemcpyAsync(h->h_vol_mirror, h->d_vol, cells * params->n_theta, cudaMemcpyDeviceToHost, h->aux));
+    const bool paged = cells * params->n_theta > (static_cast<size_t>(64) << 20);
+    BandPager pager{h, params->n_theta, {}, cudaSuccess};
+    if (paged)
+        pager.ready.assign((h->H + BandPager::ROWS - 1) / BandPager::ROWS, 0);
+    else
+        PP_CUDA(h, cudaMemcpyAsync(h->h_vol_mirror, h->d_vol, cells * params->n_theta, cudaMemcpyDeviceToHost, h->aux));
     st = pp_heuristic_build(h, gx, gy, params->cost_penalty, nullptr);
     if (st != PP_OK)
     {
@@ -90,10 +126,19 @@ extern "C" pp_status pp_plan(pp_handle h, const pp_plan_params *params, double r
     tb.H = h->H;
     tb.n_theta = params->n_theta;
     tb.heading_fraction = frac;
+    if (paged)
+    {
+        tb.band_ready = pager.ready.data();
+        tb.band_shift = BandPager::SHIFT;
+        tb.fetch_band = &BandPager::fetch;
+        tb.ctx = &pager;
+    }
     std::vector<ppb::Pose> path;
     int iterations = 0;
     const bool found = search.plan(tb, start, goal, path, iterations);
     const auto toc = std::chrono::steady_clock::now();
+    PP_REQUIRE(h, pager.error == cudaSuccess, PP_ERR_CUDA, "pp_plan: paging the volume mirror failed: %s",
+               cudaGetErrorString(pager.error));
 
     *found_out = found ? 1 : 0;
     *iterations_out = iterations;

@@ -149,6 +149,12 @@ bool HybridAStar::footprint(const Tables &tb, float x, float y, float theta_rad,
         cost = 254.0f;
         return true;
     }
+    if (tb.band_ready)
+    {
+        const unsigned int band = static_cast<unsigned int>(fy) >> tb.band_shift;
+        if (!tb.band_ready[band])
+            tb.fetch_band(tb.ctx, band);
+    }
     long t = std::lround(theta_rad / _bin - tb.heading_fraction);
     t %= static_cast<long>(_n_theta);
     if (t < 0)

@@ -45,6 +45,13 @@ struct Tables
     const float *field = nullptr;     // [H][W] obstacle heuristic for the goal cell, 0 = unreachable
     unsigned int W = 0, H = 0, n_theta = 0;
     float heading_fraction = 0.0f;
+    // Optional paging of the volume mirror by bands of (1 << band_shift) map rows: where band_ready is
+    // set, a lookup in a band whose flag is 0 first calls fetch_band(ctx, band), which must bring the
+    // rows of that band (all heading bins) into `volume` and set the flag. A search touches a corridor.
+    uint8_t *band_ready = nullptr;
+    unsigned int band_shift = 0;
+    void (*fetch_band)(void *ctx, unsigned int band) = nullptr;
+    void *ctx = nullptr;
 };
 
 class HybridAStar
