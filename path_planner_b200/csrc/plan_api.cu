@@ -28,24 +28,54 @@ struct BandPager
     static constexpr unsigned int SHIFT = 6, ROWS = 1u << SHIFT;
     pp_handle h;
     uint32_t n_theta;
-    std::vector<uint8_t> ready;
+    std::vector<uint8_t> ready;       // what the search tests: 1 = the band is in the mirror
     cudaError_t error;
+    std::vector<uint8_t> issued;      // a copy of the band has been queued on the side stream
+    std::vector<cudaEvent_t> done;    // recorded behind each queued copy (created on first use)
+    int toward = 0;                   // +1 / -1: the goal lies in higher / lower rows than the start
 
-    static void fetch(void *ctx, unsigned int band)
+    void issue(unsigned int band)
     {
-        BandPager *p = static_cast<BandPager *>(ctx);
-        pp_handle h = p->h;
+        if (issued[band] || error != cudaSuccess)
+            return;
         const size_t plane = static_cast<size_t>(h->W) * h->H;
         const uint32_t y0 = band * ROWS, y1 = std::min<uint32_t>(h->H, y0 + ROWS);
         const size_t offset = static_cast<size_t>(y0) * h->W, bytes = static_cast<size_t>(y1 - y0) * h->W;
         // one strided copy: a "row" of it is this band inside one heading bin
-        cudaError_t e = cudaMemcpy2DAsync(h->h_vol_mirror + offset, plane, h->d_vol + offset, plane, bytes, p->n_theta,
+        cudaError_t e = cudaMemcpy2DAsync(h->h_vol_mirror + offset, plane, h->d_vol + offset, plane, bytes, n_theta,
                                           cudaMemcpyDeviceToHost, h->aux);
+        if (e == cudaSuccess && !done[band])
+            e = cudaEventCreateWithFlags(&done[band], cudaEventDisableTiming);
         if (e == cudaSuccess)
-            e = cudaStreamSynchronize(h->aux);
-        if (e != cudaSuccess && p->error == cudaSuccess)
-            p->error = e;
+            e = cudaEventRecord(done[band], h->aux);
+        if (e != cudaSuccess)
+            error = e;
+        issued[band] = 1;
+    }
+    // called by the search on its first lookup in a band: wait for that band only, and queue the next
+    // band towards the goal so that it travels while the search works on this one
+    static void fetch(void *ctx, unsigned int band)
+    {
+        BandPager *p = static_cast<BandPager *>(ctx);
+        p->issue(band);
+        const long next = static_cast<long>(band) + p->toward;
+        if (p->toward != 0 && next >= 0 && next < static_cast<long>(p->ready.size()))
+            p->issue(static_cast<unsigned int>(next));
+        if (p->error == cudaSuccess)
+        {
+            const cudaError_t e = cudaEventSynchronize(p->done[band]);
+            if (e != cudaSuccess)
+                p->error = e;
+        }
         p->ready[band] = 1;  // also after an error: the search must not spin on it; pp_plan reports the error
+    }
+    ~BandPager()
+    {
+        if (!done.empty())
+            cudaStreamSynchronize(h->aux);  // nothing may still be landing in the mirror when pp_plan returns
+        for (cudaEvent_t e : done)
+            if (e)
+                cudaEventDestroy(e);
     }
 };
 }  // namespace
@@ -103,9 +133,15 @@ extern "C" pp_status pp_plan(pp_handle h, const pp_plan_params *params, double r
     PP_CUDA(h, cudaEventRecord(h->ev_fork, h->stream));
     PP_CUDA(h, cudaStreamWaitEvent(h->aux, h->ev_fork, 0));
     const bool paged = cells * params->n_theta > (static_cast<size_t>(64) << 20);
-    BandPager pager{h, params->n_theta, {}, cudaSuccess};
+    BandPager pager{h, params->n_theta, {}, cudaSuccess, {}, {}, 0};
     if (paged)
-        pager.ready.assign((h->H + BandPager::ROWS - 1) / BandPager::ROWS, 0);
+    {
+        const size_t n_bands = (h->H + BandPager::ROWS - 1) / BandPager::ROWS;
+        pager.ready.assign(n_bands, 0);
+        pager.issued.assign(n_bands, 0);
+        pager.done.assign(n_bands, nullptr);
+        pager.toward = goal.y > start.y ? 1 : (goal.y < start.y ? -1 : 0);
+    }
     else
         PP_CUDA(h, cudaMemcpyAsync(h->h_vol_mirror, h->d_vol, cells * params->n_theta, cudaMemcpyDeviceToHost, h->aux));
     st = pp_heuristic_build(h, gx, gy, params->cost_penalty, nullptr);
@@ -136,6 +172,8 @@ extern "C" pp_status pp_plan(pp_handle h, const pp_plan_params *params, double r
     std::vector<ppb::Pose> path;
     int iterations = 0;
     const bool found = search.plan(tb, start, goal, path, iterations);
+    if (paged)
+        cudaStreamSynchronize(h->aux);  // a prefetched band may still be on its way: part of the plan's time
     const auto toc = std::chrono::steady_clock::now();
     PP_REQUIRE(h, pager.error == cudaSuccess, PP_ERR_CUDA, "pp_plan: paging the volume mirror failed: %s",
                cudaGetErrorString(pager.error));
