@@ -79,6 +79,11 @@ __global__ void __launch_bounds__(HT_THREADS) heur_round_kernel(float *__restric
                                                                 uint32_t tiles_x, uint32_t tiles_y, uint32_t *flags,
                                                                 uint32_t round, float delta)
 {
+    // Programmatic dependent launch: the CTAs of round r+1 may be scheduled while round r drains (most
+    // CTAs of a round find no work and leave at once); they park here until round r has completed and its
+    // writes are visible. Without the launch attribute both instructions do nothing.
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
     const uint32_t nT = tiles_x * tiles_y;
     uint32_t *cur = flags + (round & 1) * nT;
     uint32_t *nxt = flags + ((round + 1) & 1) * nT;
@@ -373,8 +378,18 @@ pp_status pp_heuristic_build(pp_handle h, uint32_t goal_x, uint32_t goal_y, floa
     {
         for (int k = 0; k < ROUNDS_PER_CHECK; ++k, ++round)
         {
-            heur_round_kernel<<<std::min<uint32_t>(nT, ROUND_GRID), HT_THREADS, 0, h->stream>>>(h->d_field, h->d_cost, h->d_travel, W, H, tiles_x, tiles_y,
-                                                                h->d_tile_flags, round, heur_delta());
+            cudaLaunchConfig_t cfg = {};
+            cfg.gridDim = dim3(std::min<uint32_t>(nT, ROUND_GRID));
+            cfg.blockDim = dim3(HT_THREADS);
+            cfg.stream = h->stream;
+            cudaLaunchAttribute attr[1];
+            attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+            attr[0].val.programmaticStreamSerializationAllowed = 1;  // see the top of heur_round_kernel
+            cfg.attrs = attr;
+            cfg.numAttrs = 1;
+            PP_CUDA(h, cudaLaunchKernelEx(&cfg, heur_round_kernel, h->d_field, static_cast<const uint8_t *>(h->d_cost),
+                                          static_cast<const float *>(h->d_travel), W, H, tiles_x, tiles_y, h->d_tile_flags, round,
+                                          heur_delta()));
             h->launches++;
         }
         PP_CUDA(h, cudaGetLastError());
