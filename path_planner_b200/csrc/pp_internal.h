@@ -44,7 +44,8 @@ struct pp_ctx
     bool vol_valid = false;
     float2 *d_trig = nullptr;  // (cos, sin) per heading bin, from the host libm
     size_t trig_cap = 0;
-    std::vector<float2> host_trig;
+    std::vector<float2> host_trig;  // what d_trig holds (kept alive: the upload reads it asynchronously)
+    float trig_ot = 0.0f;
     int vol_mode = 0;
     uint64_t stat_fast_tiles = 0, stat_generic_tiles = 0;
     double stat_samples_per_cell = 0.0;

@@ -6,20 +6,27 @@
 // max over uint8 is exact, idempotent and order-free, so S_t may be covered by translated copies
 // of small "bricks" B (S_t = U_i (B_i + o_i), overlaps allowed, no point outside S_t), and
 //   V[t][y][x] = max_i T_{B_i}[y + o_i.y][x + o_i.x],   T_B = dilation of the costmap tile by B.
-// The brick tables are heading-independent: a CTA stages one 64x16 tile (+ halo) of the costmap in
+// The brick tables are heading-independent: a CTA stages one 128x16 tile (+ halo) of the costmap in
 // shared memory, derives the brick tables from it by doubling (each table is the max of two
-// shifted earlier tables; recipes are compile-time data; as many tables as fit twice per SM, 8 for
-// the shipped footprint), and then serves ALL heading bins of the launch from them, turning the
-// P = 48 gathers per cell of the reference into ~19 aligned 32-bit shared-memory loads per four
-// cells. Every table is stored in four byte-shifted copies so that the word for any x offset is an
-// aligned LDS.32. Bins whose offset sets coincide (t and t + n_theta/2 for a centrally symmetric
-// footprint -- verified by the planner on the exact offsets, not assumed) are evaluated once per
-// tile and stored to all of them.
+// shifted earlier tables; the recipes are run-time data, so the library can be chosen per
+// footprint), and then serves ALL heading bins of the launch from them, turning the P = 48 gathers
+// per cell of the reference into ~15 aligned 32-bit shared-memory loads per four cells.
+//
+// Table layout ("column-transposed"): the four bytes of table word w of a row are the cells
+// x0+w, x0+w+32, x0+w+64, x0+w+96 (x0 = tile origin - halo). A thread that owns output cells
+// q, q+32, q+64, q+96 of a row therefore finds the sample at ANY x offset dx in the single aligned
+// word q+halo+dx: one copy per table instead of four byte-shifted ones (2.6x less shared memory
+// per table, no copy pass in the table build), a warp reads 32 consecutive words (no bank conflict
+// for any pitch), and a warp's 32 output words are exactly one 128-byte row of the volume. The price
+// is a 4x4 byte transpose across groups of four lanes (2 SHFL + 2 PRMT per word) before the store.
+// Bins whose offset sets coincide (t and t + n_theta/2 for a centrally symmetric footprint --
+// verified by the planner on the exact offsets, not assumed) are evaluated once per tile and
+// stored to all of them.
 //
 // sm_100a has no native per-byte max (__vmaxu4 is emulated with ~7 instructions). It does have the
 // 3-input VIMNMX3.U16x2. A u16 max is decided by the high byte, so on a raw word (b0,b1,b2,b3) it
 // yields the correct maxima of b1 and b3, and on the word shifted left by 8 bits those of b0 and
-// b2; the low bytes are don't-cares. Two accumulators per quad, two samples per instruction;
+// b2; the low bytes are don't-cares. Two accumulators per word, two samples per instruction;
 // the shift is an IMAD on the otherwise idle FMA pipe.
 //
 // Exactness: the host planner evaluates the reference expression for every column, row, point
@@ -35,6 +42,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <map>
+#include <set>
 #include <utility>
 #include <vector>
 
@@ -49,57 +57,22 @@ namespace
 #ifndef PP_FT_H
 #define PP_FT_H 16
 #endif
-constexpr int FT_W = 64, FT_H = PP_FT_H, FT_THREADS = PP_FT_THREADS;
+constexpr int FT_W = 128, FT_H = PP_FT_H, FT_THREADS = PP_FT_THREADS;
+constexpr int GEN_W = 64;  // width of a work-list tile of the exact generic kernel (se2_volume.cu); same height
 constexpr int CTAS_PER_SM = PP_CTAS_PER_SM;
-constexpr int MAX_TABLES = 12;
+constexpr int MAX_TABLES = 24;
 constexpr int MAX_T_PER_LAUNCH = 160;
 constexpr int MAX_LIST_WORDS = 6400;
 constexpr int MAX_R = 15;
+constexpr int MIN_HALO = 7;
 constexpr size_t SMEM_LIMIT = (227 * 1024 - 2048) / CTAS_PER_SM;  // per CTA; 1 KB per CTA is reserved by the system
 
-
-// ---------------------------------------------------------------------------------------------
-// Brick libraries. Table 0 is the costmap itself (the one-point brick); table k > 0 is
-// T_k = max(T_a, T_b shifted by (du, dv)). Tables are listed in dependency-level order. The
-// recipes are compile-time data so that the table build below unrolls completely.
-//   STAIRS  2-runs along x, y and the two diagonals, four 4-cell "stair" bricks (two 2-runs offset by
-//           (2,+-1) or (+-1,2)) that follow rasterised oblique edges, then runs of 4 along x and y
-//           and of 8 along x (the stairs come first so that a truncated library keeps them)
-//   RUNS3   runs of 2/3/6 along x and y, diagonals of 2/3/4
-//   BLOCKS  rectangles 2x2 .. 8x8 for solid footprints
-//   RUNS    runs of 2/4/8 along x and y, diagonals of 2/4
-// ---------------------------------------------------------------------------------------------
+// A brick library: table 0 is the costmap itself (the one-point brick); table k > 0 is
+// T_k = max(T_a, T_b shifted by (du, dv)), a and b earlier tables. Listed in dependency-level order.
 struct Recipe
 {
     int a, b, du, dv;
 };
-constexpr int N_LIBS = 4;
-__host__ __device__ constexpr int lib_size(int lib) { return lib == 3 ? 11 : 12; }
-__host__ __device__ constexpr Recipe lib_recipe(int lib, int k)
-{
-    constexpr Recipe T[N_LIBS][MAX_TABLES] = {
-        {{0, 0, 0, 0}, {0, 0, 1, 0}, {0, 0, 0, 1}, {0, 0, 1, 1}, {0, 0, 1, -1}, {1, 1, 2, 1}, {1, 1, 2, -1}, {2, 2, 1, 2}, {2, 2, -1, 2}, {1, 1, 2, 0}, {2, 2, 0, 2}, {9, 9, 4, 0}},
-        {{0, 0, 0, 0}, {0, 0, 1, 0}, {0, 0, 0, 1}, {0, 0, 1, 1}, {0, 0, 1, -1}, {1, 0, 2, 0}, {2, 0, 0, 2}, {3, 0, 2, 2}, {4, 0, 2, -2}, {3, 3, 2, 2}, {5, 5, 3, 0}, {6, 6, 0, 3}},
-        {{0, 0, 0, 0}, {0, 0, 1, 0}, {0, 0, 0, 1}, {1, 1, 0, 1}, {1, 1, 2, 0}, {2, 2, 0, 2}, {3, 3, 2, 0}, {4, 4, 4, 0}, {5, 5, 0, 4}, {6, 6, 0, 2}, {9, 9, 4, 0}, {10, 10, 0, 4}},
-        {{0, 0, 0, 0}, {0, 0, 1, 0}, {0, 0, 0, 1}, {0, 0, 1, 1}, {0, 0, 1, -1}, {1, 1, 2, 0}, {2, 2, 0, 2}, {3, 3, 2, 2}, {4, 4, 2, -2}, {5, 5, 4, 0}, {6, 6, 0, 4}, {0, 0, 0, 0}}};
-    return T[lib][k];
-}
-__host__ __device__ constexpr int lib_level(int lib, int k)
-{
-    if (k == 0)
-        return 0;
-    const Recipe r = lib_recipe(lib, k);
-    const int la = lib_level(lib, r.a), lb = lib_level(lib, r.b);
-    return 1 + (la > lb ? la : lb);
-}
-constexpr int MAX_LEVEL = 6;
-__host__ __device__ constexpr bool level_in_use(int lib, int lvl)
-{
-    for (int k = 0; k < lib_size(lib); ++k)
-        if (lib_level(lib, k) == lvl)
-            return true;
-    return false;
-}
 
 struct FastArgs
 {
@@ -110,7 +83,12 @@ struct FastArgs
     const uint8_t *xclass;  // [n_theta][tiles_x]: 0/1 = column range class, 255 = not uniform
     const uint8_t *yclass;  // [n_theta][tiles_y]
     uint32_t W, H, tiles_x, tiles_y, tile_x0, tile_y0;
-    int32_t n_tables;  // pitch, halo and library are template parameters of the kernel
+    int32_t n_tables;  // the halo (and with it the row pitch) is a template parameter of the kernel
+    // table k >= 1: word i = bytemax(T[rec_a[k] + i], T_b[rec_d[k] + i]) with T_b = T + rec_b[k]; rec_d is the
+    // shift dv * pitch + du inside table b (reads that leave table b give 0: they only feed entries whose
+    // brick leaves the staged region, which no sample list references)
+    int32_t rec_a[MAX_TABLES], rec_b[MAX_TABLES], rec_d[MAX_TABLES];
+    uint32_t rec_sync;  // bit k: table k starts a new dependency level (block barrier before it)
     uint32_t t_first, n_t;
     uint16_t list_off[MAX_T_PER_LAUNCH][4];
     uint16_t list_len[MAX_T_PER_LAUNCH][4];
@@ -121,6 +99,7 @@ struct FastArgs
     alignas(16) uint32_t lists[MAX_LIST_WORDS];  // byte offsets into shared memory, relative to the thread's base
 };
 static_assert(MAX_T_PER_LAUNCH <= 255, "chain links keep the bin in 8 bits");
+static_assert(MAX_TABLES <= 32, "rec_sync is a 32-bit mask");
 static_assert(sizeof(FastArgs) < 32764, "kernel parameter block too large");
 
 constexpr uint32_t NO_LINK = 0xFFFFu;
@@ -132,12 +111,9 @@ __device__ __forceinline__ uint32_t bytemax4(uint32_t a, uint32_t b)
     return __byte_perm(even, odd, 0x7351);
 }
 
-constexpr int QPT = 8;                                     // quads (4 cells along x) per thread and bin
-constexpr int UNITS_PER_BIN = FT_W / 4 * FT_H / QPT / 32;  // a work unit is 16 rows of one bin of a tile: one warp, QPT quads per thread
-static_assert(UNITS_PER_BIN * 16 == FT_H, "tile height must be a multiple of 16");
-
-// row of quad j of a thread, relative to the thread's first row
-__host__ __device__ constexpr int quad_row(int j) { return j; }
+constexpr int QPT = 8;                       // rows per thread and work unit
+constexpr int UNITS_PER_BIN = FT_H / QPT;    // a work unit is 8 rows x 128 columns of one bin of a tile: one warp, lane = word column
+static_assert(UNITS_PER_BIN * QPT == FT_H, "tile height must be a multiple of 8");
 
 template <int PW>
 __device__ __forceinline__ void load_pair(const uint8_t *smb, uint32_t d1, uint32_t d2, uint32_t (&u)[QPT], uint32_t (&v)[QPT])
@@ -148,8 +124,8 @@ __device__ __forceinline__ void load_pair(const uint8_t *smb, uint32_t d1, uint3
 #pragma unroll
     for (int j = 0; j < QPT; ++j)
     {
-        u[j] = p1[quad_row(j) * PW];
-        v[j] = p2[quad_row(j) * PW];
+        u[j] = p1[j * PW];
+        v[j] = p2[j * PW];
     }
 }
 
@@ -163,30 +139,33 @@ __device__ __forceinline__ void accumulate(uint32_t (&odd)[QPT], uint32_t (&even
     }
 }
 
-// Output phase. A work unit is 16 rows of one evaluating bin: one warp computes 16 quad columns x
-// 16 rows, 8 quads per thread. Thread -> quad column (lane & 15) and rows 8*(lane >> 4) + j:
-// half-warps sit 8 rows apart, which is bank-conflict free for PW = 2 (mod 4). Warps fetch units
-// from a shared counter, so bins with long and short sample lists balance out. The loads of the
-// next sample pair are issued before the max operations of the current one (software pipelining
-// by hand). The result is stored to every bin of the evaluating bin's chain that is in the matching
-// class on this tile.
+// Output phase. A work unit is 8 rows of one evaluating bin: one warp, lane q owns the cells q, q+32, q+64,
+// q+96 of each row. Warps fetch units from a shared counter, so bins with long and short sample lists
+// balance out. The loads of the next sample pair are issued before the max operations of the current one
+// (software pipelining by hand). The result is transposed across groups of four lanes, so that lane 4g+i
+// holds the four consecutive cells 4g+32i .. 4g+32i+3 and a warp's store is one whole 128-byte row, and is
+// stored to every bin of the evaluating bin's chain that is in the matching class on this tile.
 template <int PW>
 __device__ __forceinline__ void run_units(const FastArgs &a, const uint32_t *sm, const uint8_t *s_cls, const uint8_t *s_lead,
                                           uint32_t n_lead, uint32_t *s_next, int lane, int tx0, int ty0)
 {
-    const int q = lane & 15;
     const int W = static_cast<int>(a.W), H = static_cast<int>(a.H);
-    const int gx = tx0 + 4 * q;
+    // after the transpose this lane holds word (lane >> 2) + 8 * (lane & 3) of the 32-word row
+    const int out_word = (lane >> 2) + 8 * (lane & 3);
+    const int gx = tx0 + 4 * out_word;
     const bool in_x = gx < W;
     const size_t plane = static_cast<size_t>(a.W) * a.H;
     const uint32_t n_units = UNITS_PER_BIN * n_lead;
-    // byte offsets of the thread's QPT rows inside a bin's plane (< 2^30): the same for every unit half
-    const uint32_t cell0 = static_cast<uint32_t>(ty0 + 8 * (lane >> 4)) * a.W + static_cast<uint32_t>(gx);
+    const uint32_t cell0 = static_cast<uint32_t>(ty0) * a.W + static_cast<uint32_t>(gx);  // < 2^30
     uint32_t row_off[QPT];
 #pragma unroll
     for (int j = 0; j < QPT; ++j)
-        row_off[j] = cell0 + static_cast<uint32_t>(quad_row(j)) * a.W;
+        row_off[j] = cell0 + static_cast<uint32_t>(j) * a.W;
     const bool tile_inside = tx0 + FT_W <= W && ty0 + FT_H <= H;
+    // lane roles of the two transpose steps
+    const bool odd_lane = lane & 1, upper_lane = lane & 2;
+    const uint32_t sel1 = odd_lane ? 0x3715u : 0x7351u;
+    const uint32_t sel2 = upper_lane ? 0x3276u : 0x5410u;
     while (true)
     {
         uint32_t unit = 0;
@@ -198,13 +177,13 @@ __device__ __forceinline__ void run_units(const FastArgs &a, const uint32_t *sm,
         // s_lead lists the bins that evaluate on this tile (see the kernel prologue)
         const uint32_t t = s_lead[unit / UNITS_PER_BIN];
         const uint32_t cls = s_cls[t];
-        const int row0 = 16 * static_cast<int>(unit % UNITS_PER_BIN) + 8 * (lane >> 4);
-        const uint8_t *smb = reinterpret_cast<const uint8_t *>(sm + row0 * PW + q);
+        const int row0 = QPT * static_cast<int>(unit % UNITS_PER_BIN);
+        const uint8_t *smb = reinterpret_cast<const uint8_t *>(sm + row0 * PW + lane);
         const int gy = ty0 + row0;
-        const uint32_t half_off = 16u * (unit % UNITS_PER_BIN) * a.W;
-        uint8_t *out = a.vol + plane * (a.t_first + t) + half_off;  // warp-uniform
+        const uint32_t unit_off = static_cast<uint32_t>(row0) * a.W;
+        uint8_t *out = a.vol + plane * (a.t_first + t) + unit_off;  // warp-uniform
         const uint32_t *list = a.lists + a.list_off[t][cls];
-        const uint32_t n_samples = a.list_len[t][cls];  // >= 1; the stored list is padded to an even count
+        const uint32_t n_samples = a.list_len[t][cls];  // >= 1
         const uint32_t len = n_samples & ~1u;            // samples consumed in pairs
         uint32_t odd[QPT], even[QPT];
 #pragma unroll
@@ -239,12 +218,23 @@ __device__ __forceinline__ void run_units(const FastArgs &a, const uint32_t *sm,
             const uint32_t *p1 = reinterpret_cast<const uint32_t *>(smb + list[n_samples - 1]);
 #pragma unroll
             for (int j = 0; j < QPT; ++j)
-                ua[j] = p1[quad_row(j) * PW];
+                ua[j] = p1[j * PW];
             accumulate(odd, even, ua, ua);
         }
+        // 4x4 byte transpose across lanes 4g .. 4g+3. The valid bytes are the high bytes of the 16-bit
+        // halves: odd = (., b1, ., b3), even = (., b0, ., b2), b_i = the lane's cell q + 32 i.
+        // Step 1 (lane ^ 1): even lanes collect (b0, b2) of both lanes, odd lanes (b1, b3).
+        // Step 2 (lane ^ 2): lower lanes collect bytes 0..1 of both, upper lanes bytes 2..3.
 #pragma unroll
         for (int j = 0; j < QPT; ++j)
-            odd[j] = __byte_perm(even[j], odd[j], 0x7351);
+        {
+            const uint32_t keep = odd_lane ? odd[j] : even[j];
+            const uint32_t give = odd_lane ? even[j] : odd[j];
+            const uint32_t got = __shfl_xor_sync(0xffffffffu, give, 1);
+            const uint32_t p = __byte_perm(keep, got, sel1);
+            const uint32_t got2 = __shfl_xor_sync(0xffffffffu, p, 2);
+            odd[j] = __byte_perm(p, got2, sel2);
+        }
         uint32_t link = a.chain_next[t][cls];
         while (true)
         {
@@ -258,7 +248,7 @@ __device__ __forceinline__ void run_units(const FastArgs &a, const uint32_t *sm,
             {
 #pragma unroll
                 for (int j = 0; j < QPT; ++j)
-                    if (gy + quad_row(j) < H)
+                    if (gy + j < H)
                     {
                         uint8_t *dst = out + row_off[j];
                         *reinterpret_cast<uint32_t *>(dst) = odd[j];
@@ -277,159 +267,36 @@ __device__ __forceinline__ void run_units(const FastArgs &a, const uint32_t *sm,
             }
             if (t2 == NO_LINK)
                 break;
-            out = a.vol + plane * (a.t_first + t2) + half_off;
+            out = a.vol + plane * (a.t_first + t2) + unit_off;
         }
     }
 }
 
-// Shared-memory geometry, compile-time (row pitch and halo are template parameters) so that every table
-// address is an immediate: PW = 22 words holds a halo of up to 10 cells, PW = 26 up to 15. The tables sit between two guard
-// regions, so a recipe may read a few rows before the first / after the last table without a bounds
-// test: such words only feed entries whose brick leaves the staged region, and those are never
-// sampled (a sample's brick lies inside the offset set, which lies inside the halo).
-template <int PW, int HALO_>
+// Shared-memory geometry, compile-time (the halo is a template parameter) so that the row offsets of the
+// output loop are immediates.
+template <int HALO_>
 struct Geo
 {
     static constexpr int HALO = HALO_;
+    static constexpr int PW = 32 + 2 * HALO;  // words per table row
     static constexpr int ROWS = FT_H + 2 * HALO;
-    static constexpr int CW = ROWS * PW;     // words per table copy
-    static constexpr int GUARD = 4 * PW + 4;  // words; recipes reach at most 4 rows + 1 word away
-    static_assert(4 + FT_W + 2 * HALO <= 4 * PW, "row pitch too small for the halo");
+    static constexpr int CW = ROWS * PW;      // words per table
 };
-// halos with an instantiation: 7..10 cells at 22 words per row, 11..15 at 26
-constexpr int halo_for(int pw, int reach) { return pw == 22 ? (reach < 7 ? 7 : reach) : (reach < 11 ? 11 : reach); }
+constexpr int halo_for(int reach) { return reach < MIN_HALO ? MIN_HALO : reach; }
 
-// Table build. Recipes and levels are compile-time constants (forced through template arguments):
-// the tables of one level are consecutive in the library, the first M of them are built by
-// straight-line code (one uniform switch on M per level), and every shared-memory address is
-// base + immediate.
-//   pass 1: copy 0 of T_k = max(T_a, T_b shifted by (du, dv))
-//   pass 2: copies 1..3 = bytes s..s+3 of the word pair (i, i+1) of copy 0
-// Each thread owns the words tid, tid + FT_THREADS, ... of a table copy.
-template <int LIB, int K>
-struct TableInfo
-{
-    static constexpr Recipe rc = lib_recipe(LIB, K < lib_size(LIB) ? K : 0);
-    static constexpr int level = K < lib_size(LIB) ? lib_level(LIB, K) : -1;
-};
-__host__ __device__ constexpr int level_first(int lib, int lvl)
-{
-    for (int k = 0; k < lib_size(lib); ++k)
-        if (lib_level(lib, k) == lvl)
-            return k;
-    return lib_size(lib);
-}
-__host__ __device__ constexpr int level_count(int lib, int lvl)
-{
-    int n = 0;
-    for (int k = 0; k < lib_size(lib); ++k)
-        n += lib_level(lib, k) == lvl;
-    return n;
-}
-__host__ __device__ constexpr bool levels_contiguous(int lib)
-{
-    for (int k = 1; k < lib_size(lib); ++k)
-        if (lib_level(lib, k) < lib_level(lib, k - 1))
-            return false;
-    return true;
-}
-static_assert(levels_contiguous(0) && levels_contiguous(1) && levels_contiguous(2) && levels_contiguous(3),
-              "libraries list their tables in level order");
-
-template <int... Ks, class F>
-__device__ __forceinline__ void for_each_index(std::integer_sequence<int, Ks...>, F &&f)
-{
-    (f(std::integral_constant<int, Ks>{}), ...);
-}
-
-// the first M tables of level LVL (M >= 1, LVL >= 1)
-template <int PW, int HALO, int LIB, int LVL, int M>
-__device__ __forceinline__ void build_tables(uint32_t *tb, int tid)
-{
-    constexpr int CW = Geo<PW, HALO>::CW;
-    constexpr int ITERS = (CW + FT_THREADS - 1) / FT_THREADS;
-    constexpr int K0 = level_first(LIB, LVL);
-    using Ms = std::make_integer_sequence<int, M>;
-#pragma unroll
-    for (int it = 0; it < ITERS; ++it)
-    {
-        const int i = tid + it * FT_THREADS;
-        if (it * FT_THREADS + FT_THREADS > CW && i >= CW)
-            break;
-        const uint32_t *src = tb + i;
-        uint32_t va[M], vb[M];
-        for_each_index(Ms{}, [&](auto mc) {
-            constexpr int m = decltype(mc)::value;
-            constexpr Recipe rc = TableInfo<LIB, K0 + m>::rc;
-            va[m] = src[rc.a * 4 * CW];
-            vb[m] = src[(rc.b * 4 + (rc.du & 3)) * CW + rc.dv * PW + (rc.du >> 2)];
-        });
-        for_each_index(Ms{}, [&](auto mc) {
-            constexpr int m = decltype(mc)::value;
-            tb[(K0 + m) * 4 * CW + i] = bytemax4(va[m], vb[m]);
-        });
-    }
-    __syncthreads();
-#pragma unroll
-    for (int it = 0; it < ITERS; ++it)
-    {
-        const int i = tid + it * FT_THREADS;
-        if (it * FT_THREADS + FT_THREADS > CW && i >= CW)
-            break;
-        uint32_t *T = tb + K0 * 4 * CW + i;
-        uint32_t v[M], nx[M];
-#pragma unroll
-        for (int m = 0; m < M; ++m)
-        {
-            v[m] = T[m * 4 * CW];
-            nx[m] = T[m * 4 * CW + 1];
-        }
-#pragma unroll
-        for (int m = 0; m < M; ++m)
-        {
-            T[(m * 4 + 1) * CW] = __funnelshift_r(v[m], nx[m], 8);
-            T[(m * 4 + 2) * CW] = __funnelshift_r(v[m], nx[m], 16);
-            T[(m * 4 + 3) * CW] = __funnelshift_r(v[m], nx[m], 24);
-        }
-    }
-    __syncthreads();
-}
-
-template <int PW, int HALO, int LIB, int LVL>
-__device__ __forceinline__ void build_level(uint32_t *tb, int n_tables, int tid)
-{
-    if constexpr (LVL >= 1 && level_count(LIB, LVL) > 0)
-    {
-        constexpr int K0 = level_first(LIB, LVL), N = level_count(LIB, LVL);
-        const int m = min(n_tables - K0, N);  // uniform
-        for_each_index(std::make_integer_sequence<int, N>{}, [&](auto mc) {
-            constexpr int mm = decltype(mc)::value + 1;
-            if (m == mm)
-                build_tables<PW, HALO, LIB, LVL, mm>(tb, tid);
-        });
-    }
-}
-
-template <int PW, int HALO, int LIB, int... LVLs>
-__device__ __forceinline__ void build_all_levels(uint32_t *tb, int n_tables, int tid, std::integer_sequence<int, LVLs...>)
-{
-    (build_level<PW, HALO, LIB, LVLs>(tb, n_tables, tid), ...);
-}
-
-template <int PW, int HALO, int LIB>
+template <int HALO>
 __global__ void __launch_bounds__(FT_THREADS, CTAS_PER_SM) se2_fast_kernel(const __grid_constant__ FastArgs a)
 {
-    extern __shared__ __align__(16) uint32_t sm[];
+    extern __shared__ __align__(16) uint32_t tb[];
     __shared__ uint8_t s_cls[MAX_T_PER_LAUNCH];
     __shared__ uint8_t s_lead[MAX_T_PER_LAUNCH];  // bins that evaluate on this tile
     __shared__ uint32_t s_next, s_nlead;
-    using G = Geo<PW, HALO>;
-    uint32_t *tb = sm + G::GUARD;
+    using G = Geo<HALO>;
     const int tid = threadIdx.x;
     const int warp = tid >> 5, lane = tid & 31;
     constexpr int NWARPS = FT_THREADS / 32;
     constexpr int ROW_ITERS = (G::ROWS + NWARPS - 1) / NWARPS;
-    constexpr int R = G::HALO, CW = G::CW;
+    constexpr int PW = G::PW, CW = G::CW;
     const uint32_t tile_x = a.tile_x0 + blockIdx.x, tile_y = a.tile_y0 + blockIdx.y;
     const int tx0 = static_cast<int>(tile_x) * FT_W, ty0 = static_cast<int>(tile_y) * FT_H;
     const int W = static_cast<int>(a.W), H = static_cast<int>(a.H);
@@ -441,25 +308,26 @@ __global__ void __launch_bounds__(FT_THREADS, CTAS_PER_SM) se2_fast_kernel(const
         my_cx = __ldg(a.xclass + static_cast<size_t>(a.t_first + tid) * a.tiles_x + tile_x);
         my_cy = __ldg(a.yclass + static_cast<size_t>(a.t_first + tid) * a.tiles_y + tile_y);
     }
-    // Costmap tile with halo, one warp per row and one lane per word; every global load of the
-    // tile is issued before the first use. Table word w of row r holds columns X0+4w .. X0+4w+3 with
-    // X0 = tx0 - R - 4: one margin word on the left, so that bricks reaching towards -x never index
-    // before the row. Map rows are 4-byte aligned (W % 4 == 0); a word that straddles two aligned
-    // words is funnelled from both; zeros outside the map.
-    const bool wlane = lane < PW;
-    uint32_t lo[ROW_ITERS], hi[ROW_ITERS];
-    const int ax = tx0 - R - 4 + 4 * lane;
-    const int ga = ax & ~3, sh = ax & 3;
-    const bool lo_ok = wlane && ga >= 0 && ga < W, hi_ok = wlane && sh != 0 && ga + 4 >= 0 && ga + 4 < W;
+    // Costmap tile with halo, one warp per row. Lane l fetches the four bytes of table word l (cells
+    // x0+l+32i: each of the four loads of a warp reads 32 consecutive bytes) and, for l < 2*HALO, the one
+    // byte that word 32+l has beyond word l shifted down by a byte. Every global load of the tile is issued
+    // before the first use; zeros outside the map (the identity of max: the reference ignores such samples).
+    const int x0 = tx0 - HALO;
+    uint32_t cell[ROW_ITERS][5];
 #pragma unroll
     for (int j = 0; j < ROW_ITERS; ++j)
     {
         const int r = warp + j * NWARPS;
-        const int gy = ty0 - R + r;
+        const int gy = ty0 - HALO + r;
         const bool row_ok = r < G::ROWS && gy >= 0 && gy < H;
         const uint8_t *rowp = a.cost + static_cast<size_t>(row_ok ? gy : 0) * a.W;
-        lo[j] = (row_ok && lo_ok) ? __ldg(reinterpret_cast<const uint32_t *>(rowp + ga)) : 0u;
-        hi[j] = (row_ok && hi_ok) ? __ldg(reinterpret_cast<const uint32_t *>(rowp + ga + 4)) : 0u;
+#pragma unroll
+        for (int i = 0; i < 5; ++i)
+        {
+            const int gxi = x0 + lane + 32 * i;
+            const bool ok = row_ok && gxi >= 0 && gxi < W && (i < 4 || lane < 2 * HALO);
+            cell[j][i] = ok ? static_cast<uint32_t>(__ldg(rowp + gxi)) : 0u;
+        }
     }
     static_assert(MAX_T_PER_LAUNCH <= FT_THREADS, "one bin class per thread");
     const uint32_t my_cls = (my_cx > 1 || my_cy > 1) ? 255u : my_cx * 2 + my_cy;
@@ -467,20 +335,16 @@ __global__ void __launch_bounds__(FT_THREADS, CTAS_PER_SM) se2_fast_kernel(const
         s_cls[tid] = static_cast<uint8_t>(my_cls);
     if (tid == 0)
         s_next = s_nlead = 0;
-    // table 0 (the costmap itself) in its four byte-shifted copies, straight from the registers
 #pragma unroll
     for (int j = 0; j < ROW_ITERS; ++j)
     {
         const int r = warp + j * NWARPS;
-        const uint32_t w0 = __funnelshift_r(lo[j], hi[j], 8 * sh);
-        const uint32_t w1 = __shfl_down_sync(0xffffffffu, w0, 1);  // the next word of the row
-        if (wlane && r < G::ROWS)
+        if (r < G::ROWS)
         {
-            uint32_t *T = tb + r * PW + lane;
-            T[0] = w0;
-            T[CW] = __funnelshift_r(w0, w1, 8);
-            T[2 * CW] = __funnelshift_r(w0, w1, 16);
-            T[3 * CW] = __funnelshift_r(w0, w1, 24);
+            const uint32_t w0 = cell[j][0] | cell[j][1] << 8 | cell[j][2] << 16 | cell[j][3] << 24;
+            tb[r * PW + lane] = w0;
+            if (lane < 2 * HALO)
+                tb[r * PW + 32 + lane] = w0 >> 8 | cell[j][4] << 24;
         }
     }
     const int any_fast = __syncthreads_or(my_cls != 255u);
@@ -498,48 +362,90 @@ __global__ void __launch_bounds__(FT_THREADS, CTAS_PER_SM) se2_fast_kernel(const
             s_lead[atomicAdd(&s_nlead, 1u)] = static_cast<uint8_t>(tid);
     }
 
-    // brick tables, level by level (tables of one level depend only on earlier levels)
-    build_all_levels<PW, HALO, LIB>(tb, a.n_tables, tid, std::make_integer_sequence<int, MAX_LEVEL + 1>{});
+    // brick tables: T_k = max(T_a, T_b shifted); tables of one dependency level need no barrier between them
+    constexpr int ITERS = (CW + FT_THREADS - 1) / FT_THREADS;
+    for (int k = 1; k < a.n_tables; ++k)
+    {
+        if (a.rec_sync >> k & 1u)
+            __syncthreads();
+        const uint32_t *pa = tb + a.rec_a[k], *pb = tb + a.rec_b[k];
+        const int d = a.rec_d[k];
+        uint32_t *pd = tb + k * CW;
+        uint32_t va[ITERS], vb[ITERS];
+#pragma unroll
+        for (int it = 0; it < ITERS; ++it)
+        {
+            const int i = tid + it * FT_THREADS;
+            va[it] = vb[it] = 0;
+            if (i < CW)
+            {
+                va[it] = pa[i];
+                if (static_cast<uint32_t>(i + d) < static_cast<uint32_t>(CW))
+                    vb[it] = pb[i + d];
+            }
+        }
+#pragma unroll
+        for (int it = 0; it < ITERS; ++it)
+        {
+            const int i = tid + it * FT_THREADS;
+            if (i < CW)
+                pd[i] = bytemax4(va[it], vb[it]);
+        }
+    }
     __syncthreads();  // also orders s_lead / s_nlead when no table beyond the costmap is built
 
-    // output phase: warps fetch (evaluating bin, 16 rows) units until none are left
+    // output phase: warps fetch (evaluating bin, 8 rows) units until none are left
     run_units<PW>(a, tb, s_cls, s_lead, s_nlead, &s_next, lane, tx0, ty0);
 }
 
-
-// one instantiation per (pitch, halo, library)
+// one instantiation per halo
 template <class F>
-auto dispatch_fast(int pw, int halo, int lib, F f)
+auto dispatch_fast(int halo, F f)
 {
-#define PP_CASE(P, HL, L) \
-    if (pw == P && halo == HL && lib == L) return f(se2_fast_kernel<P, HL, L>);
-#define PP_LIBS(P, HL) PP_CASE(P, HL, 0) PP_CASE(P, HL, 1) PP_CASE(P, HL, 2) PP_CASE(P, HL, 3)
-    PP_LIBS(22, 7) PP_LIBS(22, 8) PP_LIBS(22, 9) PP_LIBS(22, 10)
-    PP_LIBS(26, 11) PP_LIBS(26, 12) PP_LIBS(26, 13) PP_LIBS(26, 14)
-    PP_CASE(26, 15, 0) PP_CASE(26, 15, 1) PP_CASE(26, 15, 2)
-#undef PP_LIBS
+#define PP_CASE(HL) \
+    if (halo == HL) return f(se2_fast_kernel<HL>);
+    PP_CASE(7) PP_CASE(8) PP_CASE(9) PP_CASE(10) PP_CASE(11) PP_CASE(12) PP_CASE(13) PP_CASE(14)
 #undef PP_CASE
-    return f(se2_fast_kernel<26, 15, 3>);
+    return f(se2_fast_kernel<15>);
 }
-cudaError_t set_fast_smem(int pw, int halo, int lib, size_t bytes)
+cudaError_t set_fast_smem(int halo, size_t bytes)
 {
-    return dispatch_fast(pw, halo, lib, [&](auto kernel) { return cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(bytes)); });
+    return dispatch_fast(halo, [&](auto kernel) { return cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(bytes)); });
 }
-void launch_fast(int pw, int halo, int lib, dim3 grid, size_t smem, cudaStream_t stream, const FastArgs &args)
+void launch_fast(int halo, dim3 grid, size_t smem, cudaStream_t stream, const FastArgs &args)
 {
-    dispatch_fast(pw, halo, lib, [&](auto kernel) { kernel<<<grid, FT_THREADS, smem, stream>>>(args); return cudaSuccess; });
+    dispatch_fast(halo, [&](auto kernel) { kernel<<<grid, FT_THREADS, smem, stream>>>(args); return cudaSuccess; });
 }
 
 // ---------------------------------------------------------------------------------------------
 // host planner
 // ---------------------------------------------------------------------------------------------
 using Library = std::vector<Recipe>;
-Library make_library(int lib)
+// Fixed libraries, listed in dependency-level order; the planner picks the one with the smallest covers
+// for the footprint at hand and truncates it to the tables that fit.
+//   STAIRS  2-runs along x, y and the two diagonals, four 4-cell "stair" bricks (two 2-runs offset by
+//           (2,+-1) or (+-1,2)) that follow rasterised oblique edges, then runs of 4 along x and y
+//           and of 8 along x (the stairs come first so that a truncated library keeps them)
+//   RUNS3   runs of 2/3/6 along x and y, diagonals of 2/3/4
+//   BLOCKS  rectangles 2x2 .. 8x8 for solid footprints
+//   RUNS    runs of 2/4/8 along x and y, diagonals of 2/4
+const std::vector<Library> &fixed_libraries()
 {
-    Library out;
-    for (int k = 0; k < lib_size(lib); ++k)
-        out.push_back(lib_recipe(lib, k));
-    return out;
+    static const std::vector<Library> libs = {
+        {{0, 0, 0, 0}, {0, 0, 1, 0}, {0, 0, 0, 1}, {0, 0, 1, 1}, {0, 0, 1, -1}, {1, 1, 2, 1}, {1, 1, 2, -1}, {2, 2, 1, 2}, {2, 2, -1, 2}, {1, 1, 2, 0}, {2, 2, 0, 2}, {9, 9, 4, 0}},
+        {{0, 0, 0, 0}, {0, 0, 1, 0}, {0, 0, 0, 1}, {0, 0, 1, 1}, {0, 0, 1, -1}, {1, 0, 2, 0}, {2, 0, 0, 2}, {3, 0, 2, 2}, {4, 0, 2, -2}, {3, 3, 2, 2}, {5, 5, 3, 0}, {6, 6, 0, 3}},
+        {{0, 0, 0, 0}, {0, 0, 1, 0}, {0, 0, 0, 1}, {1, 1, 0, 1}, {1, 1, 2, 0}, {2, 2, 0, 2}, {3, 3, 2, 0}, {4, 4, 4, 0}, {5, 5, 0, 4}, {6, 6, 0, 2}, {9, 9, 4, 0}, {10, 10, 0, 4}},
+        {{0, 0, 0, 0}, {0, 0, 1, 0}, {0, 0, 0, 1}, {0, 0, 1, 1}, {0, 0, 1, -1}, {1, 1, 2, 0}, {2, 2, 0, 2}, {3, 3, 2, 2}, {4, 4, 2, -2}, {5, 5, 4, 0}, {6, 6, 0, 4}},
+    };
+    return libs;
+}
+// dependency level of every table of a library (table 0: level 0)
+std::vector<int> library_levels(const Library &lib)
+{
+    std::vector<int> lvl(lib.size(), 0);
+    for (size_t k = 1; k < lib.size(); ++k)
+        lvl[k] = 1 + std::max(lvl[lib[k].a], lvl[lib[k].b]);
+    return lvl;
 }
 
 using Offsets = std::vector<std::pair<int, int>>;  // sorted, unique (dx, dy)
@@ -762,7 +668,7 @@ struct Se2Plan
     uint32_t uses = 0;
     // geometry
     bool usable = false;
-    int R = 0, PW = 0, rows = 0, copy_words = 0, n_tables = 0;
+    int R = 0, PW = 0, rows = 0, table_words = 0, n_tables = 0;
     size_t smem_bytes = 0;
     Library lib;
     int lib_id = 0;
@@ -918,26 +824,21 @@ pp_status build_plan(pp_handle h, int effort)
     }
     if (R > MAX_R)
         return PP_OK;
-    // 2. geometry
-    int pw = (4 + FT_W + 2 * R + 3) / 4;  // one margin word on the left
-    pw = pw <= 22 ? 22 : 26;  // the two instantiated pitches (both 2 mod 4: conflict-free half-warps)
-    // the staged halo is a template parameter of the kernel (table addresses are immediates)
-    const int halo = halo_for(pw, R);
-    const size_t guard_bytes = static_cast<size_t>(2) * (4 * pw + 4) * 4;  // Geo::GUARD on both sides of the tables
+    // 2. geometry: the staged halo is a template parameter of the kernel, the row pitch follows from it
+    const int halo = halo_for(R);
     pl->R = halo;
     pl->rows = FT_H + 2 * halo;
-    pl->PW = pw;
-    pl->copy_words = pl->rows * pl->PW;
-    const size_t table_bytes = static_cast<size_t>(4) * pl->copy_words * 4;
-    int slots = static_cast<int>(std::min<size_t>(MAX_TABLES, (SMEM_LIMIT - 1024 - guard_bytes) / table_bytes));
+    pl->PW = 32 + 2 * halo;
+    pl->table_words = pl->rows * pl->PW;
+    const size_t table_bytes = static_cast<size_t>(pl->table_words) * 4;
+    int slots = static_cast<int>(std::min<size_t>(MAX_TABLES, (SMEM_LIMIT - 1024) / table_bytes));
     // Every table costs a fixed amount per tile and saves samples per bin: with few bins per launch
-    // (a heading-sharded rank of an 8-GPU job builds 9) the costmap plus the two 2-runs is the optimum
-    // measured on B200 (tools/probe_tables.py).
+    // (a heading-sharded rank of an 8-GPU job builds 9) a short library is the optimum.
     pl->few_bins = h->t_end - h->t_begin <= FEW_BINS;
     if (pl->few_bins)
     {
         const char *few = getenv("PP_SE2_FEW_TABLES");  // tuning knob for experiments
-        slots = std::min(slots, few ? std::max(1, atoi(few)) : 3);
+        slots = std::min(slots, few ? std::max(1, atoi(few)) : 5);
     }
     if (const char *cap = getenv("PP_SE2_MAX_TABLES"))  // tuning knob for experiments
         slots = std::max(1, std::min(slots, atoi(cap)));
@@ -958,9 +859,10 @@ pp_status build_plan(pp_handle h, int effort)
     int best_lib = 0;
     size_t best_total = ~static_cast<size_t>(0);
     const uint32_t step = std::max(1u, nt / 18);
-    for (int cand = 0; cand < N_LIBS; ++cand)
+    const std::vector<Library> &libs = fixed_libraries();
+    for (int cand = 0; cand < static_cast<int>(libs.size()); ++cand)
     {
-        const Library lib = make_library(cand);
+        const Library &lib = libs[cand];
         const int n = std::min<int>(slots, static_cast<int>(lib.size()));
         auto bricks = brick_points(lib, n);
         size_t total = 0;
@@ -973,12 +875,12 @@ pp_status build_plan(pp_handle h, int effort)
         }
     }
     {
-        const Library lib = make_library(best_lib);
+        const Library &lib = libs[best_lib];
         pl->lib_id = best_lib;
         pl->n_tables = std::min<int>(slots, static_cast<int>(lib.size()));
         pl->lib.assign(lib.begin(), lib.begin() + pl->n_tables);
     }
-    pl->smem_bytes = table_bytes * pl->n_tables + guard_bytes;
+    pl->smem_bytes = table_bytes * pl->n_tables;
     auto bricks = brick_points(pl->lib, pl->n_tables);
 
     // 5. covers -> sample lists (byte offsets relative to the thread's base address)
@@ -998,8 +900,8 @@ pp_status build_plan(pp_handle h, int effort)
                     std::vector<uint32_t> words;
                     for (const Placement &p : cover_set(S, bricks, R, node_budget))
                     {
-                        const int ax = halo + 4 + p.ox, ay = halo + p.oy;  // >= 0; +4: the margin word
-                        const uint32_t word = static_cast<uint32_t>((p.brick * 4 + (ax & 3)) * pl->copy_words + ay * pl->PW + (ax >> 2));
+                        const int ax = halo + p.ox, ay = halo + p.oy;  // >= 0: the offset set lies inside the halo
+                        const uint32_t word = static_cast<uint32_t>(p.brick * pl->table_words + ay * pl->PW + ax);
                         words.push_back(word * 4);
                     }
                     it = memo.emplace(S, words).first;
@@ -1035,10 +937,14 @@ pp_status build_plan(pp_handle h, int effort)
             for (uint32_t tx = 0; tx < pl->tiles_x; ++tx)
                 if (pl->h_xclass[static_cast<size_t>(t) * pl->tiles_x + tx] == 255 ||
                     pl->h_yclass[static_cast<size_t>(t) * pl->tiles_y + ty] == 255)
-                {
-                    pl->h_work.push_back(tx | (ty << 16));
-                    pl->h_work.push_back(t);
-                }
+                    for (uint32_t half = 0; half < FT_W / GEN_W; ++half)  // in tiles of the generic kernel
+                    {
+                        const uint32_t gtx = tx * (FT_W / GEN_W) + half;
+                        if (gtx * GEN_W >= h->W)
+                            break;
+                        pl->h_work.push_back(gtx | (ty << 16));
+                        pl->h_work.push_back(t);
+                    }
     }
     pl->work_off[nt] = static_cast<uint32_t>(pl->h_work.size() / 2);
 
@@ -1052,7 +958,7 @@ pp_status build_plan(pp_handle h, int effort)
         PP_CUDA(h, cudaMemcpyAsync(pl->d_work, pl->h_work.data(), pl->h_work.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, h->stream));
     }
     PP_CUDA(h, cudaStreamSynchronize(h->stream));
-    PP_CUDA(h, set_fast_smem(pl->PW, pl->R, pl->lib_id, pl->smem_bytes));
+    PP_CUDA(h, set_fast_smem(pl->R, pl->smem_bytes));
     pl->usable = true;
     return PP_OK;
 }
@@ -1100,6 +1006,19 @@ pp_status pp_se2_launch_fast(pp_handle h, uint32_t x0, uint32_t y0, uint32_t x1,
     args.tile_x0 = tx_lo;
     args.tile_y0 = ty_lo;
     args.n_tables = pl->n_tables;
+    {
+        const std::vector<int> lvl = library_levels(pl->lib);
+        args.rec_sync = 0;
+        for (int k = 1; k < pl->n_tables; ++k)
+        {
+            const Recipe &rc = pl->lib[k];
+            args.rec_a[k] = rc.a * pl->table_words;
+            args.rec_b[k] = rc.b * pl->table_words;
+            args.rec_d[k] = rc.dv * pl->PW + rc.du;
+            if (lvl[k] != lvl[k - 1] && lvl[k] > 1)  // level 1 reads only table 0, which the staging barrier covers
+                args.rec_sync |= 1u << k;
+        }
+    }
     const dim3 grid(tx_hi - tx_lo, ty_hi - ty_lo, 1);
     const uint64_t n_tiles = static_cast<uint64_t>(grid.x) * grid.y;
     double sample_sum = 0.0;
@@ -1161,7 +1080,7 @@ pp_status pp_se2_launch_fast(pp_handle h, uint32_t x0, uint32_t y0, uint32_t x1,
         {
             const uint32_t nw = pl->work_off[t + k + 1] - pl->work_off[t + k];
             generic_pairs += nw;
-            fast_pairs += static_cast<uint64_t>(pl->tiles_x) * pl->tiles_y - nw;
+            fast_pairs += static_cast<uint64_t>(pl->tiles_x) * pl->tiles_y - nw / (FT_W / GEN_W);
             if (args.chain_prev[k][0] == NO_LINK)  // bins that share an earlier bin's evaluation load nothing
                 sample_sum += pl->list_len[(t + k) * 4];
         }
@@ -1186,7 +1105,7 @@ pp_status pp_se2_launch_fast(pp_handle h, uint32_t x0, uint32_t y0, uint32_t x1,
                     for (uint32_t e = w0; e < w1; ++e)
                     {
                         const uint32_t tile = pl->h_work[2 * e], wx = tile & 0xFFFFu, wy = tile >> 16;
-                        if (wx >= tx_lo && wx < tx_hi && wy >= ty_lo && wy < ty_hi)
+                        if (wx / (FT_W / GEN_W) >= tx_lo && wx / (FT_W / GEN_W) < tx_hi && wy >= ty_lo && wy < ty_hi)
                         {
                             pl->region_work.push_back(tile);
                             pl->region_work.push_back(pl->h_work[2 * e + 1]);
@@ -1209,7 +1128,7 @@ pp_status pp_se2_launch_fast(pp_handle h, uint32_t x0, uint32_t y0, uint32_t x1,
                 }
             }
         }
-        launch_fast(pl->PW, pl->R, pl->lib_id, grid, pl->smem_bytes, h->stream, args);
+        launch_fast(pl->R, grid, pl->smem_bytes, h->stream, args);
         h->launches++;
         PP_CUDA(h, cudaGetLastError());
         if (forked)

@@ -299,19 +299,26 @@ pp_status pp_se2_volume_build(pp_handle h, uint32_t n_theta, float ox, float oy,
     // heading -> (cos, sin) with the host libm, formed exactly like the reference does:
     // theta = motion.theta * bin_size (astar_hybrid.cpp:283), bin_size = 2.0f*(float)M_PI/size_theta
     // (motion_hybrid.cpp:10); float cos/sin as in collision_checker.cpp:155-156.
-    std::vector<float2> trig(n_theta);
-    const float bin = 2.0f * static_cast<float>(M_PI) / static_cast<float>(n_theta);
-    for (uint32_t t = 0; t < n_theta; ++t)
+    // The table only depends on (n_theta, ot): it is recomputed and uploaded when those change, from a
+    // vector the handle keeps alive, so a rebuild with unchanged headings costs no copy and no host wait.
+    if (h->host_trig.size() != n_theta || h->trig_ot != ot || !h->d_trig)
     {
-        const float tf = static_cast<float>(t) + ot;
-        const float theta = tf * bin;
-        trig[t].x = cosf(theta);
-        trig[t].y = sinf(theta);
+        // the previous upload (if any) reads the old vector: finish it before the vector is replaced
+        PP_CUDA(h, cudaStreamSynchronize(h->stream));
+        std::vector<float2> trig(n_theta);
+        const float bin = 2.0f * static_cast<float>(M_PI) / static_cast<float>(n_theta);
+        for (uint32_t t = 0; t < n_theta; ++t)
+        {
+            const float tf = static_cast<float>(t) + ot;
+            const float theta = tf * bin;
+            trig[t].x = cosf(theta);
+            trig[t].y = sinf(theta);
+        }
+        h->host_trig.swap(trig);
+        h->trig_ot = ot;
+        PP_CUDA(h, pp_reserve(h->d_trig, h->trig_cap, static_cast<size_t>(n_theta)));
+        PP_CUDA(h, cudaMemcpyAsync(h->d_trig, h->host_trig.data(), sizeof(float2) * n_theta, cudaMemcpyHostToDevice, h->stream));
     }
-    PP_CUDA(h, pp_reserve(h->d_trig, h->trig_cap, static_cast<size_t>(n_theta)));
-    PP_CUDA(h, cudaMemcpyAsync(h->d_trig, trig.data(), sizeof(float2) * n_theta, cudaMemcpyHostToDevice, h->stream));
-    PP_CUDA(h, cudaStreamSynchronize(h->stream));  // `trig` is pageable and about to go out of scope
-    h->host_trig.swap(trig);
 
     const bool banded = h->band_y1 > h->band_y0;
     pp_status s = pp_se2_launch(h, 0, banded ? std::min(h->band_y0, h->H) : 0, h->W, banded ? std::min(h->band_y1, h->H) : h->H);
