@@ -37,6 +37,8 @@
 // greedy + branch and bound.
 #include "se2_plan.h"
 
+#include <cuda.h>  // CUtensorMap (types only; the encoder is fetched through cudaGetDriverEntryPoint)
+
 #include <algorithm>
 #include <cmath>
 #include <cstdlib>
@@ -66,6 +68,7 @@ constexpr int MAX_LIST_WORDS = 6400;
 constexpr int MAX_R = 15;
 constexpr int MIN_HALO = 7;
 constexpr size_t SMEM_LIMIT = (227 * 1024 - 2048) / CTAS_PER_SM;  // per CTA; 1 KB per CTA is reserved by the system
+constexpr size_t STAGE_BYTES = static_cast<size_t>(PP_FT_THREADS / 32) * 8 * 128 + 128;  // per-warp 8 x 128-byte store blocks (+ alignment)
 
 // A brick library: table 0 is the costmap itself (the one-point brick); table k > 0 is
 // T_k = max(T_a, T_b shifted by (du, dv)), a and b earlier tables. Listed in dependency-level order.
@@ -76,6 +79,9 @@ struct Recipe
 
 struct FastArgs
 {
+    // the own volume as a 3-D uint8 tensor (x, y, bin) for bulk-tensor stores of 128 x 8 row blocks
+    alignas(64) CUtensorMap vol_map;
+    int use_tma;  // 0: plain 32-bit stores (peer volumes mapped, or rows not 16-byte aligned)
     const uint8_t *cost;
     uint8_t *vol;             // own volume
     long long peer_delta[7];  // byte distance from the own volume to each mapped peer volume
@@ -147,7 +153,7 @@ __device__ __forceinline__ void accumulate(uint32_t (&odd)[QPT], uint32_t (&even
 // stored to every bin of the evaluating bin's chain that is in the matching class on this tile.
 template <int PW>
 __device__ __forceinline__ void run_units(const FastArgs &a, const uint32_t *sm, const uint8_t *s_cls, const uint8_t *s_lead,
-                                          uint32_t n_lead, uint32_t *s_next, int lane, int tx0, int ty0)
+                                          uint32_t n_lead, uint32_t *s_next, int lane, int tx0, int ty0, uint32_t *stage)
 {
     const int W = static_cast<int>(a.W), H = static_cast<int>(a.H);
     // after the transpose this lane holds word (lane >> 2) + 8 * (lane & 3) of the 32-word row
@@ -236,6 +242,44 @@ __device__ __forceinline__ void run_units(const FastArgs &a, const uint32_t *sm,
             odd[j] = __byte_perm(p, got2, sel2);
         }
         uint32_t link = a.chain_next[t][cls];
+        if (a.use_tma)
+        {
+            // The warp's 8 x 128-byte block goes to its staging buffer and from there to every bin of the
+            // chain with one bulk-tensor store each (the TMA unit clips at the map's edges). The buffer is
+            // reused once the previous unit's stores have read it.
+            if (lane == 0)
+                asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+            __syncwarp();
+#pragma unroll
+            for (int j = 0; j < QPT; ++j)
+                stage[j * 32 + out_word] = odd[j];
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            __syncwarp();
+            if (lane == 0)
+            {
+                const uint32_t src = static_cast<uint32_t>(__cvta_generic_to_shared(stage));
+                uint32_t tb_ = t;
+                while (true)
+                {
+                    asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%1, %2, %3}], [%4];" ::"l"(&a.vol_map), "r"(tx0),
+                                 "r"(gy), "r"(static_cast<int>(a.t_first + tb_)), "r"(src)
+                                 : "memory");
+                    uint32_t t2 = NO_LINK;
+                    while (link != NO_LINK && t2 == NO_LINK)
+                    {
+                        const uint32_t lt = link & 0xFFu, lc = link >> 8;
+                        link = a.chain_next[lt][lc];
+                        if (s_cls[lt] == lc)
+                            t2 = lt;
+                    }
+                    if (t2 == NO_LINK)
+                        break;
+                    tb_ = t2;
+                }
+                asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+            }
+            continue;
+        }
         while (true)
         {
             if (tile_inside && a.n_peers == 0)
@@ -270,6 +314,9 @@ __device__ __forceinline__ void run_units(const FastArgs &a, const uint32_t *sm,
             out = a.vol + plane * (a.t_first + t2) + unit_off;
         }
     }
+    // the staging buffer must outlive the bulk stores that read it
+    if (a.use_tma && lane == 0)
+        asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
 }
 
 // Shared-memory geometry, compile-time (the halo is a template parameter) so that the row offsets of the
@@ -287,7 +334,7 @@ constexpr int halo_for(int reach) { return reach < MIN_HALO ? MIN_HALO : reach; 
 template <int HALO>
 __global__ void __launch_bounds__(FT_THREADS, CTAS_PER_SM) se2_fast_kernel(const __grid_constant__ FastArgs a)
 {
-    extern __shared__ __align__(16) uint32_t tb[];
+    extern __shared__ __align__(128) uint32_t tb[];
     __shared__ uint8_t s_cls[MAX_T_PER_LAUNCH];
     __shared__ uint8_t s_lead[MAX_T_PER_LAUNCH];  // bins that evaluate on this tile
     __shared__ uint32_t s_next, s_nlead;
@@ -395,7 +442,9 @@ __global__ void __launch_bounds__(FT_THREADS, CTAS_PER_SM) se2_fast_kernel(const
     __syncthreads();  // also orders s_lead / s_nlead when no table beyond the costmap is built
 
     // output phase: warps fetch (evaluating bin, 8 rows) units until none are left
-    run_units<PW>(a, tb, s_cls, s_lead, s_nlead, &s_next, lane, tx0, ty0);
+    // per-warp staging blocks of the bulk stores sit behind the tables, 128-byte aligned
+    uint32_t *stage = tb + ((a.n_tables * CW + 31) & ~31) + warp * (QPT * 32);
+    run_units<PW>(a, tb, s_cls, s_lead, s_nlead, &s_next, lane, tx0, ty0, stage);
 }
 
 // one instantiation per halo
@@ -831,7 +880,7 @@ pp_status build_plan(pp_handle h, int effort)
     pl->PW = 32 + 2 * halo;
     pl->table_words = pl->rows * pl->PW;
     const size_t table_bytes = static_cast<size_t>(pl->table_words) * 4;
-    int slots = static_cast<int>(std::min<size_t>(MAX_TABLES, (SMEM_LIMIT - 1024) / table_bytes));
+    int slots = static_cast<int>(std::min<size_t>(MAX_TABLES, (SMEM_LIMIT - 1024 - STAGE_BYTES) / table_bytes));
     // Every table costs a fixed amount per tile and saves samples per bin: with few bins per launch
     // (a heading-sharded rank of an 8-GPU job builds 9) a short library is the optimum.
     pl->few_bins = h->t_end - h->t_begin <= FEW_BINS;
@@ -880,7 +929,7 @@ pp_status build_plan(pp_handle h, int effort)
         pl->n_tables = std::min<int>(slots, static_cast<int>(lib.size()));
         pl->lib.assign(lib.begin(), lib.begin() + pl->n_tables);
     }
-    pl->smem_bytes = table_bytes * pl->n_tables;
+    pl->smem_bytes = table_bytes * pl->n_tables + STAGE_BYTES;
     auto bricks = brick_points(pl->lib, pl->n_tables);
 
     // 5. covers -> sample lists (byte offsets relative to the thread's base address)
@@ -964,6 +1013,33 @@ pp_status build_plan(pp_handle h, int effort)
 }
 }  // namespace
 
+namespace
+{
+// The volume as a (x, y, bin) uint8 tensor with 128 x 8 x 1 boxes. The encoder lives in the driver library;
+// it is looked up once through the runtime, so the product does not link against libcuda.
+using EncodeTiled = CUresult (*)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
+                                 const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                 CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+bool encode_volume_map(CUtensorMap *map, uint8_t *vol, uint32_t W, uint32_t H, uint32_t n_theta)
+{
+    static EncodeTiled encode = [] {
+        void *fn = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess)
+            fn = nullptr;
+        return reinterpret_cast<EncodeTiled>(fn);
+    }();
+    if (!encode || W % 16 != 0 || reinterpret_cast<uintptr_t>(vol) % 16 != 0)
+        return false;
+    const cuuint64_t dims[3] = {W, H, n_theta};
+    const cuuint64_t strides[2] = {W, static_cast<cuuint64_t>(W) * H};
+    const cuuint32_t box[3] = {FT_W, QPT, 1};
+    const cuuint32_t estr[3] = {1, 1, 1};
+    return encode(map, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, vol, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+}  // namespace
+
 pp_status pp_se2_launch_fast(pp_handle h, uint32_t x0, uint32_t y0, uint32_t x1, uint32_t y1)
 {
     if (!plan_matches(h->plan, h))
@@ -997,6 +1073,11 @@ pp_status pp_se2_launch_fast(pp_handle h, uint32_t x0, uint32_t y0, uint32_t x1,
         for (int p = 1; p < n; ++p)
             args.peer_delta[p - 1] = static_cast<long long>(reinterpret_cast<uintptr_t>(targets[p]) - reinterpret_cast<uintptr_t>(targets[0]));
     }
+    // bulk-tensor stores unless peers' volumes are written too (those go out as plain stores over NVLink)
+    args.use_tma = args.n_peers == 0 && getenv("PP_SE2_NO_TMA") == nullptr && encode_volume_map(&args.vol_map, h->d_vol, h->W, h->H, h->n_theta);
+    if (getenv("PP_SE2_DEBUG"))
+        fprintf(stderr, "[pp] se2 fast: halo %d tables %d smem %zu tma %d grid %ux%u\n", pl->R, pl->n_tables, pl->smem_bytes, args.use_tma,
+                (x1 + FT_W - 1) / FT_W - x0 / FT_W, (y1 + FT_H - 1) / FT_H - y0 / FT_H);
     args.xclass = pl->d_xclass;
     args.yclass = pl->d_yclass;
     args.W = h->W;
@@ -1085,7 +1166,7 @@ pp_status pp_se2_launch_fast(pp_handle h, uint32_t x0, uint32_t y0, uint32_t x1,
                 sample_sum += pl->list_len[(t + k) * 4];
         }
         const uint32_t w0 = pl->work_off[t], w1 = pl->work_off[t + n];
-        if (w1 > w0)
+        if (w1 > w0 && !getenv("PP_SE2_SKIP_GENERIC"))  // (timing experiments only: the result is incomplete without it)
         {
             const bool whole_map = tx_lo == 0 && ty_lo == 0 && tx_hi >= pl->tiles_x && ty_hi >= pl->tiles_y;
             if (whole_map)
