@@ -96,6 +96,9 @@ struct FastArgs
     int32_t rec_a[MAX_TABLES], rec_b[MAX_TABLES], rec_d[MAX_TABLES];
     uint32_t rec_sync;  // bit k: table k starts a new dependency level (block barrier before it)
     uint32_t t_first, n_t;
+    // mixed tiles: first column (row) of the right-hand (upper) range of a bin and the class of the range before it
+    uint16_t xsplit[MAX_T_PER_LAUNCH], ysplit[MAX_T_PER_LAUNCH];
+    uint8_t split_left[MAX_T_PER_LAUNCH];  // bit 0: class of the columns before xsplit, bit 1: of the rows before ysplit
     uint16_t list_off[MAX_T_PER_LAUNCH][4];
     uint16_t list_len[MAX_T_PER_LAUNCH][4];
     // (bin, class) pairs of this launch with the SAME offset set form a chain in bin order (for a
@@ -145,14 +148,58 @@ __device__ __forceinline__ void accumulate(uint32_t (&odd)[QPT], uint32_t (&even
     }
 }
 
+// A range boundary of a bin crosses the tile ("mixed" tile): an evaluation with the offset set of one class pair
+// is valid for the columns / rows of those classes only. Rare (the boundaries sit in the first tiles of a few
+// bins), so this is an out-of-line call with plain stores: whole words where all four columns are in, bytes else.
+__device__ __noinline__ void store_mixed(const FastArgs &a, uint32_t cls, uint32_t t, uint32_t lc, int gx, int gy, uint32_t r0, uint32_t r1,
+                                         uint32_t r2, uint32_t r3, uint32_t r4, uint32_t r5, uint32_t r6, uint32_t r7)
+{
+    const uint32_t res[QPT] = {r0, r1, r2, r3, r4, r5, r6, r7};
+    static_assert(QPT == 8, "store_mixed takes the 8 rows of a unit");
+    const int W = static_cast<int>(a.W), H = static_cast<int>(a.H);
+    const uint32_t mcx = cls % 3u, mcy = cls / 3u;
+    const int xsplit = a.xsplit[t], ysplit = a.ysplit[t];
+    const uint32_t xleft = a.split_left[t] & 1u, yleft = (a.split_left[t] >> 1) & 1u;
+    uint32_t xm = 0;  // bit b: column gx + b is inside the map and in this evaluation's column class
+#pragma unroll
+    for (int b = 0; b < 4; ++b)
+        if (gx + b < W && (mcx != 2 || ((gx + b < xsplit) ? xleft : 1u - xleft) == (lc >> 1)))
+            xm |= 1u << b;
+    if (xm == 0)
+        return;
+    uint8_t *base = a.vol + static_cast<size_t>(a.W) * a.H * (a.t_first + t) + gx;
+#pragma unroll
+    for (int j = 0; j < QPT; ++j)
+    {
+        const int y = gy + j;
+        if (y >= H || (mcy == 2 && ((y < ysplit) ? yleft : 1u - yleft) != (lc & 1u)))
+            continue;
+        uint8_t *dst = base + static_cast<size_t>(y) * a.W;
+        for (int p = -1; p < a.n_peers; ++p)  // own volume, then the peers' over NVLink
+        {
+            uint8_t *d = p < 0 ? dst : dst + a.peer_delta[p];
+            if (xm == 0xFu)
+                *reinterpret_cast<uint32_t *>(d) = res[j];
+            else
+                for (int b = 0; b < 4; ++b)
+                    if (xm >> b & 1u)
+                        d[b] = static_cast<uint8_t>(res[j] >> (8 * b));
+        }
+    }
+}
+
 // Output phase. A work unit is 8 rows of one evaluating bin: one warp, lane q owns the cells q, q+32, q+64,
 // q+96 of each row. Warps fetch units from a shared counter, so bins with long and short sample lists
 // balance out. The loads of the next sample pair are issued before the max operations of the current one
 // (software pipelining by hand). The result is transposed across groups of four lanes, so that lane 4g+i
 // holds the four consecutive cells 4g+32i .. 4g+32i+3 and a warp's store is one whole 128-byte row, and is
 // stored to every bin of the evaluating bin's chain that is in the matching class on this tile.
+// A tile that the boundary between a bin's two column (row) ranges crosses is "mixed": the unit is evaluated
+// once per range and the results are blended per column (row).
+constexpr uint32_t LEAD_MIXED = 0x80;  // s_lead_lc flag: the evaluation covers only its classes' part of a mixed tile
+constexpr uint32_t CLS_MIXED0 = 4;  // s_cls: 0..3 uniform class cx*2+cy; 4 + cx + 3*cy with cx, cy in {0,1,2 = mixed}; 255 generic
 template <int PW>
-__device__ __forceinline__ void run_units(const FastArgs &a, const uint32_t *sm, const uint8_t *s_cls, const uint8_t *s_lead,
+__device__ __forceinline__ void run_units(const FastArgs &a, const uint32_t *sm, const uint8_t *s_cls, const uint8_t *s_lead, const uint8_t *s_lead_lc,
                                           uint32_t n_lead, uint32_t *s_next, int lane, int tx0, int ty0, uint32_t *stage)
 {
     const int W = static_cast<int>(a.W), H = static_cast<int>(a.H);
@@ -163,10 +210,6 @@ __device__ __forceinline__ void run_units(const FastArgs &a, const uint32_t *sm,
     const size_t plane = static_cast<size_t>(a.W) * a.H;
     const uint32_t n_units = UNITS_PER_BIN * n_lead;
     const uint32_t cell0 = static_cast<uint32_t>(ty0) * a.W + static_cast<uint32_t>(gx);  // < 2^30
-    uint32_t row_off[QPT];
-#pragma unroll
-    for (int j = 0; j < QPT; ++j)
-        row_off[j] = cell0 + static_cast<uint32_t>(j) * a.W;
     const bool tile_inside = tx0 + FT_W <= W && ty0 + FT_H <= H;
     // lane roles of the two transpose steps
     const bool odd_lane = lane & 1, upper_lane = lane & 2;
@@ -180,17 +223,16 @@ __device__ __forceinline__ void run_units(const FastArgs &a, const uint32_t *sm,
         unit = __shfl_sync(0xffffffffu, unit, 0);
         if (unit >= n_units)
             break;
-        // s_lead lists the bins that evaluate on this tile (see the kernel prologue)
+        // s_lead lists the (bin, class pair) evaluations of this tile (see the kernel prologue)
         const uint32_t t = s_lead[unit / UNITS_PER_BIN];
-        const uint32_t cls = s_cls[t];
+        const uint32_t lcm = s_lead_lc[unit / UNITS_PER_BIN];
+        const uint32_t lc = lcm & 3u;  // column class * 2 + row class
         const int row0 = QPT * static_cast<int>(unit % UNITS_PER_BIN);
         const uint8_t *smb = reinterpret_cast<const uint8_t *>(sm + row0 * PW + lane);
         const int gy = ty0 + row0;
-        const uint32_t unit_off = static_cast<uint32_t>(row0) * a.W;
-        uint8_t *out = a.vol + plane * (a.t_first + t) + unit_off;  // warp-uniform
-        const uint32_t *list = a.lists + a.list_off[t][cls];
-        const uint32_t n_samples = a.list_len[t][cls];  // >= 1
-        const uint32_t len = n_samples & ~1u;            // samples consumed in pairs
+        const uint32_t *list = a.lists + a.list_off[t][lc];
+        const uint32_t n_samples = a.list_len[t][lc];  // >= 1
+        const uint32_t len = n_samples & ~1u;           // samples consumed in pairs
         uint32_t odd[QPT], even[QPT];
 #pragma unroll
         for (int j = 0; j < QPT; ++j)
@@ -231,6 +273,7 @@ __device__ __forceinline__ void run_units(const FastArgs &a, const uint32_t *sm,
         // halves: odd = (., b1, ., b3), even = (., b0, ., b2), b_i = the lane's cell q + 32 i.
         // Step 1 (lane ^ 1): even lanes collect (b0, b2) of both lanes, odd lanes (b1, b3).
         // Step 2 (lane ^ 2): lower lanes collect bytes 0..1 of both, upper lanes bytes 2..3.
+        uint32_t res[QPT];
 #pragma unroll
         for (int j = 0; j < QPT; ++j)
         {
@@ -239,9 +282,14 @@ __device__ __forceinline__ void run_units(const FastArgs &a, const uint32_t *sm,
             const uint32_t got = __shfl_xor_sync(0xffffffffu, give, 1);
             const uint32_t p = __byte_perm(keep, got, sel1);
             const uint32_t got2 = __shfl_xor_sync(0xffffffffu, p, 2);
-            odd[j] = __byte_perm(p, got2, sel2);
+            res[j] = __byte_perm(p, got2, sel2);
         }
-        uint32_t link = a.chain_next[t][cls];
+        if (lcm & LEAD_MIXED)
+        {
+            store_mixed(a, s_cls[t] - CLS_MIXED0, t, lc, gx, gy, res[0], res[1], res[2], res[3], res[4], res[5], res[6], res[7]);
+            continue;
+        }
+        uint32_t link = a.chain_next[t][lc];
         if (a.use_tma)
         {
             // The warp's 8 x 128-byte block goes to its staging buffer and from there to every bin of the
@@ -252,7 +300,7 @@ __device__ __forceinline__ void run_units(const FastArgs &a, const uint32_t *sm,
             __syncwarp();
 #pragma unroll
             for (int j = 0; j < QPT; ++j)
-                stage[j * 32 + out_word] = odd[j];
+                stage[j * 32 + out_word] = res[j];
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
             __syncwarp();
             if (lane == 0)
@@ -280,13 +328,15 @@ __device__ __forceinline__ void run_units(const FastArgs &a, const uint32_t *sm,
             }
             continue;
         }
+        const uint32_t unit_off = static_cast<uint32_t>(row0) * a.W;
+        uint8_t *out = a.vol + plane * (a.t_first + t) + unit_off;  // warp-uniform
         while (true)
         {
             if (tile_inside && a.n_peers == 0)
             {
 #pragma unroll
                 for (int j = 0; j < QPT; ++j)
-                    *reinterpret_cast<uint32_t *>(out + row_off[j]) = odd[j];
+                    *reinterpret_cast<uint32_t *>(out + cell0 + static_cast<uint32_t>(j) * a.W) = res[j];
             }
             else if (in_x)
             {
@@ -294,10 +344,10 @@ __device__ __forceinline__ void run_units(const FastArgs &a, const uint32_t *sm,
                 for (int j = 0; j < QPT; ++j)
                     if (gy + j < H)
                     {
-                        uint8_t *dst = out + row_off[j];
-                        *reinterpret_cast<uint32_t *>(dst) = odd[j];
+                        uint8_t *dst = out + cell0 + static_cast<uint32_t>(j) * a.W;
+                        *reinterpret_cast<uint32_t *>(dst) = res[j];
                         for (int p = 0; p < a.n_peers; ++p)  // peer volumes over NVLink
-                            *reinterpret_cast<uint32_t *>(dst + a.peer_delta[p]) = odd[j];
+                            *reinterpret_cast<uint32_t *>(dst + a.peer_delta[p]) = res[j];
                     }
             }
             // next bin of the chain that is in the matching class on this tile
@@ -336,7 +386,8 @@ __global__ void __launch_bounds__(FT_THREADS, CTAS_PER_SM) se2_fast_kernel(const
 {
     extern __shared__ __align__(128) uint32_t tb[];
     __shared__ uint8_t s_cls[MAX_T_PER_LAUNCH];
-    __shared__ uint8_t s_lead[MAX_T_PER_LAUNCH];  // bins that evaluate on this tile
+    __shared__ uint8_t s_lead[4 * MAX_T_PER_LAUNCH];     // evaluations of this tile: bin ...
+    __shared__ uint8_t s_lead_lc[4 * MAX_T_PER_LAUNCH];  // ... and its class pair (| LEAD_MIXED)
     __shared__ uint32_t s_next, s_nlead;
     using G = Geo<HALO>;
     const int tid = threadIdx.x;
@@ -377,7 +428,8 @@ __global__ void __launch_bounds__(FT_THREADS, CTAS_PER_SM) se2_fast_kernel(const
         }
     }
     static_assert(MAX_T_PER_LAUNCH <= FT_THREADS, "one bin class per thread");
-    const uint32_t my_cls = (my_cx > 1 || my_cy > 1) ? 255u : my_cx * 2 + my_cy;
+    // 0..3: uniform class pair; CLS_MIXED0 + cx + 3 cy: a range boundary crosses the tile; 255: generic work list
+    const uint32_t my_cls = (my_cx > 2 || my_cy > 2) ? 255u : (my_cx == 2 || my_cy == 2) ? CLS_MIXED0 + my_cx + 3 * my_cy : my_cx * 2 + my_cy;
     if (static_cast<uint32_t>(tid) < a.n_t)
         s_cls[tid] = static_cast<uint8_t>(my_cls);
     if (tid == 0)
@@ -402,11 +454,32 @@ __global__ void __launch_bounds__(FT_THREADS, CTAS_PER_SM) se2_fast_kernel(const
     // chain (host-built, in bin order) evaluates and stores to all of them. One bin per thread.
     if (my_cls != 255u)
     {
-        bool evaluated_earlier = false;
-        for (uint32_t link = a.chain_prev[tid][my_cls]; link != NO_LINK && !evaluated_earlier; link = a.chain_prev[link & 0xFFu][link >> 8])
+        bool evaluated_earlier = false;  // a mixed tile of a bin is always evaluated for that bin alone
+        for (uint32_t link = my_cls < CLS_MIXED0 ? a.chain_prev[tid][my_cls] : NO_LINK; link != NO_LINK && !evaluated_earlier;
+             link = a.chain_prev[link & 0xFFu][link >> 8])
             evaluated_earlier = s_cls[link & 0xFFu] == (link >> 8);
-        if (!evaluated_earlier)
-            s_lead[atomicAdd(&s_nlead, 1u)] = static_cast<uint8_t>(tid);
+        if (my_cls < CLS_MIXED0)
+        {
+            if (!evaluated_earlier)
+            {
+                const uint32_t k = atomicAdd(&s_nlead, 1u);
+                s_lead[k] = static_cast<uint8_t>(tid);
+                s_lead_lc[k] = static_cast<uint8_t>(my_cls);
+            }
+        }
+        else
+        {
+            // one evaluation per class pair present on the tile
+            const uint32_t cx_lo = my_cx == 2 ? 0 : my_cx, cx_hi = my_cx == 2 ? 1 : my_cx;
+            const uint32_t cy_lo = my_cy == 2 ? 0 : my_cy, cy_hi = my_cy == 2 ? 1 : my_cy;
+            uint32_t k = atomicAdd(&s_nlead, (cx_hi - cx_lo + 1) * (cy_hi - cy_lo + 1));
+            for (uint32_t cxv = cx_lo; cxv <= cx_hi; ++cxv)
+                for (uint32_t cyv = cy_lo; cyv <= cy_hi; ++cyv, ++k)
+                {
+                    s_lead[k] = static_cast<uint8_t>(tid);
+                    s_lead_lc[k] = static_cast<uint8_t>(cxv * 2 + cyv) | LEAD_MIXED;
+                }
+        }
     }
 
     // brick tables: T_k = max(T_a, T_b shifted); tables of one dependency level need no barrier between them
@@ -444,7 +517,7 @@ __global__ void __launch_bounds__(FT_THREADS, CTAS_PER_SM) se2_fast_kernel(const
     // output phase: warps fetch (evaluating bin, 8 rows) units until none are left
     // per-warp staging blocks of the bulk stores sit behind the tables, 128-byte aligned
     uint32_t *stage = tb + ((a.n_tables * CW + 31) & ~31) + warp * (QPT * 32);
-    run_units<PW>(a, tb, s_cls, s_lead, s_nlead, &s_next, lane, tx0, ty0, stage);
+    run_units<PW>(a, tb, s_cls, s_lead, s_lead_lc, s_nlead, &s_next, lane, tx0, ty0, stage);
 }
 
 // one instantiation per halo
@@ -724,6 +797,8 @@ struct Se2Plan
     uint32_t tiles_x = 0, tiles_y = 0;
     uint8_t *d_xclass = nullptr, *d_yclass = nullptr;
     std::vector<uint8_t> h_xclass, h_yclass;
+    std::vector<uint16_t> xsplit, ysplit;  // per bin: where the second range starts (mixed tiles)
+    std::vector<uint8_t> split_left;      // per bin: bit 0 / 1 = class of the columns / rows before the split
     // per bin: up to 4 sample lists (class = cx*2 + cy)
     std::vector<uint32_t> lists;
     std::vector<uint32_t> list_off;  // [n_theta*4]
@@ -965,21 +1040,54 @@ pp_status build_plan(pp_handle h, int effort)
     pl->h_xclass.assign(static_cast<size_t>(nt) * pl->tiles_x, 255);
     pl->h_yclass.assign(static_cast<size_t>(nt) * pl->tiles_y, 255);
     pl->work_off.assign(nt + 1, 0);
+    pl->xsplit.assign(nt, 0);
+    pl->ysplit.assign(nt, 0);
+    pl->split_left.assign(nt, 0);
+    // class of a tile [lo, hi) on one axis: inside one range -> that class; inside the union of the two ranges
+    // when they touch -> 2 (mixed: evaluated once per range and blended); anything else -> 255 (generic kernel)
+    auto tile_class = [](const AxisClasses &ac, int lo, int hi, int split, int left) -> uint8_t {
+        for (int k = 0; k < ac.n_classes; ++k)
+            if (lo >= ac.lo[k] && hi <= ac.hi[k])
+                return static_cast<uint8_t>(k);
+        if (split >= 0 && lo >= ac.lo[left] && hi <= ac.hi[1 - left])
+            return 2;
+        return 255;
+    };
+    auto split_of = [](const AxisClasses &ac, int &left) {
+        if (ac.n_classes == 2 && ac.hi[0] == ac.lo[1])
+        {
+            left = 0;
+            return ac.hi[0];
+        }
+        if (ac.n_classes == 2 && ac.hi[1] == ac.lo[0])
+        {
+            left = 1;
+            return ac.hi[1];
+        }
+        left = 0;
+        return -1;
+    };
+    const bool allow_mixed = getenv("PP_SE2_NO_MIXED") == nullptr;  // tuning knob for experiments
     for (uint32_t t = 0; t < nt; ++t)
     {
+        int xleft = 0, yleft = 0;
+        int xs = split_of(xc[t], xleft), ys = split_of(yc[t], yleft);
+        if (!allow_mixed || xs > 0xFFFF)
+            xs = -1;
+        if (!allow_mixed || ys > 0xFFFF)
+            ys = -1;
+        pl->xsplit[t] = static_cast<uint16_t>(std::max(xs, 0));
+        pl->ysplit[t] = static_cast<uint16_t>(std::max(ys, 0));
+        pl->split_left[t] = static_cast<uint8_t>(xleft | yleft << 1);
         for (uint32_t tx = 0; tx < pl->tiles_x; ++tx)
         {
             const int lo = static_cast<int>(tx * FT_W), hi = static_cast<int>(std::min(h->W, (tx + 1) * FT_W));
-            for (int k = 0; k < xc[t].n_classes; ++k)
-                if (lo >= xc[t].lo[k] && hi <= xc[t].hi[k])
-                    pl->h_xclass[static_cast<size_t>(t) * pl->tiles_x + tx] = static_cast<uint8_t>(k);
+            pl->h_xclass[static_cast<size_t>(t) * pl->tiles_x + tx] = tile_class(xc[t], lo, hi, xs, xleft);
         }
         for (uint32_t ty = 0; ty < pl->tiles_y; ++ty)
         {
             const int lo = static_cast<int>(ty * FT_H), hi = static_cast<int>(std::min(h->H, (ty + 1) * FT_H));
-            for (int k = 0; k < yc[t].n_classes; ++k)
-                if (lo >= yc[t].lo[k] && hi <= yc[t].hi[k])
-                    pl->h_yclass[static_cast<size_t>(t) * pl->tiles_y + ty] = static_cast<uint8_t>(k);
+            pl->h_yclass[static_cast<size_t>(t) * pl->tiles_y + ty] = tile_class(yc[t], lo, hi, ys, yleft);
         }
         pl->work_off[t] = static_cast<uint32_t>(pl->h_work.size() / 2);
         for (uint32_t ty = 0; ty < pl->tiles_y; ++ty)
@@ -1120,6 +1228,9 @@ pp_status pp_se2_launch_fast(pp_handle h, uint32_t x0, uint32_t y0, uint32_t x1,
                     need += (pl->list_len[(t + n) * 4 + c] + 3u) & ~3u;
             if (words + need > MAX_LIST_WORDS)
                 break;
+            args.xsplit[n] = pl->xsplit[t + n];
+            args.ysplit[n] = pl->ysplit[t + n];
+            args.split_left[n] = pl->split_left[t + n];
             for (int c = 0; c < 4; ++c)
             {
                 const uint32_t len = pl->list_len[(t + n) * 4 + c], id = pl->list_id[(t + n) * 4 + c];
