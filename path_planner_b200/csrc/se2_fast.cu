@@ -68,7 +68,10 @@ constexpr int MAX_LIST_WORDS = 6400;
 constexpr int MAX_R = 15;
 constexpr int MIN_HALO = 7;
 constexpr size_t SMEM_LIMIT = (227 * 1024 - 2048) / CTAS_PER_SM;  // per CTA; 1 KB per CTA is reserved by the system
-constexpr size_t STAGE_BYTES = static_cast<size_t>(PP_FT_THREADS / 32) * 8 * 128 + 128;  // per-warp 8 x 128-byte store blocks (+ alignment)
+#ifndef PP_QPT
+#define PP_QPT 16
+#endif
+constexpr size_t STAGE_BYTES = static_cast<size_t>(PP_FT_THREADS / 32) * PP_QPT * 128 + 128;  // per-warp QPT x 128-byte store blocks (+ alignment)
 
 // A brick library: table 0 is the costmap itself (the one-point brick); table k > 0 is
 // T_k = max(T_a, T_b shifted by (du, dv)), a and b earlier tables. Listed in dependency-level order.
@@ -120,9 +123,9 @@ __device__ __forceinline__ uint32_t bytemax4(uint32_t a, uint32_t b)
     return __byte_perm(even, odd, 0x7351);
 }
 
-constexpr int QPT = 8;                       // rows per thread and work unit
-constexpr int UNITS_PER_BIN = FT_H / QPT;    // a work unit is 8 rows x 128 columns of one bin of a tile: one warp, lane = word column
-static_assert(UNITS_PER_BIN * QPT == FT_H, "tile height must be a multiple of 8");
+constexpr int QPT = PP_QPT;                  // rows per thread and work unit
+constexpr int UNITS_PER_BIN = FT_H / QPT;    // a work unit is QPT rows x 128 columns of one bin of a tile: one warp, lane = word column
+static_assert(UNITS_PER_BIN * QPT == FT_H && QPT % 8 == 0, "tile height must be a multiple of the unit height, that of 8");
 
 template <int PW>
 __device__ __forceinline__ void load_pair(const uint8_t *smb, uint32_t d1, uint32_t d2, uint32_t (&u)[QPT], uint32_t (&v)[QPT])
@@ -154,8 +157,7 @@ __device__ __forceinline__ void accumulate(uint32_t (&odd)[QPT], uint32_t (&even
 __device__ __noinline__ void store_mixed(const FastArgs &a, uint32_t cls, uint32_t t, uint32_t lc, int gx, int gy, uint32_t r0, uint32_t r1,
                                          uint32_t r2, uint32_t r3, uint32_t r4, uint32_t r5, uint32_t r6, uint32_t r7)
 {
-    const uint32_t res[QPT] = {r0, r1, r2, r3, r4, r5, r6, r7};
-    static_assert(QPT == 8, "store_mixed takes the 8 rows of a unit");
+    const uint32_t res[8] = {r0, r1, r2, r3, r4, r5, r6, r7};
     const int W = static_cast<int>(a.W), H = static_cast<int>(a.H);
     const uint32_t mcx = cls % 3u, mcy = cls / 3u;
     const int xsplit = a.xsplit[t], ysplit = a.ysplit[t];
@@ -169,7 +171,7 @@ __device__ __noinline__ void store_mixed(const FastArgs &a, uint32_t cls, uint32
         return;
     uint8_t *base = a.vol + static_cast<size_t>(a.W) * a.H * (a.t_first + t) + gx;
 #pragma unroll
-    for (int j = 0; j < QPT; ++j)
+    for (int j = 0; j < 8; ++j)
     {
         const int y = gy + j;
         if (y >= H || (mcy == 2 && ((y < ysplit) ? yleft : 1u - yleft) != (lc & 1u)))
@@ -188,7 +190,7 @@ __device__ __noinline__ void store_mixed(const FastArgs &a, uint32_t cls, uint32
     }
 }
 
-// Output phase. A work unit is 8 rows of one evaluating bin: one warp, lane q owns the cells q, q+32, q+64,
+// Output phase. A work unit is QPT rows of one evaluating bin: one warp, lane q owns the cells q, q+32, q+64,
 // q+96 of each row. Warps fetch units from a shared counter, so bins with long and short sample lists
 // balance out. The loads of the next sample pair are issued before the max operations of the current one
 // (software pipelining by hand). The result is transposed across groups of four lanes, so that lane 4g+i
@@ -286,7 +288,10 @@ __device__ __forceinline__ void run_units(const FastArgs &a, const uint32_t *sm,
         }
         if (lcm & LEAD_MIXED)
         {
-            store_mixed(a, s_cls[t] - CLS_MIXED0, t, lc, gx, gy, res[0], res[1], res[2], res[3], res[4], res[5], res[6], res[7]);
+#pragma unroll
+            for (int g = 0; g < QPT; g += 8)
+                store_mixed(a, s_cls[t] - CLS_MIXED0, t, lc, gx, gy + g, res[g], res[g + 1], res[g + 2], res[g + 3], res[g + 4], res[g + 5],
+                            res[g + 6], res[g + 7]);
             continue;
         }
         uint32_t link = a.chain_next[t][lc];
@@ -514,7 +519,7 @@ __global__ void __launch_bounds__(FT_THREADS, CTAS_PER_SM) se2_fast_kernel(const
     }
     __syncthreads();  // also orders s_lead / s_nlead when no table beyond the costmap is built
 
-    // output phase: warps fetch (evaluating bin, 8 rows) units until none are left
+    // output phase: warps fetch (evaluating bin, QPT rows) units until none are left
     // per-warp staging blocks of the bulk stores sit behind the tables, 128-byte aligned
     uint32_t *stage = tb + ((a.n_tables * CW + 31) & ~31) + warp * (QPT * 32);
     run_units<PW>(a, tb, s_cls, s_lead, s_lead_lc, s_nlead, &s_next, lane, tx0, ty0, stage);
