@@ -151,6 +151,16 @@ __device__ __forceinline__ void accumulate(uint32_t (&odd)[QPT], uint32_t (&even
     }
 }
 
+__device__ __forceinline__ void start(uint32_t (&odd)[QPT], uint32_t (&even)[QPT], const uint32_t (&u)[QPT], const uint32_t (&v)[QPT])
+{
+#pragma unroll
+    for (int j = 0; j < QPT; ++j)
+    {
+        odd[j] = __vmaxu2(u[j], v[j]);
+        even[j] = __vmaxu2(u[j] * 256u, v[j] * 256u);
+    }
+}
+
 // A range boundary of a bin crosses the tile ("mixed" tile): an evaluation with the offset set of one class pair
 // is valid for the columns / rows of those classes only. Rare (the boundaries sit in the first tiles of a few
 // bins), so this is an out-of-line call with plain stores: whole words where all four columns are in, bytes else.
@@ -215,7 +225,7 @@ __device__ __forceinline__ void run_units(const FastArgs &a, const uint32_t *sm,
     const bool tile_inside = tx0 + FT_W <= W && ty0 + FT_H <= H;
     // lane roles of the two transpose steps
     const bool odd_lane = lane & 1, upper_lane = lane & 2;
-    const uint32_t sel1 = odd_lane ? 0x3715u : 0x7351u;
+    const uint32_t sel1 = odd_lane ? 0x3715u : 0x6240u;
     const uint32_t sel2 = upper_lane ? 0x3276u : 0x5410u;
     while (true)
     {
@@ -236,32 +246,45 @@ __device__ __forceinline__ void run_units(const FastArgs &a, const uint32_t *sm,
         const uint32_t n_samples = a.list_len[t][lc];  // >= 1
         const uint32_t len = n_samples & ~1u;           // samples consumed in pairs
         uint32_t odd[QPT], even[QPT];
-#pragma unroll
-        for (int j = 0; j < QPT; ++j)
-            odd[j] = even[j] = 0;
         uint32_t ua[QPT], va[QPT], ub[QPT], vb[QPT];
         if (len)
         {
             load_pair<PW>(smb, list[0], list[1], ua, va);
             uint32_t i = 2;
-#pragma unroll 1
-            for (; i + 2 < len; i += 4)
-            {
-                load_pair<PW>(smb, list[i], list[i + 1], ub, vb);
-                accumulate(odd, even, ua, va);
-                load_pair<PW>(smb, list[i + 2], list[i + 3], ua, va);
-                accumulate(odd, even, ub, vb);
-            }
             if (i < len)
             {
-                load_pair<PW>(smb, list[i], list[i + 1], ub, vb);
-                accumulate(odd, even, ua, va);
-                accumulate(odd, even, ub, vb);
+                load_pair<PW>(smb, list[2], list[3], ub, vb);
+                start(odd, even, ua, va);  // the accumulators start from the first pair
+                i = 4;
+#pragma unroll 1
+                for (; i + 2 < len; i += 4)
+                {
+                    load_pair<PW>(smb, list[i], list[i + 1], ua, va);
+                    accumulate(odd, even, ub, vb);
+                    load_pair<PW>(smb, list[i + 2], list[i + 3], ub, vb);
+                    accumulate(odd, even, ua, va);
+                }
+                if (i < len)
+                {
+                    load_pair<PW>(smb, list[i], list[i + 1], ua, va);
+                    accumulate(odd, even, ub, vb);
+                    accumulate(odd, even, ua, va);
+                }
+                else
+                {
+                    accumulate(odd, even, ub, vb);
+                }
             }
             else
             {
-                accumulate(odd, even, ua, va);
+                start(odd, even, ua, va);
             }
+        }
+        else
+        {
+#pragma unroll
+            for (int j = 0; j < QPT; ++j)
+                odd[j] = even[j] = 0;
         }
         if (n_samples & 1u)  // the last sample of an odd list: one load, used for both operands
         {
@@ -271,18 +294,17 @@ __device__ __forceinline__ void run_units(const FastArgs &a, const uint32_t *sm,
                 ua[j] = p1[j * PW];
             accumulate(odd, even, ua, ua);
         }
-        // 4x4 byte transpose across lanes 4g .. 4g+3. The valid bytes are the high bytes of the 16-bit
-        // halves: odd = (., b1, ., b3), even = (., b0, ., b2), b_i = the lane's cell q + 32 i.
+        // 4x4 byte transpose across lanes 4g .. 4g+3. The valid bytes are the high bytes of the 16-bit halves
+        // (odd = (., b1, ., b3), even = (., b0, ., b2), b_i = the lane's cell q + 32 i); they are merged first.
         // Step 1 (lane ^ 1): even lanes collect (b0, b2) of both lanes, odd lanes (b1, b3).
         // Step 2 (lane ^ 2): lower lanes collect bytes 0..1 of both, upper lanes bytes 2..3.
         uint32_t res[QPT];
 #pragma unroll
         for (int j = 0; j < QPT; ++j)
         {
-            const uint32_t keep = odd_lane ? odd[j] : even[j];
-            const uint32_t give = odd_lane ? even[j] : odd[j];
-            const uint32_t got = __shfl_xor_sync(0xffffffffu, give, 1);
-            const uint32_t p = __byte_perm(keep, got, sel1);
+            const uint32_t m = __byte_perm(even[j], odd[j], 0x7351);
+            const uint32_t got = __shfl_xor_sync(0xffffffffu, m, 1);
+            const uint32_t p = __byte_perm(m, got, sel1);
             const uint32_t got2 = __shfl_xor_sync(0xffffffffu, p, 2);
             res[j] = __byte_perm(p, got2, sel2);
         }
@@ -417,19 +439,36 @@ __global__ void __launch_bounds__(FT_THREADS, CTAS_PER_SM) se2_fast_kernel(const
     // before the first use; zeros outside the map (the identity of max: the reference ignores such samples).
     const int x0 = tx0 - HALO;
     uint32_t cell[ROW_ITERS][5];
-#pragma unroll
-    for (int j = 0; j < ROW_ITERS; ++j)
+    if (x0 >= 0 && x0 + FT_W + 2 * HALO <= W && ty0 >= HALO && ty0 + FT_H + HALO <= H)
     {
-        const int r = warp + j * NWARPS;
-        const int gy = ty0 - HALO + r;
-        const bool row_ok = r < G::ROWS && gy >= 0 && gy < H;
-        const uint8_t *rowp = a.cost + static_cast<size_t>(row_ok ? gy : 0) * a.W;
+        // the tile and its halo lie inside the map: no bounds tests
+        const uint8_t *p0 = a.cost + static_cast<size_t>(ty0 - HALO + warp) * a.W + (x0 + lane);
 #pragma unroll
-        for (int i = 0; i < 5; ++i)
+        for (int j = 0; j < ROW_ITERS; ++j)
         {
-            const int gxi = x0 + lane + 32 * i;
-            const bool ok = row_ok && gxi >= 0 && gxi < W && (i < 4 || lane < 2 * HALO);
-            cell[j][i] = ok ? static_cast<uint32_t>(__ldg(rowp + gxi)) : 0u;
+            const uint8_t *rowp = p0 + static_cast<size_t>(j * NWARPS) * a.W;
+            const bool row_ok = warp + j * NWARPS < G::ROWS;
+#pragma unroll
+            for (int i = 0; i < 5; ++i)
+                cell[j][i] = (row_ok && (i < 4 || lane < 2 * HALO)) ? static_cast<uint32_t>(__ldg(rowp + 32 * i)) : 0u;
+        }
+    }
+    else
+    {
+#pragma unroll
+        for (int j = 0; j < ROW_ITERS; ++j)
+        {
+            const int r = warp + j * NWARPS;
+            const int gy = ty0 - HALO + r;
+            const bool row_ok = r < G::ROWS && gy >= 0 && gy < H;
+            const uint8_t *rowp = a.cost + static_cast<size_t>(row_ok ? gy : 0) * a.W;
+#pragma unroll
+            for (int i = 0; i < 5; ++i)
+            {
+                const int gxi = x0 + lane + 32 * i;
+                const bool ok = row_ok && gxi >= 0 && gxi < W && (i < 4 || lane < 2 * HALO);
+                cell[j][i] = ok ? static_cast<uint32_t>(__ldg(rowp + gxi)) : 0u;
+            }
         }
     }
     static_assert(MAX_T_PER_LAUNCH <= FT_THREADS, "one bin class per thread");
