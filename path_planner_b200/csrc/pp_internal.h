@@ -71,7 +71,9 @@ struct pp_ctx
     double *d_pts = nullptr;
     size_t pts_cap = 0;
     uint32_t n_pts = 0;
-    uint32_t *d_col_counts = nullptr;
+    uint32_t *d_col_counts = nullptr;  // exclusive prefix of the points per costmap column (pp_obstacles_extract)
+    uint32_t pts_cols = 0;             // > 0: d_pts is column-ordered over this many columns ...
+    double pts_col_origin = 0.0, pts_col_res = 0.0;  // ... with centres at origin + (c + 0.5) * res
     size_t col_cap = 0;
     double *d_queries = nullptr;
     size_t q_cap = 0;

@@ -14,6 +14,7 @@
 //      than the scan it saves; the kernel is launch-latency bound.
 #include "pp_internal.h"
 
+#include <cstdlib>
 #include <cstring>
 
 #include <cmath>
@@ -136,10 +137,16 @@ struct Key
 };
 __device__ __forceinline__ bool key_less(const Key &a, const Key &b) { return a.d2 < b.d2 || (a.d2 == b.d2 && a.idx < b.idx); }
 
+// col_prefix (optional): the points are those of pp_obstacles_extract, ordered by costmap column, and
+// col_prefix[c] is the index of the first point of column c (col_prefix[n_cols] = N). A query then scans only
+// the columns whose centres can lie within sqrt(radius_arg) of it in x (one column of slack either side, so
+// the exact d2 test below still decides every hit: results are unchanged).
 __global__ void __launch_bounds__(RK_THREADS) radius_topk_kernel(const double *__restrict__ pts, uint32_t N,
                                                                  const double *__restrict__ queries, double radius_arg,
                                                                  uint32_t K, uint32_t *__restrict__ idx_out,
-                                                                 double *__restrict__ d2_out, uint32_t *__restrict__ cnt_out)
+                                                                 double *__restrict__ d2_out, uint32_t *__restrict__ cnt_out,
+                                                                 const uint32_t *__restrict__ col_prefix, uint32_t n_cols,
+                                                                 double col_origin, double col_res)
 {
     __shared__ unsigned long long s_d2[RK_CAP + RK_MAXK];
     __shared__ uint32_t s_idx[RK_CAP + RK_MAXK];
@@ -157,6 +164,17 @@ __global__ void __launch_bounds__(RK_THREADS) radius_topk_kernel(const double *_
         s_nbest = 0;
     }
     __syncthreads();
+    uint32_t n_lo = 0, n_hi = N;
+    if (col_prefix)
+    {
+        const double r = sqrt(fmax(radius_arg, 0.0));
+        // column c has its centre at col_origin + (c + 0.5) * col_res
+        const double c_lo = floor((qx - r - col_origin) / col_res - 0.5) - 1.0, c_hi = ceil((qx + r - col_origin) / col_res - 0.5) + 1.0;
+        const uint32_t lo = c_lo <= 0.0 ? 0u : (c_lo >= static_cast<double>(n_cols) ? n_cols : static_cast<uint32_t>(c_lo));
+        const uint32_t hi = c_hi < 0.0 ? 0u : (c_hi + 1.0 >= static_cast<double>(n_cols) ? n_cols : static_cast<uint32_t>(c_hi) + 1u);
+        n_lo = col_prefix[lo];
+        n_hi = hi > lo ? col_prefix[hi] : n_lo;
+    }
 
     const unsigned long long EMPTY = 0xFFFFFFFFFFFFFFFFull;
     // reduce the buffered hits (plus the incumbents) to the K smallest, ascending
@@ -219,9 +237,14 @@ __global__ void __launch_bounds__(RK_THREADS) radius_topk_kernel(const double *_
         __syncthreads();
     };
 
-    for (uint32_t base = 0; base < N; base += RK_BATCH * RK_THREADS)
+    // `reduce` is uniform by construction: thread 0 publishes it through the barrier that ends an iteration. It reads
+    // the counter before that barrier, so hits of the same iteration that other warps have not added yet may be
+    // missing: the threshold leaves room for them (one batch) and for the next iteration (another batch).
+    static_assert(RK_CAP >= 3 * RK_BATCH * RK_THREADS, "buffer holds the carried hits and two batches");
+    int reduce = 0;
+    for (uint32_t base = n_lo; base < n_hi; base += RK_BATCH * RK_THREADS)
     {
-        if (s_count + RK_BATCH * RK_THREADS > RK_CAP)  // uniform across the block (read after a barrier)
+        if (reduce)
             select_best();
         // RK_BATCH points per thread between two barriers, all loads issued first
         double px[RK_BATCH], py[RK_BATCH];
@@ -229,8 +252,8 @@ __global__ void __launch_bounds__(RK_THREADS) radius_topk_kernel(const double *_
         for (int b = 0; b < RK_BATCH; ++b)
         {
             const uint32_t i = base + b * RK_THREADS + tid;
-            px[b] = i < N ? pts[2 * static_cast<size_t>(i)] : 0.0;
-            py[b] = i < N ? pts[2 * static_cast<size_t>(i) + 1] : 0.0;
+            px[b] = i < n_hi ? pts[2 * static_cast<size_t>(i)] : 0.0;
+            py[b] = i < n_hi ? pts[2 * static_cast<size_t>(i) + 1] : 0.0;
         }
 #pragma unroll
         for (int b = 0; b < RK_BATCH; ++b)
@@ -242,7 +265,7 @@ __global__ void __launch_bounds__(RK_THREADS) radius_topk_kernel(const double *_
             d2 = __dadd_rn(d2, __dmul_rn(dx, dx));
             const double dy = __dsub_rn(qy, py[b]);
             d2 = __dadd_rn(d2, __dmul_rn(dy, dy));
-            const bool hit = i < N && d2 < radius_arg;
+            const bool hit = i < n_hi && d2 < radius_arg;
             const unsigned ballot = __ballot_sync(0xffffffffu, hit);
             uint32_t warp_base = 0;
             if (lane == 0 && ballot)
@@ -255,7 +278,7 @@ __global__ void __launch_bounds__(RK_THREADS) radius_topk_kernel(const double *_
                 s_idx[slot] = i;
             }
         }
-        __syncthreads();
+        reduce = __syncthreads_or(tid == 0 && s_count + 2 * RK_BATCH * RK_THREADS > RK_CAP);
     }
     select_best();
     const uint32_t n = s_nbest;
@@ -307,6 +330,10 @@ pp_status pp_obstacles_extract(pp_handle h, double resolution, double origin_x, 
     h->launches++;
     PP_CUDA(h, cudaGetLastError());
     h->n_pts = total;
+    // the points are ordered by column: pp_radius_topk prunes with the column prefix
+    h->pts_cols = h->W;
+    h->pts_col_origin = origin_x;
+    h->pts_col_res = resolution;
     *n_out = total;
     if (pts_out && max_points)
         PP_CUDA(h, cudaMemcpyAsync(pts_out, h->d_pts, sizeof(double) * 2 * std::min(total, max_points), cudaMemcpyDeviceToHost, h->stream));
@@ -330,6 +357,7 @@ pp_status pp_radius_topk(pp_handle h, const double *pts_xy, uint32_t N, const do
         PP_CUDA(h, pp_reserve(h->d_pts, h->pts_cap, 2 * static_cast<size_t>(std::max(N, 1u))));
         PP_CUDA(h, cudaMemcpyAsync(h->d_pts, pts_xy, sizeof(double) * 2 * N, cudaMemcpyHostToDevice, h->stream));
         h->n_pts = N;
+        h->pts_cols = 0;  // caller-supplied points have no column order
         d_pts = h->d_pts;
     }
     else
@@ -366,8 +394,10 @@ pp_status pp_radius_topk(pp_handle h, const double *pts_xy, uint32_t N, const do
         h->teb_host_cap = d2_bytes + idx_bytes + cnt_bytes;
     }
     PP_CUDA(h, cudaMemcpyAsync(h->d_queries, queries_xy, sizeof(double) * 2 * Q, cudaMemcpyHostToDevice, h->stream));
+    const bool prune = h->pts_cols > 0 && h->pts_col_res > 0.0 && getenv("PP_TEB_NO_PRUNE") == nullptr;
     radius_topk_kernel<<<Q, RK_THREADS, 0, h->stream>>>(d_pts, N, h->d_queries, radius_arg, K, h->d_topk_idx, h->d_topk_d2,
-                                                        h->d_topk_cnt);
+                                                        h->d_topk_cnt, prune ? h->d_col_counts : nullptr, h->pts_cols,
+                                                        h->pts_col_origin, h->pts_col_res);
     h->launches++;
     PP_CUDA(h, cudaGetLastError());
     h->topk_Q = Q;

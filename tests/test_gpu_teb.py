@@ -83,3 +83,38 @@ def test_empty_extraction(handle):
     assert pts.shape == (0, 2)
     idx, d2, cnt = handle.radius_topk(None, np.zeros((4, 2)), 0.9574, 10)
     assert (cnt == 0).all()
+
+
+@pytest.mark.parametrize("n_in", [3500, 9000])
+def test_dense_cluster_many_hits_per_query(handle, port, n_in):
+    """More hits inside the radius than the kernel buffers between two reductions (several reduction passes per
+    query, hits arriving from every warp): the keep-first-K result must not depend on the buffering."""
+    rng = np.random.default_rng(n_in)
+    ang, rad = rng.uniform(0, 2 * np.pi, n_in), 0.9 * np.sqrt(rng.uniform(0, 1, n_in))
+    cluster = np.stack([1.0 + rad * np.cos(ang), -2.0 + rad * np.sin(ang)], 1)
+    far = rng.uniform(-50, 50, (2000, 2))
+    pts = np.ascontiguousarray(rng.permutation(np.concatenate([cluster, far])))
+    q = np.array([[1.0, -2.0], [1.3, -2.2], [30.0, 30.0], [0.2, -1.9]])
+    for K in (10, 64):
+        got = handle.radius_topk(pts, q, 0.9574, K)
+        want = port.radius_topk(pts, q, 0.9574, K)
+        assert_topk_equal(got, want)
+    assert port.radius_topk(pts, q, 0.9574, 1)[3][0] > 3072  # `found` of the first query: above the kernel's buffer
+
+
+@pytest.mark.parametrize("origin", [(0.0, 0.0), (-7.3, 2.1)])
+def test_column_pruned_query_equals_unpruned(handle, port, origin):
+    """Points left on the device by the extraction are column-ordered; queries scan only the columns in reach.
+    Same result as the full scan, for poses inside, at the edges of and outside the map."""
+    cost = make_costmap(300, 220, seed=21, coverage=0.15)
+    cost[:, 0] = 254  # obstacles in the first and the last column
+    cost[:, -1] = 254
+    handle.costmap_upload(cost)
+    pose = (origin[0] + 7.0, origin[1] + 5.0, 0.4)
+    pts = handle.obstacles_extract(0.05, origin, pose, 100.0, 0.0)
+    assert len(pts) > 5000
+    rng = np.random.default_rng(3)
+    q = np.concatenate([rng.uniform(-1.0, 16.0, (60, 2)) + np.array(origin), np.array([[0.0, 5.0], [15.0, 5.0], [-30.0, 0.0], [40.0, 3.0]]) + np.array(origin)])
+    for r in (0.9574, 0.01, 30.0):
+        got = handle.radius_topk(None, q, r, 10)
+        assert_topk_equal(got, port.radius_topk(pts, q, r, 10))
