@@ -159,8 +159,11 @@ pp_status pp_heuristic_stats(pp_handle h, uint32_t *rounds, uint64_t *tile_visit
  *   limit    ceil(W/32) * ceil(H/32) <= 16384 tiles (e.g. 4096 x 4096); larger maps are refused
  *            with PP_ERR_RANGE and a message on stderr
  *   device   the CUDA device that is current in the calling thread
- *   set-up   the first call on each device looks up the array's device address; make that call
- *            before any stream capture on that device
+ *   set-up   the first call on each device looks up the array's device address (and, like any first
+ *            use of this library on a device, makes the CUDA runtime load the library's kernels, which
+ *            the driver may serve with allocations of its own): make one warm-up call per device during
+ *            start-up, before the real-time phase and before any stream capture on that device. First
+ *            calls from several threads at once are safe (they store the same address)
  *   sharing  one array per device, cleared at the start of every call; calls whose GPU work
  *            overlaps race on it, so serialise them. Returns after the field is complete. */
 pp_status pp_heuristic_build_noalloc(const uint8_t *d_cost, uint32_t W, uint32_t H, uint32_t goal_x, uint32_t goal_y,
@@ -174,7 +177,8 @@ pp_status pp_heuristic_build_noalloc(const uint8_t *d_cost, uint32_t W, uint32_t
  * The parameters are SearchInfo's (planner/commons.h:26-48; defaults config/params.yaml:32-45).
  * Poses are (x [m], y [m], yaw [rad]) in the map frame; the path comes back goal -> start, like the
  * reference's before path_planner_ros.cpp:140 reverses it. *found_out is 0 when the search fails
- * (that is a result, not an error). Needs an uploaded costmap and a footprint.
+ * (that is a result, not an error). *n_points_out is the length of the whole path; at most max_points
+ * poses are written, so a larger value means the output was truncated. Needs an uploaded costmap and a footprint.
  * Footprint checks use the pose's cell centre and nearest heading bin. */
 typedef struct pp_plan_params
 {

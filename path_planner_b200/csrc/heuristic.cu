@@ -15,6 +15,7 @@
 #include "pp_internal.h"
 
 #include <algorithm>
+#include <atomic>
 #include <cmath>
 #include <cstdlib>
 #include <limits>
@@ -324,10 +325,30 @@ float heur_delta()
 {
     static const float d = [] {
         const char *e = getenv("PP_HEUR_DELTA");  // tuning knob for experiments
-        return e ? static_cast<float>(atof(e)) : 96.0f;
+        const float v = e ? static_cast<float>(atof(e)) : 96.0f;
+        return (v >= 0.0f && v <= 1e30f) ? v : 96.0f;  // a negative or NaN width would leave every bucket empty
     }();
     return d;
 }
+
+// travel-cost table (2 x 256: straight, diagonal) with the reference's float expression and evaluation
+// order (astar_hybrid.cpp:151); entering a cell with cost >= 253 is impossible (:143-145)
+void fill_travel_table(float cost_penalty, float (&travel)[512])
+{
+    const float sqrt_2 = sqrtf(2.0f);
+    for (int c = 0; c < 256; ++c)
+    {
+        const float cost = static_cast<float>(c);
+        const float scale = 1.0f + (cost_penalty * cost / 252.0f);
+        travel[c] = c >= PP_COST_INSCRIBED ? std::numeric_limits<float>::infinity() : 1.0f * scale;
+        travel[256 + c] = c >= PP_COST_INSCRIBED ? std::numeric_limits<float>::infinity() : sqrt_2 * scale;
+    }
+}
+
+// Guard against a schedule that stops making progress. A round that has active tiles lowers at least one
+// cell, and the values along any shortest path are fixed one 32-cell tile (or at worst a few cells of a
+// serpentine corridor) per round, so W*H/8 rounds are out of reach of every map; typical: a few hundred.
+uint64_t heur_max_rounds(size_t n_cells) { return n_cells / 8 + 1024; }
 }  // namespace
 
 extern "C" {
@@ -348,16 +369,8 @@ pp_status pp_heuristic_build(pp_handle h, uint32_t goal_x, uint32_t goal_y, floa
     size_t travel_cap = h->d_travel ? 512 : 0;
     PP_CUDA(h, pp_reserve(h->d_travel, travel_cap, static_cast<size_t>(512)));
 
-    // travel-cost table with the reference's float expression and evaluation order (:151)
     float travel[512];
-    const float sqrt_2 = sqrtf(2.0f);
-    for (int c = 0; c < 256; ++c)
-    {
-        const float cost = static_cast<float>(c);
-        const float scale = 1.0f + (cost_penalty * cost / 252.0f);
-        travel[c] = c >= PP_COST_INSCRIBED ? std::numeric_limits<float>::infinity() : 1.0f * scale;
-        travel[256 + c] = c >= PP_COST_INSCRIBED ? std::numeric_limits<float>::infinity() : sqrt_2 * scale;
-    }
+    fill_travel_table(cost_penalty, travel);
     PP_CUDA(h, cudaMemcpyAsync(h->d_travel, travel, sizeof(travel), cudaMemcpyHostToDevice, h->stream));
     PP_CUDA(h, cudaStreamSynchronize(h->stream));  // `travel` lives on this stack frame
 
@@ -369,9 +382,7 @@ pp_status pp_heuristic_build(pp_handle h, uint32_t goal_x, uint32_t goal_y, floa
 
     h->heur_rounds = 0;
     h->heur_tile_visits = 0;
-    // every round moves information across at least one tile border, and a shortest path visits a
-    // cell at most once, so W*H rounds is a (very loose) hard bound
-    const uint64_t max_rounds = 4 * static_cast<uint64_t>(n) + 64;  // loose: every round moves some value forward
+    const uint64_t max_rounds = heur_max_rounds(n);
     uint32_t round = 0;
     bool done = false;
     while (!done)
@@ -471,7 +482,7 @@ constexpr int NOALLOC_MAX_DEVICES = 64;
 
 static __device__ __align__(256) uint32_t g_noalloc_scratch[NOALLOC_WORDS];
 
-uint32_t *g_noalloc_addr[NOALLOC_MAX_DEVICES] = {};  // device address of the array, per device ordinal
+std::atomic<uint32_t *> g_noalloc_addr[NOALLOC_MAX_DEVICES] = {};  // device address of the array, per device ordinal
 }  // namespace
 
 extern "C" pp_status pp_heuristic_build_noalloc(const uint8_t *d_cost, uint32_t W, uint32_t H, uint32_t goal_x,
@@ -498,7 +509,7 @@ extern "C" pp_status pp_heuristic_build_noalloc(const uint8_t *d_cost, uint32_t 
         return pp_fail(nullptr, PP_ERR_CUDA, "pp_heuristic_build_noalloc: cudaGetDevice: %s", cudaGetErrorString(e));
     if (dev < 0 || dev >= NOALLOC_MAX_DEVICES)
         return pp_fail(nullptr, PP_ERR_RANGE, "pp_heuristic_build_noalloc: device ordinal %d not supported", dev);
-    if (!g_noalloc_addr[dev])
+    if (!g_noalloc_addr[dev].load(std::memory_order_acquire))
     {
         // once per device, with that device current: turn the host-side stand-in into the address
         // the kernels can dereference
@@ -506,20 +517,13 @@ extern "C" pp_status pp_heuristic_build_noalloc(const uint8_t *d_cost, uint32_t 
         e = cudaGetSymbolAddress(reinterpret_cast<void **>(&p), g_noalloc_scratch);
         if (e != cudaSuccess || !p)
             return pp_fail(nullptr, PP_ERR_CUDA, "pp_heuristic_build_noalloc: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
-        g_noalloc_addr[dev] = p;
+        g_noalloc_addr[dev].store(p, std::memory_order_release);  // two first calls racing store the same address
     }
-    uint32_t *flags = g_noalloc_addr[dev];
+    uint32_t *flags = g_noalloc_addr[dev].load(std::memory_order_acquire);
     float *travel_dev = reinterpret_cast<float *>(flags + NOALLOC_FLAG_WORDS);
 
     float travel[512];
-    const float sqrt_2 = sqrtf(2.0f);
-    for (int c = 0; c < 256; ++c)
-    {
-        const float cost = static_cast<float>(c);
-        const float scale = 1.0f + (cost_penalty * cost / 252.0f);
-        travel[c] = c >= PP_COST_INSCRIBED ? std::numeric_limits<float>::infinity() : 1.0f * scale;
-        travel[256 + c] = c >= PP_COST_INSCRIBED ? std::numeric_limits<float>::infinity() : sqrt_2 * scale;
-    }
+    fill_travel_table(cost_penalty, travel);
     e = cudaMemcpyAsync(travel_dev, travel, sizeof(travel), cudaMemcpyHostToDevice, stream);
     if (e == cudaSuccess)
         e = cudaStreamSynchronize(stream);  // `travel` is on this stack frame
@@ -534,7 +538,7 @@ extern "C" pp_status pp_heuristic_build_noalloc(const uint8_t *d_cost, uint32_t 
     heur_init_kernel<<<148 * 8, 256, 0, stream>>>(d_field_out, n, flags, n_flags, goal_index, goal_tile);
     uint32_t round = 0;
     uint32_t counters[N_COUNTERS];
-    const uint64_t max_rounds = 4 * static_cast<uint64_t>(n) + 64;
+    const uint64_t max_rounds = heur_max_rounds(n);
     for (;;)
     {
         for (int k = 0; k < ROUNDS_PER_CHECK; ++k, ++round)

@@ -125,6 +125,11 @@ bool B200GlobalPlanner::makePlan(const geometry_msgs::PoseStamped &start, const 
         ROS_WARN("[B200GlobalPlanner] No path found");
         return false;
     }
+    if (n > max_points)  // pp_plan reports the full length and writes at most max_points poses
+    {
+        ROS_ERROR("[B200GlobalPlanner] path of %u poses does not fit the %u-pose buffer", n, max_points);
+        return false;
+    }
     // the search returns goal -> start; the reference reverses it (path_planner_ros.cpp:140)
     const ros::Time stamp = ros::Time::now();
     plan.reserve(n);
