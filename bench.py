@@ -362,10 +362,76 @@ def main():
         gathered["theta_sharded_fused_push"] = {"value": cells_per_s(ms), "unit": UNIT, "ms_per_step": ms,
                                                 "how": "slab build kernels store every output word to all ranks' volumes; no separate collective"}
         h.se2_volume_set_push(False)
+        # pairs of bins (u, u + n/2) dealt out in runs, the exchange of part k hidden behind the build of part
+        # k + 1 (pp_se2_volume_build_sharded); next to it the exchange alone on the same volume, so that what is
+        # reported is the cost of the link and how much of the build hides behind it
+        import zlib
+        recv_bytes = int(W * H * (N_THETA - per))
+        for key, push in (("theta_pairs_pipelined_nccl", False), ("theta_pairs_pipelined_push", True)):
+            best = None
+            for chunks in (1, 2, 3, 4):
+                def sharded_step():
+                    h.se2_volume_build_sharded(N_THETA, chunks, push=push)
+                for _ in range(3):
+                    sharded_step()
+                h.sync()
+                ms, _ = timed(sharded_step, args.steps)
+                if best is None or ms < best[0]:
+                    best = (ms, chunks)
+            chunks = best[1]
+
+            def exchange_only():
+                h.se2_volume_build_sharded(N_THETA, chunks, push=push, exchange_only=True)
+            ms_x, _ = timed(exchange_only, args.steps)
+            h.se2_volume_build_sharded(N_THETA, chunks, push=push)
+            h.sync()
+            gathered[key] = {"value": cells_per_s(best[0]), "unit": UNIT, "ms_per_step": best[0], "chunks": chunks,
+                             "exchange_alone_ms": ms_x, "ratio_to_exchange_alone": best[0] / ms_x,
+                             "bytes_received_per_gpu": recv_bytes, "inbound_GBps": recv_bytes / (best[0] * 1e-3) / 1e9,
+                             "how": ("copy engines into the peers' mapped volumes + one-word all-reduce" if push else
+                                     "one group of ncclBroadcast calls per part (2 per owner)")}
+        # plain ncclAllGather of equal slabs on an already built volume, for reference
+        h.se2_volume_build(N_THETA, 0.5, 0.5, 0.0, t0, t1)
+        ms, _ = timed(h.se2_volume_allgather, args.steps)
+        gathered["allgather_alone"] = {"ms_per_step": ms, "inbound_GBps": recv_bytes / (ms * 1e-3) / 1e9,
+                                       "collective": "ncclAllGather of heading slabs, in place, nothing built"}
+        # every rank checks what it now holds against a volume built on ONE GPU (rank 0's CRC-32 per heading bin):
+        # the driver's GPU test box has a single GPU, so this is where the multi-GPU bytes are verified
+        h.se2_volume_build_sharded(N_THETA, 3, push=False)
+        h.sync()
+        mine = [zlib.crc32(h.se2_volume_download(t, t + 1).tobytes()) for t in range(N_THETA)]
+        h.se2_volume_build(N_THETA)
+        h.sync()
+        single = [zlib.crc32(h.se2_volume_download(t, t + 1).tobytes()) for t in range(N_THETA)]
+        ref_crc = [single if rank == 0 else None]
+        dist.broadcast_object_list(ref_crc, src=0)
+        ok = torch.tensor([int(mine == ref_crc[0] and single == ref_crc[0])], device="cuda")
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        gathered["verified"] = {"sharded_volume_equals_single_gpu_build_on_every_rank": bool(ok.item()),
+                                "how": "CRC-32 per heading bin against rank 0's single-GPU build"}
         h.se2_volume_set_rows(y0, y1)
         for _ in range(4):  # back to the primary configuration (its plan may have been replaced above)
             step()
         h.sync()
+        # the row bands are verified the same way: this rank's band of every bin against rank 0's whole volume
+        band_crc = [zlib.crc32(np.ascontiguousarray(h.se2_volume_download(t, t + 1)[0, y0:y1]).tobytes()) for t in range(N_THETA)]
+        all_crc = [None] * world
+        dist.all_gather_object(all_crc, (y0, y1, band_crc))
+        if rank == 0:
+            h.se2_volume_set_rows(0, 0)
+            h.se2_volume_build(N_THETA)
+            h.sync()
+            good = True
+            for t in range(N_THETA):
+                plane = h.se2_volume_download(t, t + 1)[0]
+                for (a, b, crcs) in all_crc:
+                    good = good and zlib.crc32(np.ascontiguousarray(plane[a:b]).tobytes()) == crcs[t]
+            gathered["verified"]["row_bands_equal_single_gpu_build"] = bool(good)
+            h.se2_volume_set_rows(y0, y1)
+            for _ in range(4):
+                step()
+            h.sync()
+        barrier()
 
     # ---- end to end through the C ABI with host buffers (`e2e`) ----------------------------------
     band = y1 - y0

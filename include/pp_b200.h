@@ -112,6 +112,11 @@ pp_status pp_footprint_get(pp_handle h, int32_t *offsets_xy_out, uint32_t max_po
  */
 pp_status pp_se2_volume_build(pp_handle h, uint32_t n_theta, float ox, float oy, float ot, uint32_t t_begin,
                               uint32_t t_end);
+/* The same for an arbitrary set of heading bins (any order, duplicates ignored): what a rank of a
+ * heading-sharded job builds when it owns the bins t and t + n_theta/2 together, which a centrally
+ * symmetric footprint lets it evaluate once. pp_se2_volume_refresh afterwards refreshes these bins. */
+pp_status pp_se2_volume_build_bins(pp_handle h, uint32_t n_theta, float ox, float oy, float ot, const uint32_t *bins,
+                                   uint32_t n_bins);
 pp_status pp_se2_volume_refresh(pp_handle h);
 pp_status pp_se2_volume_download(pp_handle h, uint32_t t_begin, uint32_t t_end, uint8_t *host_out,
                                  int host_is_pinned);
@@ -247,6 +252,19 @@ pp_status pp_obstacle_edges(pp_handle h, const double *poses_xyt, uint32_t Q, ui
 pp_status pp_comm_unique_id(void *id_out);
 pp_status pp_comm_init(pp_handle h, const void *id, int rank, int world);
 pp_status pp_se2_volume_allgather(pp_handle h);
+/* Heading-sharded build with the exchange hidden behind it (no counterpart in the reference). The
+ * n_theta/2 pairs of bins (u, u + n_theta/2) are dealt out in contiguous runs, rank g owning pairs
+ * [g*U/world, (g+1)*U/world) (single bins when n_theta is odd); a rank's run is cut into n_chunks
+ * parts, and while part k+1 is being built on the handle's stream, part k of EVERY rank travels on a
+ * second stream: by default as one group of ncclBroadcast calls (one per owner and half of the
+ * volume; the parts need not be equal), with PP_SHARD_PUSH through the copy engines into the peers'
+ * mapped volumes (pp_se2_volume_ipc_open) followed by a one-word all-reduce. When the call's work
+ * is done on the handle's stream every rank holds the whole volume. PP_SHARD_EXCHANGE_ONLY skips
+ * the builds (to time the exchange alone on an already built volume). Needs pp_comm_init. */
+#define PP_SHARD_PUSH 1u
+#define PP_SHARD_EXCHANGE_ONLY 2u
+pp_status pp_se2_volume_build_sharded(pp_handle h, uint32_t n_theta, float ox, float oy, float ot, uint32_t n_chunks,
+                                      uint32_t flags);
 
 /* Fused build + exchange (no counterpart in the reference). Instead of building a slab and then
  * gathering, the build kernels store every output word into the volume of EVERY rank over

@@ -16,7 +16,7 @@ LIB_PATH = os.environ.get("PP_B200_LIB", os.path.join(_HERE, "libpp_b200.so"))  
 SYMBOLS = [
     "pp_version", "pp_create", "pp_destroy", "pp_last_error", "pp_sync", "pp_host_alloc", "pp_host_free",
     "pp_timer_start", "pp_timer_stop", "pp_l2_flush", "pp_launch_count", "pp_costmap_upload", "pp_costmap_update_rect", "pp_costmap_download",
-    "pp_footprint_from_boundary", "pp_footprint_set", "pp_footprint_get", "pp_se2_volume_build",
+    "pp_footprint_from_boundary", "pp_footprint_set", "pp_footprint_get", "pp_se2_volume_build", "pp_se2_volume_build_bins", "pp_se2_volume_build_sharded",
     "pp_se2_volume_refresh", "pp_se2_volume_download", "pp_se2_volume_download_rows", "pp_se2_volume_ptr", "pp_se2_volume_set_mode",
     "pp_se2_volume_stats", "pp_footprint_cost_batch", "pp_heuristic_build", "pp_heuristic_ptr", "pp_heuristic_stats", "pp_heuristic_build_noalloc", "pp_plan",
     "pp_obstacles_extract", "pp_radius_topk", "pp_comm_unique_id", "pp_comm_init", "pp_se2_volume_allgather", "pp_se2_volume_reserve",
@@ -105,6 +105,8 @@ def load():
     L.pp_footprint_set.argtypes = [_vp, _vp, _u32]
     L.pp_footprint_get.argtypes = [_vp, _vp, _u32, C.POINTER(_u32)]
     L.pp_se2_volume_build.argtypes = [_vp, _u32, C.c_float, C.c_float, C.c_float, _u32, _u32]
+    L.pp_se2_volume_build_bins.argtypes = [_vp, _u32, C.c_float, C.c_float, C.c_float, _vp, _u32]
+    L.pp_se2_volume_build_sharded.argtypes = [_vp, _u32, C.c_float, C.c_float, C.c_float, _u32, _u32]
     L.pp_se2_volume_refresh.argtypes = [_vp]
     L.pp_se2_volume_download.argtypes = [_vp, _u32, _u32, _vp, C.c_int]
     L.pp_se2_volume_download_rows.argtypes = [_vp, _u32, _u32, _u32, _u32, _vp]
@@ -277,6 +279,15 @@ class Handle:
         return out
 
     # K1
+    def se2_volume_build_bins(self, n_theta, bins, ox=0.5, oy=0.5, ot=0.0):
+        b = np.ascontiguousarray(bins, np.uint32)
+        self._ck(self.L.pp_se2_volume_build_bins(self.h, n_theta, ox, oy, ot, b.ctypes.data, len(b)))
+        self.n_theta = n_theta
+
+    def se2_volume_build_sharded(self, n_theta, n_chunks=3, push=False, exchange_only=False, ox=0.5, oy=0.5, ot=0.0):
+        self._ck(self.L.pp_se2_volume_build_sharded(self.h, n_theta, ox, oy, ot, n_chunks, (1 if push else 0) | (2 if exchange_only else 0)))
+        self.n_theta = n_theta
+
     def se2_volume_build(self, n_theta, ox=0.5, oy=0.5, ot=0.0, t_begin=0, t_end=None):
         t_end = n_theta if t_end is None else t_end
         self.n_theta = n_theta

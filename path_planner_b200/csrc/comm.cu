@@ -7,6 +7,7 @@
 #include <dlfcn.h>
 #include <nccl.h>
 #include <cstring>
+#include <vector>
 
 namespace
 {
@@ -16,6 +17,10 @@ struct NcclApi
     ncclResult_t (*GetUniqueId)(ncclUniqueId *) = nullptr;
     ncclResult_t (*CommInitRank)(ncclComm_t *, int, ncclUniqueId, int) = nullptr;
     ncclResult_t (*AllGather)(const void *, void *, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*Broadcast)(const void *, void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*AllReduce)(const void *, void *, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*GroupStart)() = nullptr;
+    ncclResult_t (*GroupEnd)() = nullptr;
     ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
     const char *(*GetErrorString)(ncclResult_t) = nullptr;
 };
@@ -36,9 +41,14 @@ NcclApi *nccl_api(std::string &why)
     api.GetUniqueId = reinterpret_cast<decltype(api.GetUniqueId)>(dlsym(lib, "ncclGetUniqueId"));
     api.CommInitRank = reinterpret_cast<decltype(api.CommInitRank)>(dlsym(lib, "ncclCommInitRank"));
     api.AllGather = reinterpret_cast<decltype(api.AllGather)>(dlsym(lib, "ncclAllGather"));
+    api.Broadcast = reinterpret_cast<decltype(api.Broadcast)>(dlsym(lib, "ncclBroadcast"));
+    api.AllReduce = reinterpret_cast<decltype(api.AllReduce)>(dlsym(lib, "ncclAllReduce"));
+    api.GroupStart = reinterpret_cast<decltype(api.GroupStart)>(dlsym(lib, "ncclGroupStart"));
+    api.GroupEnd = reinterpret_cast<decltype(api.GroupEnd)>(dlsym(lib, "ncclGroupEnd"));
     api.CommDestroy = reinterpret_cast<decltype(api.CommDestroy)>(dlsym(lib, "ncclCommDestroy"));
     api.GetErrorString = reinterpret_cast<decltype(api.GetErrorString)>(dlsym(lib, "ncclGetErrorString"));
-    if (!api.GetUniqueId || !api.CommInitRank || !api.AllGather || !api.CommDestroy || !api.GetErrorString)
+    if (!api.GetUniqueId || !api.CommInitRank || !api.AllGather || !api.Broadcast || !api.AllReduce || !api.GroupStart || !api.GroupEnd ||
+        !api.CommDestroy || !api.GetErrorString)
     {
         why = "libnccl.so.2 lacks a required symbol";
         return nullptr;
@@ -103,6 +113,148 @@ pp_status pp_se2_volume_allgather(pp_handle h)
     const size_t slab = static_cast<size_t>(h->W) * h->H * per;
     ncclResult_t r = n->AllGather(h->d_vol + slab * h->rank, h->d_vol, slab, ncclUint8, static_cast<ncclComm_t>(h->comm), h->stream);
     PP_REQUIRE(h, r == ncclSuccess, PP_ERR_COMM, "ncclAllGather: %s", n->GetErrorString(r));
+    return PP_OK;
+}
+
+// Heading-sharded build with the exchange hidden behind it (see include/pp_b200.h).
+pp_status pp_se2_volume_build_sharded(pp_handle h, uint32_t n_theta, float ox, float oy, float ot, uint32_t n_chunks, uint32_t flags)
+{
+    if (!h)
+        return PP_ERR_INVALID;
+    const bool use_push = flags & PP_SHARD_PUSH, exchange_only = flags & PP_SHARD_EXCHANGE_ONLY;
+    PP_REQUIRE(h, h->comm, PP_ERR_STATE, "pp_se2_volume_build_sharded: call pp_comm_init first");
+    PP_REQUIRE(h, !use_push || h->n_peer == h->world, PP_ERR_STATE, "pp_se2_volume_build_sharded: PP_SHARD_PUSH needs the peers' volumes mapped (pp_se2_volume_ipc_open)");
+    PP_REQUIRE(h, !h->push, PP_ERR_STATE, "pp_se2_volume_build_sharded: switch the fused store exchange off first (pp_se2_volume_set_push(h, 0))");
+    PP_REQUIRE(h, n_chunks >= 1 && n_chunks <= 16, PP_ERR_RANGE, "pp_se2_volume_build_sharded: n_chunks %u outside 1..16", n_chunks);
+    PP_REQUIRE(h, n_theta > 0 && n_theta <= 4096, PP_ERR_RANGE, "n_theta %u outside 1..4096", n_theta);
+    PP_REQUIRE(h, h->d_cost, PP_ERR_STATE, "pp_se2_volume_build_sharded: upload a costmap first");
+    std::string why;
+    NcclApi *n = nccl_api(why);
+    PP_CUDA(h, cudaSetDevice(h->device));
+    if (!h->comm_stream)
+    {
+        PP_CUDA(h, cudaStreamCreateWithFlags(&h->comm_stream, cudaStreamNonBlocking));
+        PP_CUDA(h, cudaEventCreateWithFlags(&h->ev_comm, cudaEventDisableTiming));
+        for (int c = 0; c < 16; ++c)
+            PP_CUDA(h, cudaEventCreateWithFlags(&h->ev_chunk[c], cudaEventDisableTiming));
+        PP_CUDA(h, cudaMalloc(reinterpret_cast<void **>(&h->d_token), sizeof(int)));
+        PP_CUDA(h, cudaMemset(h->d_token, 0, sizeof(int)));
+    }
+    if (use_push)
+        for (int p = 0; p < h->world; ++p)
+            if (p != h->rank && !h->push_stream[p])
+            {
+                PP_CUDA(h, cudaStreamCreateWithFlags(&h->push_stream[p], cudaStreamNonBlocking));
+                PP_CUDA(h, cudaEventCreateWithFlags(&h->ev_push[p], cudaEventDisableTiming));
+            }
+    const size_t plane = static_cast<size_t>(h->W) * h->H;
+    PP_REQUIRE(h, h->n_peer == 0 || plane * n_theta <= h->vol_cap, PP_ERR_STATE,
+               "pp_se2_volume_build_sharded: the volume is mapped by peers and too small for %u bins", n_theta);
+    PP_CUDA(h, pp_reserve(h->d_vol, h->vol_cap, plane * n_theta));
+    // units: pairs of bins (u, u + n/2) stay on one rank, so that a centrally symmetric footprint is
+    // evaluated once per pair (an odd bin count has single bins as units)
+    const bool pairs = n_theta % 2 == 0;
+    const uint32_t U = pairs ? n_theta / 2 : n_theta;
+    auto unit_range = [&](int rank, uint32_t chunk, uint32_t &a, uint32_t &b) {
+        const uint32_t r0 = static_cast<uint32_t>(static_cast<uint64_t>(U) * rank / h->world);
+        const uint32_t r1 = static_cast<uint32_t>(static_cast<uint64_t>(U) * (rank + 1) / h->world);
+        a = r0 + static_cast<uint32_t>(static_cast<uint64_t>(r1 - r0) * chunk / n_chunks);
+        b = r0 + static_cast<uint32_t>(static_cast<uint64_t>(r1 - r0) * (chunk + 1) / n_chunks);
+    };
+    // one table count for all chunks of this call (chunks of different sizes must not flip the plan)
+    {
+        uint32_t a0, b0, a1, b1;
+        unit_range(h->rank, 0, a0, b0);
+        unit_range(h->rank, n_chunks - 1, a1, b1);
+        const uint32_t per_chunk = (b1 - a0 + n_chunks - 1) / n_chunks * (pairs ? 2 : 1);
+        h->few_bins_override = per_chunk <= 12 ? 1 : 0;
+    }
+    // everything queued so far (the costmap upload) precedes the exchange streams' first use of the volume
+    PP_CUDA(h, cudaEventRecord(h->ev_comm, h->stream));
+    PP_CUDA(h, cudaStreamWaitEvent(h->comm_stream, h->ev_comm, 0));
+    pp_status st = PP_OK;
+    for (uint32_t c = 0; c < n_chunks && st == PP_OK; ++c)
+    {
+        uint32_t a, b;
+        unit_range(h->rank, c, a, b);
+        if (!exchange_only && b > a)
+        {
+            std::vector<uint32_t> bins;
+            for (uint32_t u = a; u < b; ++u)
+            {
+                bins.push_back(u);
+                if (pairs)
+                    bins.push_back(u + U);
+            }
+            st = pp_se2_volume_build_bins(h, n_theta, ox, oy, ot, bins.data(), static_cast<uint32_t>(bins.size()));
+            if (st != PP_OK)
+                break;
+        }
+        PP_CUDA(h, cudaEventRecord(h->ev_chunk[c], h->stream));
+        if (use_push)
+        {
+            // copy engines: this rank's part of the chunk goes to every peer's mapped volume
+            for (int p = 0; p < h->world; ++p)
+            {
+                if (p == h->rank || b == a)
+                    continue;
+                PP_CUDA(h, cudaStreamWaitEvent(h->push_stream[p], h->ev_chunk[c], 0));
+                for (int half = 0; half < (pairs ? 2 : 1); ++half)
+                {
+                    const size_t off = plane * (a + static_cast<size_t>(half) * U);
+                    PP_CUDA(h, cudaMemcpyAsync(h->peer_vol[p] + off, h->d_vol + off, plane * (b - a), cudaMemcpyDeviceToDevice, h->push_stream[p]));
+                }
+            }
+        }
+        else
+        {
+            // NCCL: every rank's part of the chunk is broadcast from its owner, all in one group
+            PP_CUDA(h, cudaStreamWaitEvent(h->comm_stream, h->ev_chunk[c], 0));
+            ncclResult_t r = n->GroupStart();
+            for (int root = 0; root < h->world && r == ncclSuccess; ++root)
+            {
+                uint32_t ra, rb;
+                unit_range(root, c, ra, rb);
+                if (rb == ra)
+                    continue;
+                for (int half = 0; half < (pairs ? 2 : 1) && r == ncclSuccess; ++half)
+                {
+                    uint8_t *buf = h->d_vol + plane * (ra + static_cast<size_t>(half) * U);
+                    r = n->Broadcast(buf, buf, plane * (rb - ra), ncclUint8, root, static_cast<ncclComm_t>(h->comm), h->comm_stream);
+                }
+            }
+            const ncclResult_t r2 = n->GroupEnd();
+            PP_REQUIRE(h, r == ncclSuccess && r2 == ncclSuccess, PP_ERR_COMM, "ncclBroadcast (chunk %u): %s", c,
+                       n->GetErrorString(r != ncclSuccess ? r : r2));
+        }
+    }
+    h->few_bins_override = -1;
+    if (st != PP_OK)
+        return st;
+    if (use_push)
+    {
+        // the peers' parts are here once THEY have finished pushing: a one-word all-reduce queued behind this
+        // rank's copies completes on a rank only after every rank has reached it
+        for (int p = 0; p < h->world; ++p)
+            if (p != h->rank)
+            {
+                PP_CUDA(h, cudaEventRecord(h->ev_push[p], h->push_stream[p]));
+                PP_CUDA(h, cudaStreamWaitEvent(h->comm_stream, h->ev_push[p], 0));
+            }
+        ncclResult_t r = n->AllReduce(h->d_token, h->d_token, 1, ncclInt32, ncclSum, static_cast<ncclComm_t>(h->comm), h->comm_stream);
+        PP_REQUIRE(h, r == ncclSuccess, PP_ERR_COMM, "ncclAllReduce: %s", n->GetErrorString(r));
+    }
+    // the caller's stream continues when the exchange is complete
+    PP_CUDA(h, cudaEventRecord(h->ev_comm, h->comm_stream));
+    PP_CUDA(h, cudaStreamWaitEvent(h->stream, h->ev_comm, 0));
+    // the handle now holds every bin
+    h->t_begin = 0;
+    h->t_end = n_theta;
+    h->bins.resize(n_theta);
+    for (uint32_t t = 0; t < n_theta; ++t)
+        h->bins[t] = t;
+    h->vol_valid = true;
+    h->dirty = false;
     return PP_OK;
 }
 
@@ -193,6 +345,24 @@ void pp_comm_destroy(pp_handle h)
             cudaIpcCloseMemHandle(h->peer_vol[r]);
     h->n_peer = 0;
     h->push = false;
+    if (h->comm_stream)
+    {
+        cudaStreamSynchronize(h->comm_stream);
+        cudaStreamDestroy(h->comm_stream);
+        cudaEventDestroy(h->ev_comm);
+        for (int c = 0; c < 16; ++c)
+            cudaEventDestroy(h->ev_chunk[c]);
+        cudaFree(h->d_token);
+        h->comm_stream = nullptr;
+    }
+    for (int p = 0; p < 8; ++p)
+        if (h->push_stream[p])
+        {
+            cudaStreamSynchronize(h->push_stream[p]);
+            cudaStreamDestroy(h->push_stream[p]);
+            cudaEventDestroy(h->ev_push[p]);
+            h->push_stream[p] = nullptr;
+        }
     if (!h->comm)
         return;
     std::string why;

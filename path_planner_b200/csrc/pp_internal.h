@@ -39,7 +39,8 @@ struct pp_ctx
     // K1 volume
     uint8_t *d_vol = nullptr;
     size_t vol_cap = 0;
-    uint32_t n_theta = 0, t_begin = 0, t_end = 0;
+    uint32_t n_theta = 0, t_begin = 0, t_end = 0;  // t_begin/t_end: the hull of `bins`
+    std::vector<uint32_t> bins;                    // heading bins of the current build, ascending
     float ox = 0.5f, oy = 0.5f, ot = 0.0f;
     bool vol_valid = false;
     float2 *d_trig = nullptr;  // (cos, sin) per heading bin, from the host libm
@@ -113,6 +114,11 @@ struct pp_ctx
     bool push = false;          // builds store to every mapped volume
     uint32_t band_y0 = 0, band_y1 = 0;  // row band of pp_se2_volume_build (0,0 = whole map)
     void *comm = nullptr;  // ncclComm_t
+    // pp_se2_volume_build_sharded: the exchange runs on streams of its own beside the build
+    cudaStream_t comm_stream = nullptr, push_stream[8] = {};
+    cudaEvent_t ev_comm = nullptr, ev_chunk[16] = {}, ev_push[8] = {};
+    int *d_token = nullptr;
+    int few_bins_override = -1;  // -1: by the number of bins of a build; 0 / 1: forced (one plan for all chunks of a sharded build)
     int rank = 0, world = 1;
 };
 

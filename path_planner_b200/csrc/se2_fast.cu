@@ -98,7 +98,8 @@ struct FastArgs
     // brick leaves the staged region, which no sample list references)
     int32_t rec_a[MAX_TABLES], rec_b[MAX_TABLES], rec_d[MAX_TABLES];
     uint32_t rec_sync;  // bit k: table k starts a new dependency level (block barrier before it)
-    uint32_t t_first, n_t;
+    uint32_t n_t;                        // bins of this launch ...
+    uint16_t bin[MAX_T_PER_LAUNCH];      // ... and which heading bin each one is
     // mixed tiles: first column (row) of the right-hand (upper) range of a bin and the class of the range before it
     uint16_t xsplit[MAX_T_PER_LAUNCH], ysplit[MAX_T_PER_LAUNCH];
     uint8_t split_left[MAX_T_PER_LAUNCH];  // bit 0: class of the columns before xsplit, bit 1: of the rows before ysplit
@@ -179,7 +180,7 @@ __device__ __noinline__ void store_mixed(const FastArgs &a, uint32_t cls, uint32
             xm |= 1u << b;
     if (xm == 0)
         return;
-    uint8_t *base = a.vol + static_cast<size_t>(a.W) * a.H * (a.t_first + t) + gx;
+    uint8_t *base = a.vol + static_cast<size_t>(a.W) * a.H * a.bin[t] + gx;
 #pragma unroll
     for (int j = 0; j < 8; ++j)
     {
@@ -337,7 +338,7 @@ __device__ __forceinline__ void run_units(const FastArgs &a, const uint32_t *sm,
                 while (true)
                 {
                     asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%1, %2, %3}], [%4];" ::"l"(&a.vol_map), "r"(tx0),
-                                 "r"(gy), "r"(static_cast<int>(a.t_first + tb_)), "r"(src)
+                                 "r"(gy), "r"(static_cast<int>(a.bin[tb_])), "r"(src)
                                  : "memory");
                     uint32_t t2 = NO_LINK;
                     while (link != NO_LINK && t2 == NO_LINK)
@@ -356,7 +357,7 @@ __device__ __forceinline__ void run_units(const FastArgs &a, const uint32_t *sm,
             continue;
         }
         const uint32_t unit_off = static_cast<uint32_t>(row0) * a.W;
-        uint8_t *out = a.vol + plane * (a.t_first + t) + unit_off;  // warp-uniform
+        uint8_t *out = a.vol + plane * a.bin[t] + unit_off;  // warp-uniform
         while (true)
         {
             if (tile_inside && a.n_peers == 0)
@@ -388,7 +389,7 @@ __device__ __forceinline__ void run_units(const FastArgs &a, const uint32_t *sm,
             }
             if (t2 == NO_LINK)
                 break;
-            out = a.vol + plane * (a.t_first + t2) + unit_off;
+            out = a.vol + plane * a.bin[t2] + unit_off;
         }
     }
     // the staging buffer must outlive the bulk stores that read it
@@ -430,8 +431,8 @@ __global__ void __launch_bounds__(FT_THREADS, CTAS_PER_SM) se2_fast_kernel(const
     uint32_t my_cx = 255u, my_cy = 255u;
     if (static_cast<uint32_t>(tid) < a.n_t)
     {
-        my_cx = __ldg(a.xclass + static_cast<size_t>(a.t_first + tid) * a.tiles_x + tile_x);
-        my_cy = __ldg(a.yclass + static_cast<size_t>(a.t_first + tid) * a.tiles_y + tile_y);
+        my_cx = __ldg(a.xclass + static_cast<size_t>(a.bin[tid]) * a.tiles_x + tile_x);
+        my_cy = __ldg(a.yclass + static_cast<size_t>(a.bin[tid]) * a.tiles_y + tile_y);
     }
     // Costmap tile with halo, one warp per row. Lane l fetches the four bytes of table word l (cells
     // x0+l+32i: each of the four loads of a warp reads 32 consecutive bytes) and, for l < 2*HALO, the one
@@ -946,9 +947,10 @@ AxisClasses classify_axis(bool is_x, uint32_t n, float sample_off, const std::ve
 }
 
 constexpr uint32_t FEW_BINS = 12;
+bool wants_few_bins(pp_handle h) { return h->few_bins_override >= 0 ? h->few_bins_override != 0 : h->bins.size() <= FEW_BINS; }
 bool plan_matches(const Se2Plan *p, pp_handle h)
 {
-    return p && p->few_bins == (h->t_end - h->t_begin <= FEW_BINS) && p->W == h->W && p->H == h->H && p->n_theta == h->n_theta && p->ox == h->ox && p->oy == h->oy &&
+    return p && p->few_bins == wants_few_bins(h) && p->W == h->W && p->H == h->H && p->n_theta == h->n_theta && p->ox == h->ox && p->oy == h->oy &&
            p->ot == h->ot && p->fp == h->fp;
 }
 
@@ -1002,7 +1004,7 @@ pp_status build_plan(pp_handle h, int effort)
     int slots = static_cast<int>(std::min<size_t>(MAX_TABLES, (SMEM_LIMIT - 1024 - STAGE_BYTES) / table_bytes));
     // Every table costs a fixed amount per tile and saves samples per bin: with few bins per launch
     // (a heading-sharded rank of an 8-GPU job builds 9) a short library is the optimum.
-    pl->few_bins = h->t_end - h->t_begin <= FEW_BINS;
+    pl->few_bins = wants_few_bins(h);
     if (pl->few_bins)
     {
         const char *few = getenv("PP_SE2_FEW_TABLES");  // tuning knob for experiments
@@ -1257,27 +1259,29 @@ pp_status pp_se2_launch_fast(pp_handle h, uint32_t x0, uint32_t y0, uint32_t x1,
     double sample_sum = 0.0;
     uint64_t fast_pairs = 0, generic_pairs = 0;
 
-    uint32_t t = h->t_begin;
-    while (t < h->t_end)
+    const std::vector<uint32_t> &bins = h->bins;  // ascending
+    size_t bi = 0;
+    while (bi < bins.size())
     {
         // as many bins as fit in the parameter block
         uint32_t n = 0, words = 0;
         std::map<uint32_t, uint32_t> stored;           // offset-set id -> where its list sits in args.lists
         std::map<uint32_t, uint32_t> last_with;        // offset-set id -> last (bin, class) link that has it
-        while (t + n < h->t_end && n < MAX_T_PER_LAUNCH)
+        while (bi + n < bins.size() && n < MAX_T_PER_LAUNCH)
         {
+            const uint32_t t = bins[bi + n];
             uint32_t need = 0;
             for (int c = 0; c < 4; ++c)
-                if (!stored.count(pl->list_id[(t + n) * 4 + c]))
-                    need += (pl->list_len[(t + n) * 4 + c] + 3u) & ~3u;
+                if (!stored.count(pl->list_id[t * 4 + c]))
+                    need += (pl->list_len[t * 4 + c] + 3u) & ~3u;
             if (words + need > MAX_LIST_WORDS)
                 break;
-            args.xsplit[n] = pl->xsplit[t + n];
-            args.ysplit[n] = pl->ysplit[t + n];
-            args.split_left[n] = pl->split_left[t + n];
+            args.xsplit[n] = pl->xsplit[t];
+            args.ysplit[n] = pl->ysplit[t];
+            args.split_left[n] = pl->split_left[t];
             for (int c = 0; c < 4; ++c)
             {
-                const uint32_t len = pl->list_len[(t + n) * 4 + c], id = pl->list_id[(t + n) * 4 + c];
+                const uint32_t len = pl->list_len[t * 4 + c], id = pl->list_id[t * 4 + c];
                 args.list_len[n][c] = static_cast<uint16_t>(len);
                 args.chain_prev[n][c] = args.chain_next[n][c] = static_cast<uint16_t>(NO_LINK);
                 if (id == Se2Plan::NO_ID)
@@ -1289,7 +1293,7 @@ pp_status pp_se2_launch_fast(pp_handle h, uint32_t x0, uint32_t y0, uint32_t x1,
                 if (st == stored.end())
                 {
                     st = stored.emplace(id, words).first;
-                    std::memcpy(args.lists + words, pl->lists.data() + pl->list_off[(t + n) * 4 + c], len * sizeof(uint32_t));
+                    std::memcpy(args.lists + words, pl->lists.data() + pl->list_off[t * 4 + c], len * sizeof(uint32_t));
                     words += (len + 3u) & ~3u;  // keep every list 16-byte aligned
                 }
                 args.list_off[n][c] = static_cast<uint16_t>(st->second);
@@ -1304,49 +1308,55 @@ pp_status pp_se2_launch_fast(pp_handle h, uint32_t x0, uint32_t y0, uint32_t x1,
                 else
                     last_with.emplace(id, me);
             }
+            args.bin[n] = static_cast<uint16_t>(t);
             ++n;
         }
         PP_REQUIRE(h, n > 0, PP_ERR_RANGE, "a single heading bin needs more than %d sample words", MAX_LIST_WORDS);
-        args.t_first = t;
         args.n_t = n;
         // bookkeeping + the exact path for the (tile, bin) pairs outside uniform ranges: queued first, on the
         // side stream, so that its CTAs share the SMs with the tiled kernel instead of running after it
         bool forked = false;
+        uint32_t n_work = 0;
         for (uint32_t k = 0; k < n; ++k)
         {
-            const uint32_t nw = pl->work_off[t + k + 1] - pl->work_off[t + k];
+            const uint32_t t = bins[bi + k];
+            const uint32_t nw = pl->work_off[t + 1] - pl->work_off[t];
+            n_work += nw;
             generic_pairs += nw;
             fast_pairs += static_cast<uint64_t>(pl->tiles_x) * pl->tiles_y - nw / (FT_W / GEN_W);
             if (args.chain_prev[k][0] == NO_LINK)  // bins that share an earlier bin's evaluation load nothing
-                sample_sum += pl->list_len[(t + k) * 4];
+                sample_sum += pl->list_len[t * 4];
         }
-        const uint32_t w0 = pl->work_off[t], w1 = pl->work_off[t + n];
-        if (w1 > w0 && !getenv("PP_SE2_SKIP_GENERIC"))  // (timing experiments only: the result is incomplete without it)
+        if (n_work > 0 && !getenv("PP_SE2_SKIP_GENERIC"))  // (timing experiments only: the result is incomplete without it)
         {
             const bool whole_map = tx_lo == 0 && ty_lo == 0 && tx_hi >= pl->tiles_x && ty_hi >= pl->tiles_y;
-            if (whole_map)
+            const uint32_t t_lo = bins[bi], t_hi = bins[bi + n - 1];
+            if (whole_map && t_hi - t_lo + 1 == n)  // consecutive bins: a slice of the bin-sorted work list
             {
-                pp_status s = pp_se2_generic_worklist(h, pl->d_work + 2 * static_cast<size_t>(w0), w1 - w0);
+                pp_status s = pp_se2_generic_worklist(h, pl->d_work + 2 * static_cast<size_t>(pl->work_off[t_lo]), n_work);
                 if (s != PP_OK)
                     return s;
                 forked = true;
             }
             else
             {
-                // a row band or a dirty region: only the listed (tile, bin) pairs inside it
-                const uint64_t key[6] = {tx_lo, tx_hi, ty_lo, ty_hi, t, n};
+                // a row band, a dirty region or a scattered set of bins: only the listed (tile, bin) pairs inside
+                uint64_t key[6] = {tx_lo, tx_hi, ty_lo, ty_hi, 0, n};
+                for (uint32_t k = 0; k < n; ++k)
+                    key[4] = key[4] * 1000003ull + bins[bi + k] + 1;
                 if (std::memcmp(key, pl->region_key, sizeof(key)) != 0)
                 {
                     pl->region_work.clear();
-                    for (uint32_t e = w0; e < w1; ++e)
-                    {
-                        const uint32_t tile = pl->h_work[2 * e], wx = tile & 0xFFFFu, wy = tile >> 16;
-                        if (wx / (FT_W / GEN_W) >= tx_lo && wx / (FT_W / GEN_W) < tx_hi && wy >= ty_lo && wy < ty_hi)
+                    for (uint32_t k = 0; k < n; ++k)
+                        for (uint32_t e = pl->work_off[bins[bi + k]]; e < pl->work_off[bins[bi + k] + 1]; ++e)
                         {
-                            pl->region_work.push_back(tile);
-                            pl->region_work.push_back(pl->h_work[2 * e + 1]);
+                            const uint32_t tile = pl->h_work[2 * e], wx = tile & 0xFFFFu, wy = tile >> 16;
+                            if (wx / (FT_W / GEN_W) >= tx_lo && wx / (FT_W / GEN_W) < tx_hi && wy >= ty_lo && wy < ty_hi)
+                            {
+                                pl->region_work.push_back(tile);
+                                pl->region_work.push_back(pl->h_work[2 * e + 1]);
+                            }
                         }
-                    }
                     if (!pl->region_work.empty())
                     {
                         PP_CUDA(h, pp_reserve(pl->d_region_work, pl->region_cap, pl->region_work.size()));
@@ -1373,10 +1383,10 @@ pp_status pp_se2_launch_fast(pp_handle h, uint32_t x0, uint32_t y0, uint32_t x1,
             if (s != PP_OK)
                 return s;
         }
-        t += n;
+        bi += n;
     }
     (void)n_tiles;
     h->stat_fast_tiles = fast_pairs;
-    h->stat_samples_per_cell = sample_sum / std::max(1u, h->t_end - h->t_begin);
+    h->stat_samples_per_cell = sample_sum / std::max<size_t>(1, h->bins.size());
     return PP_OK;
 }

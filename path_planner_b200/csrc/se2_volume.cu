@@ -217,7 +217,7 @@ pp_status pp_se2_launch(pp_handle h, uint32_t x0, uint32_t y0, uint32_t x1, uint
     h->stat_fast_tiles = 0;
     h->stat_generic_tiles = 0;
     h->stat_samples_per_cell = 0.0;
-    if (x1 <= x0 || y1 <= y0 || h->t_end <= h->t_begin)
+    if (x1 <= x0 || y1 <= y0 || h->bins.empty())
         return PP_OK;
     if (h->vol_mode == 0)
     {
@@ -225,7 +225,23 @@ pp_status pp_se2_launch(pp_handle h, uint32_t x0, uint32_t y0, uint32_t x1, uint
         if (s != PP_INTERNAL_DECLINED)
             return s;
     }
-    return launch_generic(h, x0, y0, x1, y1, nullptr, 0, h->stream);
+    // the generic kernel takes a range of bins: one launch per run of consecutive bins
+    size_t i = 0;
+    const uint32_t keep_b = h->t_begin, keep_e = h->t_end;
+    pp_status s = PP_OK;
+    while (i < h->bins.size() && s == PP_OK)
+    {
+        size_t j = i + 1;
+        while (j < h->bins.size() && h->bins[j] == h->bins[j - 1] + 1)
+            ++j;
+        h->t_begin = h->bins[i];
+        h->t_end = h->bins[j - 1] + 1;
+        s = launch_generic(h, x0, y0, x1, y1, nullptr, 0, h->stream);
+        i = j;
+    }
+    h->t_begin = keep_b;
+    h->t_end = keep_e;
+    return s;
 }
 
 pp_status pp_se2_generic_worklist(pp_handle h, const uint32_t *d_worklist, uint32_t n_work)
@@ -275,10 +291,28 @@ pp_status pp_se2_volume_build(pp_handle h, uint32_t n_theta, float ox, float oy,
 {
     if (!h)
         return PP_ERR_INVALID;
+    PP_REQUIRE(h, t_begin <= t_end && t_end <= n_theta, PP_ERR_INVALID, "bins [%u,%u) outside [0,%u)", t_begin, t_end, n_theta);
+    std::vector<uint32_t> bins(t_end - t_begin);
+    for (uint32_t t = t_begin; t < t_end; ++t)
+        bins[t - t_begin] = t;
+    return pp_se2_volume_build_bins(h, n_theta, ox, oy, ot, bins.data(), static_cast<uint32_t>(bins.size()));
+}
+
+pp_status pp_se2_volume_build_bins(pp_handle h, uint32_t n_theta, float ox, float oy, float ot, const uint32_t *bins_in,
+                                   uint32_t n_bins)
+{
+    if (!h)
+        return PP_ERR_INVALID;
+    PP_REQUIRE(h, bins_in || n_bins == 0, PP_ERR_INVALID, "pp_se2_volume_build_bins: null bin list");
+    std::vector<uint32_t> bins(bins_in, bins_in + n_bins);
+    std::sort(bins.begin(), bins.end());
+    bins.erase(std::unique(bins.begin(), bins.end()), bins.end());
+    PP_REQUIRE(h, bins.empty() || bins.back() < n_theta, PP_ERR_INVALID, "pp_se2_volume_build_bins: bin %u outside [0,%u)",
+               bins.empty() ? 0u : bins.back(), n_theta);
+    const uint32_t t_begin = bins.empty() ? 0u : bins.front(), t_end = bins.empty() ? 0u : bins.back() + 1;
     PP_REQUIRE(h, h->d_cost, PP_ERR_STATE, "pp_se2_volume_build: upload a costmap first");
     PP_REQUIRE(h, !h->fp.empty(), PP_ERR_STATE, "pp_se2_volume_build: set a footprint first");
     PP_REQUIRE(h, n_theta > 0 && n_theta <= 4096, PP_ERR_RANGE, "n_theta %u outside 1..4096", n_theta);
-    PP_REQUIRE(h, t_begin <= t_end && t_end <= n_theta, PP_ERR_INVALID, "bins [%u,%u) outside [0,%u)", t_begin, t_end, n_theta);
     PP_REQUIRE(h, ox >= -1.0f && ox <= 1.0f && oy >= -1.0f && oy <= 1.0f, PP_ERR_INVALID,
                "sample offsets must lie in [-1,1] (got %g, %g)", ox, oy);
     PP_CUDA(h, cudaSetDevice(h->device));
@@ -295,6 +329,7 @@ pp_status pp_se2_volume_build(pp_handle h, uint32_t n_theta, float ox, float oy,
     h->ot = ot;
     h->t_begin = t_begin;
     h->t_end = t_end;
+    h->bins.swap(bins);
 
     // heading -> (cos, sin) with the host libm, formed exactly like the reference does:
     // theta = motion.theta * bin_size (astar_hybrid.cpp:283), bin_size = 2.0f*(float)M_PI/size_theta

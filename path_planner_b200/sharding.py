@@ -1,5 +1,6 @@
 """Sharding of the SE2 volume over the GPUs of one box. Two partitions of the same
-independent units: heading bins -- rank g of `world` owns bins [g*n/world, (g+1)*n/world) -- and map-row
+independent units: heading bins -- rank g of `world` owns bins [g*n/world, (g+1)*n/world), or, with
+pp_se2_volume_build_sharded, runs of the pairs (u, u + n/2) (twin_chunks below) -- and map-row
 bands (row_band below; what bench.py --gpus N times as `value`). Host-side helpers shared by bench.py and
 the tests; the data path itself (pp_se2_volume_build per rank, pp_se2_volume_set_rows,
 pp_se2_volume_allgather) is in the library."""
@@ -26,14 +27,24 @@ def max_over_ranks(value, dist=None, device="cpu"):
     return float(t.item())
 
 
-def gather_slabs(local_slab, dist):
-    """Emulation of pp_se2_volume_allgather on host tensors (gloo): every rank contributes its
-    [bins_per_rank, H, W] uint8 slab and receives the whole [n_theta, H, W] volume."""
-    import torch
-    world = dist.get_world_size()
-    slab = torch.as_tensor(local_slab).contiguous()
-    out = torch.empty((world * slab.shape[0],) + tuple(slab.shape[1:]), dtype=slab.dtype)
-    dist.all_gather_into_tensor(out, slab)
+def twin_chunks(n_theta, rank, world, n_chunks=1):
+    """The heading bins of `rank` in pp_se2_volume_build_sharded, chunk by chunk: the n_theta/2 pairs of bins
+    (u, u + n_theta/2) are dealt out in contiguous runs (single bins when n_theta is odd), rank g owning pairs
+    [g*U/world, (g+1)*U/world); a rank's run is cut into n_chunks parts. Returns a list of lists of bins."""
+    if world < 1 or not 0 <= rank < world:
+        raise ValueError(f"rank {rank} of {world}")
+    pairs = n_theta % 2 == 0
+    U = n_theta // 2 if pairs else n_theta
+    r0, r1 = U * rank // world, U * (rank + 1) // world
+    out = []
+    for c in range(n_chunks):
+        a, b = r0 + (r1 - r0) * c // n_chunks, r0 + (r1 - r0) * (c + 1) // n_chunks
+        bins = []
+        for u in range(a, b):
+            bins.append(u)
+            if pairs:
+                bins.append(u + U)
+        out.append(bins)
     return out
 
 

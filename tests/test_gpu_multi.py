@@ -71,7 +71,26 @@ def _worker(rank, world, port, q):
         h.costmap_upload(cost)
         h.se2_volume_build(72)  # the whole volume on this GPU alone
         single = h.se2_volume_download()
-        q.put((rank, bool(np.array_equal(gathered, single)) and bool(np.array_equal(pushed, single)) and banded_ok,
+        # pair-sharded build with the exchange pipelined behind it: NCCL broadcasts, then copy-engine pushes
+        sharded_ok = True
+        h2.se2_volume_set_push(False)
+        h2.se2_volume_set_rows(0, 0)
+        h2.costmap_upload(cost)
+        obj2 = [capi.comm_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(obj2, src=0)
+        h2.comm_init(obj2[0], rank, world)
+        for push in (False, True):
+            for chunks in (1, 3):
+                h2.costmap_upload(cost[::-1].copy())  # fill the volume with another map's values first
+                h2.se2_volume_build(72)
+                h2.costmap_upload(cost)
+                h2.sync()
+                dist.barrier()
+                h2.se2_volume_build_sharded(72, chunks, push=push)
+                h2.sync()
+                sharded_ok = sharded_ok and bool(np.array_equal(h2.se2_volume_download(), single))
+                dist.barrier()
+        q.put((rank, bool(np.array_equal(gathered, single)) and bool(np.array_equal(pushed, single)) and banded_ok and sharded_ok,
                int(gathered.sum() % 1000003)))
         dist.barrier()
         h2.close()

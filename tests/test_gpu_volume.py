@@ -237,3 +237,36 @@ def test_every_halo_instantiation(handle, port, boundary):
     stats = handle.se2_volume_stats()
     assert stats["fast_tiles"] > 0  # the tiled kernel did take part
     assert np.array_equal(handle.se2_volume_download(), port.se2_volume(cost, pts, 72))
+
+
+def test_build_of_a_scattered_bin_set(handle, golden):
+    """pp_se2_volume_build_bins: any set of heading bins (here pairs t, t + 36 as a heading-sharded rank owns
+    them, a lone bin, and bins given out of order and twice); the other planes of the volume stay untouched."""
+    cost = golden["cost"]
+    want = golden["vol_rect_hole_centre_72"]
+    handle.costmap_upload(cost)
+    handle.footprint_from_boundary(0.05, *FOOTPRINTS["rect_hole"])
+    handle.se2_volume_build(72)
+    handle.costmap_upload(np.zeros_like(cost))
+    handle.se2_volume_build(72)  # all planes now hold the empty map's volume
+    handle.costmap_upload(cost)
+    bins = [40, 4, 5, 41, 17, 4, 70, 34]
+    handle.se2_volume_build_bins(72, bins)
+    got = handle.se2_volume_download()
+    for t in range(72):
+        if t in bins:
+            assert np.array_equal(got[t], want[t]), t
+        else:
+            assert not got[t].any(), t
+    # a refresh after a costmap change recomputes exactly these bins
+    patch = np.full((9, 11), 254, np.uint8)
+    handle.costmap_update_rect(20, 30, patch)
+    handle.se2_volume_refresh()
+    c2 = cost.copy()
+    c2[30:39, 20:31] = 254
+    handle.costmap_upload(c2)
+    got2 = handle.se2_volume_download()
+    handle.se2_volume_build(72)
+    full = handle.se2_volume_download()
+    for t in set(bins):
+        assert np.array_equal(got2[t], full[t]), t

@@ -7,7 +7,18 @@ import socket
 import numpy as np
 import pytest
 
-from path_planner_b200.sharding import bin_range
+from path_planner_b200.sharding import bin_range, twin_chunks
+
+
+def gather_slabs(local_slab, dist):
+    """Stand-in for pp_se2_volume_allgather on host tensors (gloo): every rank contributes its
+    [bins_per_rank, H, W] uint8 slab and receives the whole [n_theta, H, W] volume."""
+    import torch
+    world = dist.get_world_size()
+    slab = torch.as_tensor(local_slab).contiguous()
+    out = torch.empty((world * slab.shape[0],) + tuple(slab.shape[1:]), dtype=slab.dtype)
+    dist.all_gather_into_tensor(out, slab)
+    return out
 
 
 def test_bin_ranges_cover_exactly():
@@ -21,6 +32,23 @@ def test_bin_ranges_cover_exactly():
         bin_range(72, 0, 5)
     with pytest.raises(ValueError):
         bin_range(72, 2, 2)
+
+
+def test_twin_chunks_partition_the_bins_and_keep_pairs_together():
+    for n in (72, 144, 9, 2):
+        for world in (1, 2, 3, 4, 8):
+            for chunks in (1, 3, 5):
+                seen = []
+                for g in range(world):
+                    per_rank = twin_chunks(n, g, world, chunks)
+                    assert len(per_rank) == chunks
+                    for c in per_rank:
+                        if n % 2 == 0:  # a bin and its twin sit in the same chunk of the same rank
+                            assert all(((b + n // 2) % n) in c for b in c)
+                        seen += c
+                assert sorted(seen) == list(range(n))
+            sizes = [sum(len(c) for c in twin_chunks(n, g, world, 1)) for g in range(world)]
+            assert max(sizes) - min(sizes) <= (2 if n % 2 == 0 else 1)
 
 
 def test_row_bands_cover_exactly():
@@ -44,7 +72,7 @@ def _free_port():
 def _worker(rank, world, port, q):
     import torch.distributed as dist
     import oracle
-    from path_planner_b200.sharding import gather_slabs, max_over_ranks
+    from path_planner_b200.sharding import max_over_ranks
     from path_planner_b200.synth import make_costmap
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
@@ -58,6 +86,18 @@ def _worker(rank, world, port, q):
         full = gather_slabs(slab, dist).numpy()
         want = p.se2_volume(cost, pts, 72)
         ok = np.array_equal(full, want)
+        # the pair-sharded, chunked exchange of pp_se2_volume_build_sharded: every chunk of every rank is broadcast
+        # from its owner into a full-size volume (gloo broadcasts standing in for the grouped ncclBroadcast calls)
+        import torch
+        vol = torch.zeros(want.shape, dtype=torch.uint8)
+        n_chunks = 3
+        for c in range(n_chunks):
+            for b in twin_chunks(72, rank, world, n_chunks)[c]:
+                vol[b] = torch.from_numpy(p.se2_volume(cost, pts, 72, t0=b, t1=b + 1)[0])
+            for root in range(world):
+                for b in twin_chunks(72, root, world, n_chunks)[c]:
+                    dist.broadcast(vol[b], src=root)
+        ok = ok and np.array_equal(vol.numpy(), want)
         slowest = max_over_ranks(1.0 + rank, dist)
         q.put((rank, bool(ok), slowest))
     finally:
