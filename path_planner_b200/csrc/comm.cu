@@ -158,8 +158,11 @@ pp_status pp_se2_volume_build_sharded(pp_handle h, uint32_t n_theta, float ox, f
     auto unit_range = [&](int rank, uint32_t chunk, uint32_t &a, uint32_t &b) {
         const uint32_t r0 = static_cast<uint32_t>(static_cast<uint64_t>(U) * rank / h->world);
         const uint32_t r1 = static_cast<uint32_t>(static_cast<uint64_t>(U) * (rank + 1) / h->world);
-        a = r0 + static_cast<uint32_t>(static_cast<uint64_t>(r1 - r0) * chunk / n_chunks);
-        b = r0 + static_cast<uint32_t>(static_cast<uint64_t>(r1 - r0) * (chunk + 1) / n_chunks);
+        // the first part is half as long as the others: nothing travels while it is being built
+        const uint64_t total = 2ull * n_chunks - 1;
+        auto cut = [&](uint32_t c) { return c == 0 ? 0ull : 2ull * c - 1; };
+        a = r0 + static_cast<uint32_t>((static_cast<uint64_t>(r1 - r0) * cut(chunk) + total / 2) / total);
+        b = chunk + 1 == n_chunks ? r1 : r0 + static_cast<uint32_t>((static_cast<uint64_t>(r1 - r0) * cut(chunk + 1) + total / 2) / total);
     };
     // one table count for all chunks of this call (chunks of different sizes must not flip the plan)
     {
@@ -199,11 +202,15 @@ pp_status pp_se2_volume_build_sharded(pp_handle h, uint32_t n_theta, float ox, f
                 if (p == h->rank || b == a)
                     continue;
                 PP_CUDA(h, cudaStreamWaitEvent(h->push_stream[p], h->ev_chunk[c], 0));
-                for (int half = 0; half < (pairs ? 2 : 1); ++half)
-                {
-                    const size_t off = plane * (a + static_cast<size_t>(half) * U);
-                    PP_CUDA(h, cudaMemcpyAsync(h->peer_vol[p] + off, h->d_vol + off, plane * (b - a), cudaMemcpyDeviceToDevice, h->push_stream[p]));
-                }
+                // both halves of the volume in one strided copy where the pitch allows it
+                const size_t off = plane * a, pitch = plane * U;
+                if (pairs && pitch <= static_cast<size_t>(0x7FFFFFFF))
+                    PP_CUDA(h, cudaMemcpy2DAsync(h->peer_vol[p] + off, pitch, h->d_vol + off, pitch, plane * (b - a), 2, cudaMemcpyDeviceToDevice,
+                                                 h->push_stream[p]));
+                else
+                    for (int half = 0; half < (pairs ? 2 : 1); ++half)
+                        PP_CUDA(h, cudaMemcpyAsync(h->peer_vol[p] + off + half * pitch, h->d_vol + off + half * pitch, plane * (b - a),
+                                                   cudaMemcpyDeviceToDevice, h->push_stream[p]));
             }
         }
         else

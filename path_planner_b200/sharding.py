@@ -30,15 +30,18 @@ def max_over_ranks(value, dist=None, device="cpu"):
 def twin_chunks(n_theta, rank, world, n_chunks=1):
     """The heading bins of `rank` in pp_se2_volume_build_sharded, chunk by chunk: the n_theta/2 pairs of bins
     (u, u + n_theta/2) are dealt out in contiguous runs (single bins when n_theta is odd), rank g owning pairs
-    [g*U/world, (g+1)*U/world); a rank's run is cut into n_chunks parts. Returns a list of lists of bins."""
+    [g*U/world, (g+1)*U/world); a rank's run is cut into n_chunks parts, the first half as long as the others. Returns a list of lists of bins."""
     if world < 1 or not 0 <= rank < world:
         raise ValueError(f"rank {rank} of {world}")
     pairs = n_theta % 2 == 0
     U = n_theta // 2 if pairs else n_theta
     r0, r1 = U * rank // world, U * (rank + 1) // world
     out = []
+    total = 2 * n_chunks - 1  # the first part is half as long as the others (nothing travels while it is built)
+    cut = lambda c: 0 if c == 0 else 2 * c - 1
     for c in range(n_chunks):
-        a, b = r0 + (r1 - r0) * c // n_chunks, r0 + (r1 - r0) * (c + 1) // n_chunks
+        a = r0 + ((r1 - r0) * cut(c) + total // 2) // total
+        b = r1 if c + 1 == n_chunks else r0 + ((r1 - r0) * cut(c + 1) + total // 2) // total
         bins = []
         for u in range(a, b):
             bins.append(u)
