@@ -192,11 +192,42 @@ typedef struct pp_plan_params
     float minimum_turning_radius, cost_penalty, change_penalty, non_straight_penalty, reverse_penalty;
     float analytic_expansion_ratio, analytic_expansion_tolerance, tolerance;
     uint32_t max_iterations, max_on_approach_iterations;
+    uint32_t flags; /* PP_PLAN_* */
 } pp_plan_params;
+/* PP_PLAN_EXACT_ANALYTIC: the samples of every analytic expansion (astar_hybrid.cpp:315-329) are decided at
+ * their CONTINUOUS poses like the reference's checkFootPrintCollision (collision_checker.cpp:126-142) instead
+ * of at the cell centre / nearest bin: the volume filters, flagged samples are re-checked exactly, and an
+ * expansion that survives is confirmed by one batched pp_footprint_cost_batch launch over all its samples.
+ * PP_PLAN_VALIDATE_PATH: after a successful search every pose of the path is evaluated exactly at its
+ * continuous position in one batched launch; the count of colliding poses is reported by pp_plan_stats
+ * (the primitives of the search are still decided by the volume: see DESIGN.md for measured rates). */
+#define PP_PLAN_EXACT_ANALYTIC 1u
+#define PP_PLAN_VALIDATE_PATH 2u
 pp_status pp_plan(pp_handle h, const pp_plan_params *params, double resolution, double origin_x, double origin_y,
                   const float *start_xyt, const float *goal_xyt, float *path_xyt_out, uint32_t max_points,
                   uint32_t *n_points_out, int32_t *iterations_out, int32_t *found_out, double *tables_ms_out,
                   double *search_ms_out);
+
+/* Counters of the last pp_plan on this handle. */
+typedef struct pp_plan_stats_t
+{
+    uint64_t lookups;                    /* volume lookups of the search */
+    uint32_t analytic_attempts;          /* analytic expansions tried */
+    uint32_t analytic_confirm_batches;   /* PP_PLAN_EXACT_ANALYTIC: batched exact confirmations launched */
+    uint32_t exact_host_checks;          /* ... samples the volume flagged that were re-checked exactly */
+    uint32_t false_collisions_overruled; /* ... of those, found free at the continuous pose */
+    uint32_t false_free_caught;          /* ... samples the volume called free that the exact batch rejected */
+    uint32_t path_poses_checked;         /* PP_PLAN_VALIDATE_PATH: poses of the path evaluated exactly ... */
+    uint32_t path_poses_in_collision;    /* ... and how many of them collide at their continuous pose */
+} pp_plan_stats_t;
+pp_status pp_plan_stats(pp_handle h, pp_plan_stats_t *out);
+/* Quantisation statistics: with the log enabled, pp_plan records every footprint question of the search --
+ * the continuous pose (cells, cells, radians) the reference would have evaluated, whether it came from a
+ * motion primitive / end pose (kind 0, astar_hybrid.cpp:37,40,283) or an analytic-expansion sample (kind 1,
+ * :325), and what the volume answered. Feeding the poses to pp_footprint_cost_batch gives the exact answers. */
+pp_status pp_plan_set_query_log(pp_handle h, int enable);
+pp_status pp_plan_query_log(pp_handle h, float *poses_xyt_out, uint8_t *kind_out, uint8_t *flag_out, uint8_t *cost_out,
+                            uint32_t max_queries, uint32_t *n_out);
 
 /* ---- K3: TEB obstacle association -----------------------------------------------------------
  * pp_obstacles_extract replaces TebFollower::addObstacles (teb_follower.cpp:140-169): all cells

@@ -69,10 +69,21 @@ class E2E:
                                       C.POINTER(C.c_int), C.POINTER(C.c_double), C.POINTER(C.c_double),
                                       C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
 
+        self.lib.e2e_query_log.argtypes = [f32p, u8p, u8p, u8p, C.c_int]
+
     def heading_fraction(self, start_theta, n_theta):
         return float(self.lib.e2e_heading_fraction(start_theta, n_theta))
 
+    def query_log(self):
+        """Footprint questions of the last plan() run with mode + 8: (poses[n,3], kind[n], volume flag[n], volume cost[n])."""
+        n = self.lib.e2e_query_log(np.zeros((1, 3), np.float32), np.zeros(1, np.uint8), np.zeros(1, np.uint8), np.zeros(1, np.uint8), 0)
+        poses = np.zeros((max(n, 1), 3), np.float32)
+        kind, flag, cost = (np.zeros(max(n, 1), np.uint8) for _ in range(3))
+        self.lib.e2e_query_log(poses, kind, flag, cost, n)
+        return poses[:n], kind[:n], flag[:n], cost[:n]
+
     def plan(self, mode, cost, res, boundary, hole, start, goal, oracle_volume=None, params=None):
+        """mode 0 / 1 (+ 4: analytic-expansion samples at their continuous poses, + 8: log the questions)."""
         P = plan_params(**(params or {}))
         H, W = cost.shape
         b = np.ascontiguousarray(boundary, np.float32)

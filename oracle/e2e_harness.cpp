@@ -8,6 +8,10 @@
 //               reference's own lazily grown heuristic table (no injection)
 //   mode 1 (B)  collision lookups into the GPU-built volume, and the GPU heuristic field
 //               injected over the reference's table right after cacheObstacleHeuristic()
+//   + 4         the samples of analytic expansions (checkFootPrintCollision, astar_hybrid.cpp:325) are decided
+//               at their continuous poses (CollisionChecker::setExactAnalytic): what pp_plan's
+//               PP_PLAN_EXACT_ANALYTIC mode must reproduce
+//   + 8         every footprint question and the volume's answer are logged (e2e_query_log)
 // Pass = same Coordinates element-wise and same iteration count. Both modes quantise poses to
 // the cell centre / nearest bin, which is what separates them from the unmodified reference
 // (ref_plan in ref_harness.cpp, reported for context only).
@@ -22,6 +26,7 @@ namespace
 {
 int g_mode = 0;
 double g_inject_ms = 0.0;
+std::vector<CollisionChecker::Query> g_log;
 }
 
 void pp_b200_after_cache_heuristic(AstarHybrid *self)
@@ -66,8 +71,11 @@ int e2e_plan(int mode, const uint8_t *cost, uint32_t W, uint32_t H, double res, 
              float *path_out, int max_pts, int *n_pts, int *iterations, double *plan_ms, double *prepare_ms,
              unsigned long long *lookups, unsigned long long *exact_calls)
 {
+    const bool exact_analytic = mode & 4, log_queries = mode & 8;
+    mode &= 3;
     g_mode = mode;
     g_inject_ms = 0.0;
+    g_log.clear();
     costmap_2d::Costmap2D map(W, H, res, 0.0, 0.0);
     std::memcpy(map.getCharMap(), cost, static_cast<size_t>(W) * H);
     CollisionChecker checker;
@@ -102,6 +110,9 @@ int e2e_plan(int mode, const uint8_t *cost, uint32_t W, uint32_t H, double res, 
     }
     *prepare_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - tic).count();
 
+    checker.setExactAnalytic(exact_analytic);
+    if (log_queries)
+        checker.setQueryLog(&g_log);
     AstarHybrid astar(&info, &checker);
     Coordinate start(start_xyt[0], start_xyt[1], start_xyt[2]), goal(goal_xyt[0], goal_xyt[1], goal_xyt[2]);
     Coordinates path;
@@ -123,5 +134,22 @@ int e2e_plan(int mode, const uint8_t *cost, uint32_t W, uint32_t H, double res, 
         path_out[3 * i + 2] = path[i].theta;
     }
     return ok ? 1 : 0;
+}
+
+// the footprint questions of the last e2e_plan run with mode + 8: pose (cells, cells, radians), kind
+// (0 primitive / end pose, 1 analytic-expansion sample), and the volume's flag and cost
+int e2e_query_log(float *xyt, uint8_t *kind, uint8_t *flag, uint8_t *cost, int max_n)
+{
+    const int n = static_cast<int>(g_log.size());
+    for (int i = 0; i < n && i < max_n; ++i)
+    {
+        xyt[3 * i] = g_log[i].x;
+        xyt[3 * i + 1] = g_log[i].y;
+        xyt[3 * i + 2] = g_log[i].theta;
+        kind[i] = g_log[i].kind;
+        flag[i] = g_log[i].flag;
+        cost[i] = g_log[i].cost;
+    }
+    return n;
 }
 }

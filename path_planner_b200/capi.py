@@ -18,7 +18,7 @@ SYMBOLS = [
     "pp_timer_start", "pp_timer_stop", "pp_l2_flush", "pp_launch_count", "pp_costmap_upload", "pp_costmap_update_rect", "pp_costmap_download",
     "pp_footprint_from_boundary", "pp_footprint_set", "pp_footprint_get", "pp_se2_volume_build", "pp_se2_volume_build_bins", "pp_se2_volume_build_sharded",
     "pp_se2_volume_refresh", "pp_se2_volume_download", "pp_se2_volume_download_rows", "pp_se2_volume_ptr", "pp_se2_volume_set_mode",
-    "pp_se2_volume_stats", "pp_footprint_cost_batch", "pp_heuristic_build", "pp_heuristic_ptr", "pp_heuristic_stats", "pp_heuristic_build_noalloc", "pp_plan",
+    "pp_se2_volume_stats", "pp_footprint_cost_batch", "pp_heuristic_build", "pp_heuristic_ptr", "pp_heuristic_stats", "pp_heuristic_build_noalloc", "pp_plan", "pp_plan_stats", "pp_plan_set_query_log", "pp_plan_query_log",
     "pp_obstacles_extract", "pp_radius_topk", "pp_comm_unique_id", "pp_comm_init", "pp_se2_volume_allgather", "pp_se2_volume_reserve",
     "pp_se2_volume_ipc_export", "pp_se2_volume_ipc_open", "pp_se2_volume_set_push", "pp_se2_volume_set_rows",
     "pp_occupancy_from_image", "pp_occupancy_upload", "pp_occupancy_update_rect", "pp_occupancy_download",
@@ -36,15 +36,23 @@ class PlanParams(C.Structure):
                 ("cost_penalty", C.c_float), ("change_penalty", C.c_float), ("non_straight_penalty", C.c_float),
                 ("reverse_penalty", C.c_float), ("analytic_expansion_ratio", C.c_float),
                 ("analytic_expansion_tolerance", C.c_float), ("tolerance", C.c_float), ("max_iterations", C.c_uint32),
-                ("max_on_approach_iterations", C.c_uint32)]
+                ("max_on_approach_iterations", C.c_uint32), ("flags", C.c_uint32)]
 
     @classmethod
     def make(cls, motion_type=2, n_theta=72, minimum_turning_radius=0.84, cost_penalty=2.0, change_penalty=0.01,
              non_straight_penalty=1.2, reverse_penalty=3.0, analytic_expansion_ratio=1.0,
-             analytic_expansion_tolerance=3.0, tolerance=0.6, max_iterations=100000, max_on_approach_iterations=1000):
+             analytic_expansion_tolerance=3.0, tolerance=0.6, max_iterations=100000, max_on_approach_iterations=1000,
+             exact_analytic=False, validate_path=False):
         return cls(motion_type, n_theta, minimum_turning_radius, cost_penalty, change_penalty, non_straight_penalty,
                    reverse_penalty, analytic_expansion_ratio, analytic_expansion_tolerance, tolerance, max_iterations,
-                   max_on_approach_iterations)
+                   max_on_approach_iterations, (1 if exact_analytic else 0) | (2 if validate_path else 0))
+
+
+class PlanStats(C.Structure):
+    """pp_plan_stats_t"""
+    _fields_ = [("lookups", C.c_uint64), ("analytic_attempts", C.c_uint32), ("analytic_confirm_batches", C.c_uint32),
+                ("exact_host_checks", C.c_uint32), ("false_collisions_overruled", C.c_uint32), ("false_free_caught", C.c_uint32),
+                ("path_poses_checked", C.c_uint32), ("path_poses_in_collision", C.c_uint32)]
 
 
 class LayerParams(C.Structure):
@@ -119,6 +127,9 @@ def load():
     L.pp_plan.argtypes = [_vp, C.POINTER(PlanParams), C.c_double, C.c_double, C.c_double, _vp, _vp, _vp, _u32,
                           C.POINTER(_u32), C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_double),
                           C.POINTER(C.c_double)]
+    L.pp_plan_stats.argtypes = [_vp, C.POINTER(PlanStats)]
+    L.pp_plan_set_query_log.argtypes = [_vp, C.c_int]
+    L.pp_plan_query_log.argtypes = [_vp, _vp, _vp, _vp, _vp, _u32, C.POINTER(_u32)]
     L.pp_heuristic_ptr.argtypes = [_vp, C.POINTER(_vp)]
     L.pp_heuristic_stats.argtypes = [_vp, C.POINTER(_u32), C.POINTER(C.c_uint64)]
     L.pp_obstacles_extract.argtypes = [_vp] + [C.c_double] * 8 + [_vp, _u32, C.POINTER(_u32)]
@@ -354,8 +365,23 @@ class Handle:
         t_ms, s_ms = C.c_double(0), C.c_double(0)
         self._ck(self.L.pp_plan(self.h, C.byref(P), resolution, origin[0], origin[1], _ptr(s), _ptr(g), _ptr(path), max_points,
                                 C.byref(n), C.byref(it), C.byref(found), C.byref(t_ms), C.byref(s_ms)))
+        st = PlanStats()
+        self._ck(self.L.pp_plan_stats(self.h, C.byref(st)))
         return {"ok": found.value, "path": path[:n.value].copy(), "iterations": it.value, "tables_ms": t_ms.value,
-                "search_ms": s_ms.value}
+                "search_ms": s_ms.value, "stats": {f: int(getattr(st, f)) for f, _ in PlanStats._fields_}}
+
+    def plan_set_query_log(self, enable):
+        self._ck(self.L.pp_plan_set_query_log(self.h, int(enable)))
+
+    def plan_query_log(self):
+        """(poses[n,3] float32 (cells, cells, rad), kind[n], volume flag[n], volume cost[n]) of the last pp_plan."""
+        n = _u32(0)
+        self._ck(self.L.pp_plan_query_log(self.h, None, None, None, None, 0, C.byref(n)))
+        poses = np.zeros((n.value, 3), np.float32)
+        kind, flag, cost = (np.zeros(n.value, np.uint8) for _ in range(3))
+        if n.value:
+            self._ck(self.L.pp_plan_query_log(self.h, _ptr(poses), _ptr(kind), _ptr(flag), _ptr(cost), n.value, C.byref(n)))
+        return poses, kind, flag, cost
 
     # K3
     def obstacles_extract(self, resolution, origin, robot_pose, max_follow_range, behind_ignore_range, download=True):

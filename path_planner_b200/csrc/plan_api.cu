@@ -22,6 +22,7 @@ cudaError_t reserve_pinned(T *&ptr, size_t &cap, size_t need)
         cap = need;
     return e;
 }
+std::vector<ppb::Query> *query_log(pp_handle h) { return static_cast<std::vector<ppb::Query> *>(h->plan_log); }
 // on-demand mirror of the SE2 volume for the host search (see pp_plan)
 struct BandPager
 {
@@ -113,6 +114,14 @@ extern "C" pp_status pp_plan(pp_handle h, const pp_plan_params *params, double r
     pp.max_iterations = params->max_iterations;
     pp.max_on_approach_iterations = params->max_on_approach_iterations;
     ppb::HybridAStar search(pp, h->W, h->H, resolution, origin_x, origin_y);
+    const bool exact_analytic = params->flags & PP_PLAN_EXACT_ANALYTIC, validate = params->flags & PP_PLAN_VALIDATE_PATH;
+    h->plan_stats = pp_plan_stats_t{};
+    if (h->plan_log_on && !h->plan_log)
+        h->plan_log = new std::vector<ppb::Query>();
+    if (h->plan_log)
+        query_log(h)->clear();
+    if (h->plan_log_on)
+        search.setQueryLog(query_log(h));
     const ppb::Pose start{start_xyt[0], start_xyt[1], start_xyt[2]}, goal{goal_xyt[0], goal_xyt[1], goal_xyt[2]};
 
     const auto tic = std::chrono::steady_clock::now();
@@ -144,6 +153,12 @@ extern "C" pp_status pp_plan(pp_handle h, const pp_plan_params *params, double r
     }
     else
         PP_CUDA(h, cudaMemcpyAsync(h->h_vol_mirror, h->d_vol, cells * params->n_theta, cudaMemcpyDeviceToHost, h->aux));
+    if (exact_analytic)
+    {
+        // the continuous-pose re-checks of the search read the costmap on the host
+        PP_CUDA(h, reserve_pinned(h->h_cost_mirror, h->cost_mirror_cap, cells));
+        PP_CUDA(h, cudaMemcpyAsync(h->h_cost_mirror, h->d_cost, cells, cudaMemcpyDeviceToHost, h->aux));
+    }
     st = pp_heuristic_build(h, gx, gy, params->cost_penalty, nullptr);
     if (st != PP_OK)
     {
@@ -169,9 +184,49 @@ extern "C" pp_status pp_plan(pp_handle h, const pp_plan_params *params, double r
         tb.fetch_band = &BandPager::fetch;
         tb.ctx = &pager;
     }
+    if (exact_analytic)
+    {
+        tb.exact_analytic = true;
+        tb.cost = h->h_cost_mirror;
+        tb.fp = h->fp.data();
+        tb.n_fp = static_cast<unsigned int>(h->fp.size() / 2);
+        tb.confirm_ctx = h;
+        tb.confirm_batch = [](void *ctx, const float *poses, unsigned int n, uint8_t *flags) {
+            std::vector<float> costs(n);
+            return pp_footprint_cost_batch(static_cast<pp_handle>(ctx), poses, n, costs.data(), flags) == PP_OK;
+        };
+    }
     std::vector<ppb::Pose> path;
     int iterations = 0;
     const bool found = search.plan(tb, start, goal, path, iterations);
+    {
+        const ppb::PlanStats &ps = search.stats();
+        h->plan_stats.lookups = ps.lookups;
+        h->plan_stats.analytic_attempts = ps.analytic_attempts;
+        h->plan_stats.analytic_confirm_batches = ps.analytic_confirm_batches;
+        h->plan_stats.exact_host_checks = ps.exact_host_checks;
+        h->plan_stats.false_collisions_overruled = ps.false_collisions_overruled;
+        h->plan_stats.false_free_caught = ps.false_free_caught;
+    }
+    if (found && validate)
+    {
+        // every pose of the path at its continuous position, exactly, in one batched launch
+        const std::vector<ppb::Pose> &pc = search.pathCells();
+        std::vector<float> poses(3 * pc.size()), costs(pc.size());
+        std::vector<uint8_t> flags(pc.size());
+        for (size_t i = 0; i < pc.size(); ++i)
+        {
+            poses[3 * i] = pc[i].x;
+            poses[3 * i + 1] = pc[i].y;
+            poses[3 * i + 2] = pc[i].theta;
+        }
+        pp_status vs = pp_footprint_cost_batch(h, poses.data(), static_cast<uint32_t>(pc.size()), costs.data(), flags.data());
+        if (vs != PP_OK)
+            return vs;
+        h->plan_stats.path_poses_checked = static_cast<uint32_t>(pc.size());
+        for (uint8_t f : flags)
+            h->plan_stats.path_poses_in_collision += f != 0;
+    }
     if (paged)
         cudaStreamSynchronize(h->aux);  // a prefetched band may still be on its way: part of the plan's time
     const auto toc = std::chrono::steady_clock::now();
@@ -193,4 +248,56 @@ extern "C" pp_status pp_plan(pp_handle h, const pp_plan_params *params, double r
     if (search_ms_out)
         *search_ms_out = std::chrono::duration<double, std::milli>(toc - mid).count();
     return PP_OK;
+}
+
+extern "C" pp_status pp_plan_stats(pp_handle h, pp_plan_stats_t *out)
+{
+    if (!h || !out)
+        return PP_ERR_INVALID;
+    *out = h->plan_stats;
+    return PP_OK;
+}
+
+extern "C" pp_status pp_plan_set_query_log(pp_handle h, int enable)
+{
+    if (!h)
+        return PP_ERR_INVALID;
+    h->plan_log_on = enable != 0;
+    if (!enable)
+        pp_plan_log_free(h);
+    return PP_OK;
+}
+
+extern "C" pp_status pp_plan_query_log(pp_handle h, float *poses_xyt_out, uint8_t *kind_out, uint8_t *flag_out, uint8_t *cost_out,
+                                       uint32_t max_queries, uint32_t *n_out)
+{
+    if (!h || !n_out)
+        return PP_ERR_INVALID;
+    static const std::vector<ppb::Query> none;
+    const std::vector<ppb::Query> &log = h->plan_log ? *query_log(h) : none;
+    *n_out = static_cast<uint32_t>(log.size());
+    const size_t n = std::min<size_t>(log.size(), max_queries);
+    for (size_t i = 0; i < n; ++i)
+    {
+        const ppb::Query &q = log[i];
+        if (poses_xyt_out)
+        {
+            poses_xyt_out[3 * i] = q.x;
+            poses_xyt_out[3 * i + 1] = q.y;
+            poses_xyt_out[3 * i + 2] = q.theta;
+        }
+        if (kind_out)
+            kind_out[i] = q.kind;
+        if (flag_out)
+            flag_out[i] = q.flag;
+        if (cost_out)
+            cost_out[i] = q.cost;
+    }
+    return PP_OK;
+}
+
+void pp_plan_log_free(pp_handle h)
+{
+    delete query_log(h);
+    h->plan_log = nullptr;
 }

@@ -79,6 +79,9 @@ pp_status pp_destroy(pp_handle h)
         cudaStreamSynchronize(h->aux);
     pp_se2_plan_free(h);
     pp_comm_destroy(h);
+    pp_plan_log_free(h);
+    if (h->h_cost_mirror)
+        cudaFreeHost(h->h_cost_mirror);
     cudaFree(h->d_cost);
     cudaFree(h->d_occ);
     cudaFree(h->d_infl);

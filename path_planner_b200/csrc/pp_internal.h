@@ -67,6 +67,11 @@ struct pp_ctx
     size_t vol_mirror_cap = 0;
     float *h_field_mirror = nullptr;
     size_t field_mirror_cap = 0;
+    uint8_t *h_cost_mirror = nullptr;  // exact analytic expansion: the costmap on the host
+    size_t cost_mirror_cap = 0;
+    pp_plan_stats_t plan_stats = {};
+    bool plan_log_on = false;
+    void *plan_log = nullptr;  // std::vector<ppb::Query>, owned by plan_api.cu (pp_plan_log_free)
 
     // K3 TEB
     double *d_pts = nullptr;
@@ -166,5 +171,6 @@ pp_status pp_ensure_stage(pp_handle h, size_t bytes);
 pp_status pp_se2_launch(pp_handle h, uint32_t x0, uint32_t y0, uint32_t x1, uint32_t y1);
 void pp_se2_plan_free(pp_handle h);
 void pp_comm_destroy(pp_handle h);
+void pp_plan_log_free(pp_handle h);
 // fills up to 8 destination volumes for a build (own first); returns how many
 int pp_volume_targets(pp_handle h, uint8_t **out);

@@ -202,7 +202,10 @@ bool CollisionChecker::checkFootPrintCollision(const float &x, const float &y, c
 {
     float cost = 0.0f;
     bool flag = false;
-    if (!lookup(x, y, theta, cost, flag) && !exactEval(x, y, theta, cost, flag))
+    const bool looked = lookup(x, y, theta, cost, flag);
+    if (looked && _log)
+        _log->push_back({x, y, theta, 1, static_cast<uint8_t>(flag), static_cast<uint8_t>(cost)});
+    if ((!looked || _exact_analytic) && !exactEval(x, y, theta, cost, flag))
     {
         std::fprintf(stderr, "CollisionChecker: GPU query failed: %s\n", lastError());
         return true;  // fail closed: report a collision rather than let the search walk through
@@ -214,7 +217,10 @@ bool CollisionChecker::checkFootPrintCollision(const float &x, const float &y, c
 bool CollisionChecker::checkAndGetFootprintCost(const float &x, const float &y, const float &theta, float &cost)
 {
     bool flag = false;
-    if (!lookup(x, y, theta, cost, flag) && !exactEval(x, y, theta, cost, flag))
+    const bool looked = lookup(x, y, theta, cost, flag);
+    if (looked && _log)
+        _log->push_back({x, y, theta, 0, static_cast<uint8_t>(flag), static_cast<uint8_t>(cost)});
+    if (!looked && !exactEval(x, y, theta, cost, flag))
     {
         std::fprintf(stderr, "CollisionChecker: GPU query failed: %s\n", lastError());
         cost = 254.0f;

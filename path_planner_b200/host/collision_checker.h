@@ -14,7 +14,8 @@
 //     This QUANTISES the pose to the cell centre; the reference evaluates the continuous pose.
 //   * exact mode (setExact(true), or before prepare()): every call is answered by
 //     pp_footprint_cost_batch for the continuous pose -- bit-identical to the reference, one kernel
-//     launch per call.
+//     launch per call. setExactAnalytic(true) does that for checkFootPrintCollision only, i.e. for the
+//     samples of analytic expansions, whose headings are not bin-aligned.
 //   * point queries and getCost read the host grid exactly like the reference (:174-214).
 #pragma once
 #include "commons.h"
@@ -57,6 +58,17 @@ public:
     // Use an externally built volume ([n_theta][H][W], stays owned by the caller) instead of the GPU's.
     void attachVolume(const uint8_t *volume, unsigned int n_theta, float heading_fraction);
     void setExact(bool exact) { _exact = exact; }
+    // checkFootPrintCollision -- the analytic-expansion samples of astar_hybrid.cpp:325, whose poses are not
+    // bin-aligned -- always at the continuous pose (pp_footprint_cost_batch); checkAndGetFootprintCost -- the
+    // motion primitives of :283 -- from the volume
+    void setExactAnalytic(bool exact) { _exact_analytic = exact; }
+    // record every footprint question with the volume's answer (quantisation statistics)
+    struct Query
+    {
+        float x, y, theta;
+        uint8_t kind, flag, cost;  // kind 0: checkAndGetFootprintCost, 1: checkFootPrintCollision
+    };
+    void setQueryLog(std::vector<Query> *log) { _log = log; }
     // Whole obstacle-heuristic field for a goal cell (replaces AstarHybrid::cacheObstacleHeuristic's table).
     bool buildHeuristicField(unsigned int goal_x, unsigned int goal_y, float cost_penalty, std::vector<float> &field);
     const char *lastError() const;
@@ -73,7 +85,8 @@ private:
     costmap_2d::Costmap2D *_costmap;
     bool _hole;
     pp_ctx *_h;
-    bool _uploaded, _footprint_dirty, _exact;
+    bool _uploaded, _footprint_dirty, _exact, _exact_analytic = false;
+    std::vector<Query> *_log = nullptr;
     std::vector<uint8_t> _volume_mirror;
     const uint8_t *_volume;
     unsigned int _n_theta;

@@ -141,7 +141,7 @@ void HybridAStar::growGraph()
 
 // Volume lookup in place of collision_checker.cpp:126-172: cell of the pose, nearest heading bin.
 // Returns the collision flag; poses outside the map count as collisions (the search never asks).
-bool HybridAStar::footprint(const Tables &tb, float x, float y, float theta_rad, float &cost) const
+bool HybridAStar::footprint(const Tables &tb, float x, float y, float theta_rad, float &cost, uint8_t kind) const
 {
     const float fx = std::floor(x), fy = std::floor(y);
     if (!(fx >= 0.0f && fy >= 0.0f && fx < static_cast<float>(_W) && fy < static_cast<float>(_H)))
@@ -149,6 +149,7 @@ bool HybridAStar::footprint(const Tables &tb, float x, float y, float theta_rad,
         cost = 254.0f;
         return true;
     }
+    ++_stats.lookups;
     if (tb.band_ready)
     {
         const unsigned int band = static_cast<unsigned int>(fy) >> tb.band_shift;
@@ -161,7 +162,29 @@ bool HybridAStar::footprint(const Tables &tb, float x, float y, float theta_rad,
         t += _n_theta;
     const uint8_t v = tb.volume[(static_cast<size_t>(t) * _H + static_cast<size_t>(fy)) * _W + static_cast<size_t>(fx)];
     cost = static_cast<float>(v);
+    if (_log)
+        _log->push_back({x, y, theta_rad, kind, static_cast<uint8_t>(v >= 253), v});
     return v >= 253;
+}
+
+// collision_checker.cpp:126-142 at a continuous pose, on the host copy of the costmap: the same float
+// expression, one rounded operation at a time (this file is compiled without contraction), cosf / sinf of
+// the host libm like the reference build; a sample outside the map is skipped (:134). The float -> unsigned
+// conversion of a negative floor() wraps to a huge index there and fails the bounds test: a sign test here.
+bool HybridAStar::exactCollisionHost(const Tables &tb, float x, float y, float theta_rad) const
+{
+    const float c = cosf(theta_rad), s = sinf(theta_rad);
+    for (unsigned int p = 0; p < tb.n_fp; ++p)
+    {
+        const float px = static_cast<float>(tb.fp[2 * p]), py = static_cast<float>(tb.fp[2 * p + 1]);
+        const float a = px * c, b = py * s, u = x + a, xn = u - b;
+        const float a2 = px * s, b2 = py * c, u2 = y + a2, yn = u2 + b2;
+        const float fx = std::floor(xn), fy = std::floor(yn);
+        if (fx >= 0.0f && fy >= 0.0f && fx < static_cast<float>(_W) && fy < static_cast<float>(_H) &&
+            tb.cost[static_cast<size_t>(fy) * _W + static_cast<size_t>(fx)] >= 253)
+            return true;
+    }
+    return false;
 }
 
 // astar_hybrid.cpp:242-247 with :82-92 (motion heuristic) and the table hit of :166-183
@@ -255,7 +278,10 @@ HybridAStar::Node *HybridAStar::analyticExpansion(const Tables &tb, Node *n)
         unsigned int index;
         Pose at;
     };
+    ++_stats.analytic_attempts;
+    const bool exact = tb.exact_analytic && tb.cost && tb.fp && tb.confirm_batch;
     std::vector<Step> steps;
+    std::vector<float> samples;  // exact mode: x, y, yaw of every sample that still needs an exact answer
     for (float i = 1; i < intervals; i += 1.0f)
     {
         const SE2 q = _curves->interpolate(from, to, i / intervals);
@@ -264,11 +290,39 @@ HybridAStar::Node *HybridAStar::analyticExpansion(const Tables &tb, Node *n)
         const unsigned int xi = static_cast<unsigned int>(q.x), yi = static_cast<unsigned int>(q.y);
         if (xi <= 0 || xi >= _W - 1 || yi <= 0 || yi >= _H - 1)
             return nullptr;
+        const float sx = static_cast<float>(q.x), sy = static_cast<float>(q.y), syaw = static_cast<float>(q.yaw);
         float ignored;
-        if (footprint(tb, static_cast<float>(q.x), static_cast<float>(q.y), static_cast<float>(q.yaw), ignored))
+        if (footprint(tb, sx, sy, syaw, ignored, 1))
+        {
+            if (!exact)
+                return nullptr;
+            // the volume speaks for the cell centre and the nearest bin: ask the continuous pose
+            ++_stats.exact_host_checks;
+            if (exactCollisionHost(tb, sx, sy, syaw))
+                return nullptr;
+            ++_stats.false_collisions_overruled;
+        }
+        else if (exact)
+        {
+            samples.push_back(sx);
+            samples.push_back(sy);
+            samples.push_back(syaw);
+        }
+        steps.push_back({indexOf(xi, yi, static_cast<unsigned int>(heading)), {sx, sy, heading}});
+    }
+    if (exact && !samples.empty())
+    {
+        // every sample passed the filter: one batched exact evaluation decides
+        std::vector<uint8_t> flags(samples.size() / 3);
+        ++_stats.analytic_confirm_batches;
+        if (!tb.confirm_batch(tb.confirm_ctx, samples.data(), static_cast<unsigned int>(flags.size()), flags.data()))
+            return nullptr;  // a failed query fails closed
+        unsigned int hits = 0;
+        for (uint8_t f : flags)
+            hits += f != 0;
+        _stats.false_free_caught += hits;
+        if (hits)
             return nullptr;
-        steps.push_back({indexOf(xi, yi, static_cast<unsigned int>(heading)),
-                         {static_cast<float>(q.x), static_cast<float>(q.y), heading}});
     }
     if (steps.empty())
         return nullptr;
@@ -309,6 +363,8 @@ bool HybridAStar::backtrace(Node *n, std::vector<Pose> &path) const
 bool HybridAStar::plan(const Tables &tb, const Pose &start_world, const Pose &goal_world, std::vector<Pose> &path, int &iterations)
 {
     path.clear();
+    _path_cells.clear();
+    _stats = PlanStats();
     iterations = 0;
     // astar_hybrid.cpp:392-433: world -> cells (costmap_2d::worldToMap rejects poses outside the map)
     auto inside = [&](const Pose &p) {
@@ -418,6 +474,8 @@ bool HybridAStar::plan(const Tables &tb, const Pose &start_world, const Pose &go
         path.clear();
         return false;
     }
+    for (const Pose &p : path)
+        _path_cells.push_back({p.x, p.y, p.theta * _bin});
     // fromCellToWorld, :516-528, then the two end poses are replaced by the requested ones (:428-429)
     for (Pose &p : path)
     {

@@ -52,6 +52,36 @@ struct Tables
     unsigned int band_shift = 0;
     void (*fetch_band)(void *ctx, unsigned int band) = nullptr;
     void *ctx = nullptr;
+    // Exact analytic expansion (optional). The reference checks every sample of an analytic expansion at the
+    // CONTINUOUS pose (astar_hybrid.cpp:315-329 -> collision_checker.cpp:126-142); the volume answers for the
+    // cell centre and the nearest heading bin. With exact_analytic set, the volume is only a filter: samples it
+    // flags are re-checked exactly on the host against `cost` (the expansion fails if one of them really
+    // collides), and an expansion that survives is confirmed by ONE batched exact evaluation of all its samples
+    // (confirm_batch: pp_footprint_cost_batch on the GPU). The outcome of every expansion then equals the
+    // reference's.
+    bool exact_analytic = false;
+    const uint8_t *cost = nullptr;   // host copy of the costmap [H][W]
+    const int32_t *fp = nullptr;     // footprint offsets x0,y0,x1,y1,... (cells)
+    unsigned int n_fp = 0;
+    bool (*confirm_batch)(void *ctx, const float *poses_xyt, unsigned int n, uint8_t *flags_out) = nullptr;
+    void *confirm_ctx = nullptr;
+};
+
+struct Query  // one footprint question of a search, for the quantisation statistics (pp_plan_query_log)
+{
+    float x, y, theta;     // cells, cells, radians: what the reference would pass to its CollisionChecker
+    uint8_t kind;          // 0 = checkAndGetFootprintCost (primitive / end pose), 1 = checkFootPrintCollision (analytic sample)
+    uint8_t flag, cost;    // what the volume lookup answered
+};
+
+struct PlanStats
+{
+    unsigned long long lookups = 0;            // volume lookups
+    unsigned int analytic_attempts = 0;        // analytic expansions tried
+    unsigned int analytic_confirm_batches = 0; // batched exact confirmations (exact mode)
+    unsigned int exact_host_checks = 0;        // samples re-checked exactly on the host (exact mode)
+    unsigned int false_collisions_overruled = 0;  // ... of which the exact check said free
+    unsigned int false_free_caught = 0;        // samples the volume called free that the exact batch rejected
 };
 
 class HybridAStar
@@ -67,6 +97,10 @@ public:
     // world poses in (metres, metres, radians); path runs goal -> start like the reference's
     // (path_planner_ros.cpp:140 reverses it afterwards)
     bool plan(const Tables &tables, const Pose &start_world, const Pose &goal_world, std::vector<Pose> &path, int &iterations);
+    // after plan(): the poses of the path as the search held them (cells, cells, radians), goal -> start
+    const std::vector<Pose> &pathCells() const { return _path_cells; }
+    const PlanStats &stats() const { return _stats; }
+    void setQueryLog(std::vector<Query> *log) { _log = log; }
 
 private:
     struct Node
@@ -89,7 +123,8 @@ private:
     Node *node(unsigned int index);
     unsigned int indexOf(unsigned int x, unsigned int y, unsigned int t) const { return t + x * _n_theta + y * _n_theta * _W; }
     void wrapHeading(float &h) const;
-    bool footprint(const Tables &tb, float x, float y, float theta_rad, float &cost) const;
+    bool footprint(const Tables &tb, float x, float y, float theta_rad, float &cost, uint8_t kind = 0) const;
+    bool exactCollisionHost(const Tables &tb, float x, float y, float theta_rad) const;
     float heuristic(const Tables &tb, const Pose &at) const;
     float travelCost(const Node *from, const Node *to) const;
     void expand(const Tables &tb, Node *n, std::vector<Node *> &out);
@@ -121,5 +156,8 @@ private:
         CurveSpace::HeadingTrig trig{1.0, 0.0, 0.0, 1.0};
     };
     mutable std::vector<HeadingEntry> _heading_cache;
+    std::vector<Pose> _path_cells;
+    mutable PlanStats _stats;
+    std::vector<Query> *_log = nullptr;
 };
 }  // namespace ppb

@@ -45,6 +45,9 @@ void B200GlobalPlanner::initialize(std::string name, costmap_2d::Costmap2DROS *c
     std::string motion_type;
     pp.param<std::string>("motion_type", motion_type, "ReedsShepp");
     nh.param<int>("device", device, 0);
+    bool exact_analytic;
+    nh.param<bool>("exact_analytic_expansion", exact_analytic, true);  // continuous-pose checks of analytic expansions, like the reference
+    _params.flags = exact_analytic ? PP_PLAN_EXACT_ANALYTIC : 0u;
     _params.n_theta = static_cast<uint32_t>(bins);
     _params.max_iterations = static_cast<uint32_t>(max_iterations);
     _params.max_on_approach_iterations = static_cast<uint32_t>(max_on_approach_iterations);
