@@ -492,6 +492,27 @@ def main():
     }
     if gathered:
         line["gathered"] = gathered
+    if rank == 0 and world == 1:
+        # the same build with the other footprint kinds (BASELINE config 2 uses the asymmetric box: no twin bins)
+        line["footprints"] = {}
+        hf = capi.Handle(local_rank)
+        hf.costmap_upload(cost_pinned, pinned=True)
+        for name, (bnd, hole) in {"box_-0.2_-0.25_0.6_0.25_rim": ([-0.2, -0.25, 0.6, 0.25], True), "rect_0.64x0.46_solid": ([0.64, 0.46], False),
+                                  "circle_0.35_rim": ([0.35], True)}.items():
+            hf.footprint_from_boundary(RES, bnd, hole)
+            for _ in range(4):
+                hf.se2_volume_build(N_THETA)
+            hf.sync()
+            ms = 0.0
+            for _ in range(10):
+                hf.l2_flush()
+                hf.timer_start()
+                hf.se2_volume_build(N_THETA)
+                ms += hf.timer_stop() / 10
+            st = hf.se2_volume_stats()
+            line["footprints"][name] = {"ms_per_build": ms, "roofline_frac": (W * H * (1 + N_THETA)) / (ms * 1e-3) / 1e9 / peak,
+                                        "samples_per_cell": st["samples_per_cell"], "generic_tiles": st["generic_tiles"]}
+        hf.close()
 
     if rank == 0:
         # heuristic field and TEB queries stay on one GPU
@@ -516,6 +537,21 @@ def main():
             r = hp.plan(RES, (0.0, 0.0), sc["start"], sc["goal"], sc["params"])
             line["plan"][name] = {"ms": r["tables_ms"] + r["search_ms"], "tables_ms": r["tables_ms"], "search_ms": r["search_ms"],
                                   "iterations": r["iterations"], "path_poses": int(len(r["path"])), "found": bool(r["ok"])}
+            # the same plan with the analytic expansion decided at continuous poses and the path validated exactly,
+            # and how often the volume lookup (cell centre, nearest bin) disagrees with the continuous-pose check
+            hp.plan_set_query_log(True)
+            rx = hp.plan(RES, (0.0, 0.0), sc["start"], sc["goal"], dict(sc["params"], exact_analytic=True, validate_path=True))
+            qp, qk, qf, qc = hp.plan_query_log()
+            hp.plan_set_query_log(False)
+            xc_, xf_ = hp.footprint_cost_batch(qp)
+            prim = qk == 0
+            line["plan"][name]["exact_analytic"] = {"ms": rx["tables_ms"] + rx["search_ms"], "iterations": rx["iterations"],
+                                                    "path_poses_in_collision": rx["stats"]["path_poses_in_collision"],
+                                                    "path_poses_checked": rx["stats"]["path_poses_checked"],
+                                                    "confirm_batches": rx["stats"]["analytic_confirm_batches"]}
+            line["plan"][name]["quantisation"] = {"questions": int(len(qp)), "primitive_false_free": float(((qf == 0) & (xf_ == 1) & prim).mean()),
+                                                  "primitive_false_collision": float(((qf == 1) & (xf_ == 0) & prim).mean()),
+                                                  "cost_differs": float((qc != xc_.astype(np.uint8)).mean())}
         hp.close()
         # K0: costmap upload over the host link: pinned, pageable (staged), one dirty rectangle
         hu = capi.Handle(local_rank)
@@ -572,7 +608,7 @@ def main():
                           "inflation_cells": 10, "algorithmic_bytes": 2 * W * H,
                           "note": "full_recompute_ms includes the 101-byte cost-table upload that a parameter change triggers"}
         hi.close()
-        from path_planner_b200.synth import make_teb_scene
+        from path_planner_b200.synth import make_teb_scene, make_costmap
         pts, poses = make_teb_scene(10000, 100, seed=0)
         h.radius_topk(pts, poses, 0.9574, 10)
         t = time.perf_counter()
@@ -581,6 +617,29 @@ def main():
             h.radius_topk(None, poses, 0.9574, 10)
         line["teb"] = {"us_per_round_e2e": 1e6 * (time.perf_counter() - t) / rounds,
                        "workload": "100 poses x 10000 points, K=10, host buffers in and out"}
+        # K3b over larger follower windows: candidates extracted from a costmap stay column-ordered on the device and a
+        # query scans only the columns in reach; `full_scan` is the same kernel without the pruning
+        sweep = {}
+        hs_ = capi.Handle(local_rank)
+        for target, (ww, cov) in {"1e4": (500, 0.035), "1e5": (1000, 0.09), "1e6": (2400, 0.16)}.items():
+            cm = make_costmap(ww, ww, seed=11, coverage=cov, unknown_frac=0.0)
+            hs_.costmap_upload(cm)
+            centre = ww * RES / 2
+            n_pts = hs_.obstacles_extract(RES, (0.0, 0.0), (centre, centre, 0.0), 1e6, 0.0, download=False)
+            q = np.stack([np.linspace(0.1 * ww * RES, 0.9 * ww * RES, 100), centre + 2.0 * np.sin(np.linspace(0, 6, 100))], 1)
+            res_ = {}
+            for key, env in (("pruned_us", None), ("full_scan_us", "1")):
+                if env:
+                    os.environ["PP_TEB_NO_PRUNE"] = env
+                hs_.radius_topk(None, q, 0.9574, 10)
+                t = time.perf_counter()
+                for _ in range(10):
+                    hs_.radius_topk(None, q, 0.9574, 10)
+                res_[key] = 1e6 * (time.perf_counter() - t) / 10
+                os.environ.pop("PP_TEB_NO_PRUNE", None)
+            sweep[target] = dict(points=int(n_pts), window_cells=ww, **res_)
+        hs_.close()
+        line["teb"]["n_sweep_100_queries"] = sweep
         # N3: errors + numeric Jacobians of all obstacle edges of one optimiser iteration (association on the device)
         poses3 = np.ascontiguousarray(np.concatenate([poses, 0.6 * np.cos(poses[:, :1])], axis=1))
         h.robot_model_set([0.72, 0.50])

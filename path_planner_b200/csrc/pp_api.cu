@@ -4,6 +4,7 @@
 
 #include <cmath>
 #include <cstdarg>
+#include <cstdlib>
 #include <cstring>
 #include <algorithm>
 
@@ -276,6 +277,8 @@ static pp_status commit_footprint(pp_handle h)
         r2 = std::max(r2, x * x + y * y);
     }
     h->reach = static_cast<int>(std::ceil(std::sqrt(r2)));
+    if (const char *bias = getenv("PP_DEBUG_REACH_BIAS"))  // test hook: a deliberately short reach must be refused by the build
+        h->reach = std::max(0, h->reach + atoi(bias));
     PP_REQUIRE(h, h->reach <= 120, PP_ERR_RANGE, "footprint reach %d cells exceeds the limit of 120", h->reach);
     PP_CUDA(h, cudaSetDevice(h->device));
     PP_CUDA(h, pp_reserve(h->d_fp, h->fp_cap, static_cast<size_t>(2) * P));

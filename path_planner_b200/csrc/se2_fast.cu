@@ -836,6 +836,7 @@ struct Se2Plan
     // geometry
     bool usable = false;
     int R = 0, PW = 0, rows = 0, table_words = 0, n_tables = 0;
+    int max_abs_offset = 0;  // largest |sample offset| of any bin, point, column or row (exact, from the reference expression)
     size_t smem_bytes = 0;
     Library lib;
     int lib_id = 0;
@@ -900,7 +901,7 @@ inline int ref_y_index(float y, float px, float py, float c, float s)
 }
 
 AxisClasses classify_axis(bool is_x, uint32_t n, float sample_off, const std::vector<int32_t> &fp, float c, float s,
-                          std::vector<int8_t> &scratch)
+                          std::vector<int8_t> &scratch, int &max_abs_offset)
 {
     const size_t P = fp.size() / 2;
     scratch.resize(P * n);
@@ -913,7 +914,8 @@ AxisClasses classify_axis(bool is_x, uint32_t n, float sample_off, const std::ve
             const float pos = static_cast<float>(i) + sample_off;
             const int idx = is_x ? ref_x_index(pos, px, py, c, s) : ref_y_index(pos, px, py, c, s);
             int d = idx - static_cast<int>(i);
-            d = std::max(-127, std::min(127, d));
+            max_abs_offset = std::max(max_abs_offset, std::abs(d));
+            d = std::max(-127, std::min(127, d));  // storage only: a plan with such offsets is never used (R > MAX_R below)
             dst[i] = static_cast<int8_t>(d);
         }
     }
@@ -970,8 +972,6 @@ pp_status build_plan(pp_handle h, int effort)
     pl->ot = h->ot;
     pl->fp = h->fp;
     pl->usable = false;
-    if (h->W % 4 != 0)
-        return PP_OK;  // rows would not be 4-byte aligned: leave everything to the generic kernel
     const uint32_t nt = h->n_theta;
     pl->tiles_x = (h->W + FT_W - 1) / FT_W;
     pl->tiles_y = (h->H + FT_H - 1) / FT_H;
@@ -983,8 +983,8 @@ pp_status build_plan(pp_handle h, int effort)
     for (uint32_t t = 0; t < nt; ++t)
     {
         const float c = h->host_trig[t].x, s = h->host_trig[t].y;
-        xc[t] = classify_axis(true, h->W, h->ox, h->fp, c, s, scratch);
-        yc[t] = classify_axis(false, h->H, h->oy, h->fp, c, s, scratch);
+        xc[t] = classify_axis(true, h->W, h->ox, h->fp, c, s, scratch, pl->max_abs_offset);
+        yc[t] = classify_axis(false, h->H, h->oy, h->fp, c, s, scratch, pl->max_abs_offset);
         for (int k = 0; k < xc[t].n_classes; ++k)
             for (int d : xc[t].offs[k])
                 R = std::max(R, std::abs(d));
@@ -994,6 +994,8 @@ pp_status build_plan(pp_handle h, int effort)
     }
     if (R > MAX_R)
         return PP_OK;
+    if (h->W % 4 != 0)
+        return PP_OK;  // rows would not be 4-byte aligned: leave everything to the generic kernel
     // 2. geometry: the staged halo is a template parameter of the kernel, the row pitch follows from it
     const int halo = halo_for(R);
     pl->R = halo;
@@ -1194,7 +1196,7 @@ bool encode_volume_map(CUtensorMap *map, uint8_t *vol, uint32_t W, uint32_t H, u
 }
 }  // namespace
 
-pp_status pp_se2_launch_fast(pp_handle h, uint32_t x0, uint32_t y0, uint32_t x1, uint32_t y1)
+pp_status pp_se2_prepare_plan(pp_handle h)
 {
     if (!plan_matches(h->plan, h))
     {
@@ -1211,6 +1213,16 @@ pp_status pp_se2_launch_fast(pp_handle h, uint32_t x0, uint32_t y0, uint32_t x1,
         if (s != PP_OK)
             return s;
     }
+    // Both kernels stage reach + 2 cells around a tile; that this covers every sample follows from
+    // |p| <= reach and a sample offset in [-1, 1]. The planner has evaluated every offset exactly, so a
+    // configuration that broke the bound is refused here instead of being sampled wrongly.
+    PP_REQUIRE(h, h->plan->max_abs_offset <= h->reach + 2, PP_ERR_RANGE,
+               "a footprint sample lies %d cells from its pose, beyond the staged reach of %d + 2", h->plan->max_abs_offset, h->reach);
+    return PP_OK;
+}
+
+pp_status pp_se2_launch_fast(pp_handle h, uint32_t x0, uint32_t y0, uint32_t x1, uint32_t y1)
+{
     Se2Plan *pl = h->plan;
     if (!pl->usable)
         return PP_INTERNAL_DECLINED;

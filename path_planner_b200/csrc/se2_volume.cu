@@ -107,7 +107,7 @@ __global__ void __launch_bounds__(GT_THREADS) se2_generic_kernel(GenericArgs a)
                 const float x = __fadd_rn(static_cast<float>(gx), a.ox);
                 const float xn = __fsub_rn(__fadd_rn(x, __fmul_rn(px, cs.x)), __fmul_rn(py, cs.y));
                 int off = __float2int_rd(xn) - gx;
-                off = max(-R, min(R, off));
+                off = max(-R, min(R, off));  // memory safety only: the host refuses configurations that would need it (pp_se2_prepare_plan)
                 xo[i] = static_cast<int8_t>(off);
             }
             for (int i = tid; i < pc * GT_H; i += GT_THREADS)
@@ -118,7 +118,7 @@ __global__ void __launch_bounds__(GT_THREADS) se2_generic_kernel(GenericArgs a)
                 const float y = __fadd_rn(static_cast<float>(gy), a.oy);
                 const float yn = __fadd_rn(__fadd_rn(y, __fmul_rn(px, cs.y)), __fmul_rn(py, cs.x));
                 int off = __float2int_rd(yn) - gy;
-                off = max(-R, min(R, off));
+                off = max(-R, min(R, off));  // see above
                 yo[i] = static_cast<int8_t>(off);
             }
             __syncthreads();
@@ -219,6 +219,11 @@ pp_status pp_se2_launch(pp_handle h, uint32_t x0, uint32_t y0, uint32_t x1, uint
     h->stat_samples_per_cell = 0.0;
     if (x1 <= x0 || y1 <= y0 || h->bins.empty())
         return PP_OK;
+    {
+        pp_status s = pp_se2_prepare_plan(h);
+        if (s != PP_OK)
+            return s;
+    }
     if (h->vol_mode == 0)
     {
         pp_status s = pp_se2_launch_fast(h, x0, y0, x1, y1);

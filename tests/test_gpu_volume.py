@@ -270,3 +270,22 @@ def test_build_of_a_scattered_bin_set(handle, golden):
     full = handle.se2_volume_download()
     for t in set(bins):
         assert np.array_equal(got2[t], full[t]), t
+
+
+def test_short_reach_is_refused_not_clamped(monkeypatch):
+    """Both kernels stage reach + 2 cells around a tile. If the reach were ever short of a sample offset the
+    result would be wrong, so such a configuration is refused (PP_ERR_RANGE) by either kernel variant. The
+    bound cannot be broken through the ABI (the reach is derived from the footprint); a debug knob shortens it."""
+    from path_planner_b200 import capi
+    cost = make_costmap(200, 150, seed=2)
+    for mode in (0, 1):
+        monkeypatch.setenv("PP_DEBUG_REACH_BIAS", "-4")
+        h = capi.Handle(0)
+        h.costmap_upload(cost)
+        h.footprint_from_boundary(RES, *FOOTPRINTS["rect_hole"])
+        monkeypatch.delenv("PP_DEBUG_REACH_BIAS")
+        h.se2_volume_set_mode(mode)
+        with pytest.raises(capi.PPError) as ei:
+            h.se2_volume_build(72)
+        assert ei.value.status == 4  # PP_ERR_RANGE
+        h.close()
