@@ -539,6 +539,8 @@ def main():
                                   "iterations": r["iterations"], "path_poses": int(len(r["path"])), "found": bool(r["ok"])}
             # the same plan with the analytic expansion decided at continuous poses and the path validated exactly,
             # and how often the volume lookup (cell centre, nearest bin) disagrees with the continuous-pose check
+            for _ in range(2):  # (a handle re-plans its volume build thoroughly on the third use of a configuration: not timed)
+                hp.plan(RES, (0.0, 0.0), sc["start"], sc["goal"], dict(sc["params"], exact_analytic=True, validate_path=True))
             hp.plan_set_query_log(True)
             rx = hp.plan(RES, (0.0, 0.0), sc["start"], sc["goal"], dict(sc["params"], exact_analytic=True, validate_path=True))
             qp, qk, qf, qc = hp.plan_query_log()
