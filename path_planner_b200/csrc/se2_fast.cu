@@ -1084,6 +1084,15 @@ pp_status build_plan(pp_handle h, int effort)
                 pl->lists.insert(pl->lists.end(), it->second.begin(), it->second.end());
             }
 
+    // Every shared-memory address of the output phase is (thread base) + (list word) + (row of the unit) * pitch,
+    // with host-made list words: checked here once for all launches (the kernel has no bounds tests in that loop).
+    for (uint32_t w : pl->lists)
+    {
+        const uint32_t first = w / 4, last = first + static_cast<uint32_t>(FT_H - 1) * pl->PW + 31;
+        PP_REQUIRE(h, w % 4 == 0 && last < static_cast<uint32_t>(pl->n_tables) * pl->table_words, PP_ERR_STATE,
+                   "internal: a sample list addresses word %u of %u table words", last, pl->n_tables * pl->table_words);
+    }
+
     // 6. tile classes and the generic work list
     pl->h_xclass.assign(static_cast<size_t>(nt) * pl->tiles_x, 255);
     pl->h_yclass.assign(static_cast<size_t>(nt) * pl->tiles_y, 255);
