@@ -592,14 +592,15 @@ using Library = std::vector<Recipe>;
 // for the footprint at hand and truncates it to the tables that fit.
 //   STAIRS  2-runs along x, y and the two diagonals, four 4-cell "stair" bricks (two 2-runs offset by
 //           (2,+-1) or (+-1,2)) that follow rasterised oblique edges, then runs of 4 along x and y
-//           and of 8 along x (the stairs come first so that a truncated library keeps them)
+//           and of 8 along x (the stairs come first so that a truncated library keeps them), then the two
+//           diagonals of 4 and the run of 8 along y (found by tools/lib_search.cpp as the next best bricks)
 //   RUNS3   runs of 2/3/6 along x and y, diagonals of 2/3/4
 //   BLOCKS  rectangles 2x2 .. 8x8 for solid footprints
 //   RUNS    runs of 2/4/8 along x and y, diagonals of 2/4
 const std::vector<Library> &fixed_libraries()
 {
     static const std::vector<Library> libs = {
-        {{0, 0, 0, 0}, {0, 0, 1, 0}, {0, 0, 0, 1}, {0, 0, 1, 1}, {0, 0, 1, -1}, {1, 1, 2, 1}, {1, 1, 2, -1}, {2, 2, 1, 2}, {2, 2, -1, 2}, {1, 1, 2, 0}, {2, 2, 0, 2}, {9, 9, 4, 0}},
+        {{0, 0, 0, 0}, {0, 0, 1, 0}, {0, 0, 0, 1}, {0, 0, 1, 1}, {0, 0, 1, -1}, {1, 1, 2, 1}, {1, 1, 2, -1}, {2, 2, 1, 2}, {2, 2, -1, 2}, {1, 1, 2, 0}, {2, 2, 0, 2}, {9, 9, 4, 0}, {4, 4, 2, -2}, {3, 3, 2, 2}, {10, 10, 0, 4}},
         {{0, 0, 0, 0}, {0, 0, 1, 0}, {0, 0, 0, 1}, {0, 0, 1, 1}, {0, 0, 1, -1}, {1, 0, 2, 0}, {2, 0, 0, 2}, {3, 0, 2, 2}, {4, 0, 2, -2}, {3, 3, 2, 2}, {5, 5, 3, 0}, {6, 6, 0, 3}},
         {{0, 0, 0, 0}, {0, 0, 1, 0}, {0, 0, 0, 1}, {1, 1, 0, 1}, {1, 1, 2, 0}, {2, 2, 0, 2}, {3, 3, 2, 0}, {4, 4, 4, 0}, {5, 5, 0, 4}, {6, 6, 0, 2}, {9, 9, 4, 0}, {10, 10, 0, 4}},
         {{0, 0, 0, 0}, {0, 0, 1, 0}, {0, 0, 0, 1}, {0, 0, 1, 1}, {0, 0, 1, -1}, {1, 1, 2, 0}, {2, 2, 0, 2}, {3, 3, 2, 2}, {4, 4, 2, -2}, {5, 5, 4, 0}, {6, 6, 0, 4}},

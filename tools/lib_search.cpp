@@ -163,16 +163,31 @@ int main(int argc, char **argv)
         int a, b, du, dv;
     };
     std::vector<Brick> lib{{{{0, 0}}, 0, 0, 0, 0}};
+    if (argc > 3 && std::string(argv[3]) == "stairs")
+    {
+        // seed: the STAIRS library of se2_fast.cu (12 tables)
+        const int R[11][4] = {{0, 0, 1, 0}, {0, 0, 0, 1}, {0, 0, 1, 1}, {0, 0, 1, -1}, {1, 1, 2, 1}, {1, 1, 2, -1}, {2, 2, 1, 2}, {2, 2, -1, 2}, {1, 1, 2, 0}, {2, 2, 0, 2}, {9, 9, 4, 0}};
+        for (auto &r : R)
+        {
+            Offsets p = lib[r[0]].pts;
+            for (auto &q : lib[r[1]].pts)
+                p.emplace_back(q.first + r[2], q.second + r[3]);
+            std::sort(p.begin(), p.end());
+            p.erase(std::unique(p.begin(), p.end()), p.end());
+            lib.push_back({p, r[0], r[1], r[2], r[3]});  // NOT normalised: recipes refer to table a's origin
+        }
+    }
     std::vector<std::vector<Mask>> cur(sets.size());  // placements of the current library per set
     for (size_t s = 0; s < sets.size(); ++s)
-        placements(sets[s], lib[0].pts, cur[s]);
+        for (auto &b : lib)
+            placements(sets[s], normalise(b.pts), cur[s]);
     auto total = [&](const std::vector<std::vector<Mask>> &c) {
         long tot = 0;
         for (size_t s = 0; s < sets.size(); ++s)
             tot += greedy(c[s], (int)sets[s].S.size());
         return tot;
     };
-    printf("K=1 total %ld (%.2f per set)\n", total(cur), (double)total(cur) / sets.size());
+    printf("K=%zu total %ld (%.2f per set)\n", lib.size(), total(cur), (double)total(cur) / sets.size());
     while ((int)lib.size() < K)
     {
         // candidates
