@@ -466,15 +466,16 @@ def main():
     peak, peak_src = measured_peak_gbs()
     alg_bytes = W * (y1 - y0) * (1 + N_THETA)   # read the costmap once, write every output byte once (this rank's rows)
     achieved = alg_bytes / (my_ms * 1e-3) / 1e9
-    traffic = None
-    tpath = os.path.join(ROOT, "profiles", "se2_traffic.json")
+    traffic = traffic_src = None
+    tpath = os.path.join(ROOT, "profiles", "se2_traffic.json")  # written by tools/make_traffic_json.py from an ncu capture
     if os.path.exists(tpath):
         try:
-            traffic = json.load(open(tpath)).get("dram_bytes_per_launch")
+            tj = json.load(open(tpath))
+            traffic, traffic_src = tj.get("dram_bytes_per_launch"), tj.get("source")
         except Exception:
             traffic = None
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": traffic, "peak_source": peak_src, "kernel": "se2 volume build (all launches of one pp_se2_volume_build)",
+                "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src, "kernel": "se2 volume build (all launches of one pp_se2_volume_build)",
                 "algorithmic_bytes_per_launch": alg_bytes, "ms_per_launch": my_ms,
                 "frac_of_nominal_8TBs": achieved / 8000.0}
 
