@@ -10,6 +10,9 @@ n = int(sys.argv[2]) if len(sys.argv) > 2 else 10
 fp = {"rect": ([0.64, 0.46], True), "box": ([-0.2, -0.25, 0.6, 0.25], True), "solid": ([0.64, 0.46], False)}[kind]
 cost = make_costmap(4096, 4096, seed=1, pockets=[(3000, 1000, 6)])
 h = capi.Handle(0); h.costmap_upload(cost); h.footprint_from_boundary(0.05, fp[0], fp[1])
+if os.environ.get('ROWS'):
+    y0, y1 = map(int, os.environ['ROWS'].split(','))
+    h.se2_volume_set_rows(y0, y1)
 for _ in range(4):
     h.se2_volume_build(72)
 h.sync()
