@@ -27,7 +27,13 @@ struct ExtractArgs
     const uint8_t *cost;
     uint32_t W, H;
     double res, origin_x, origin_y, robot_x, robot_y, dir_x, dir_y, max_distance, behind_range;
+    // candidates whose distance is within rounding of behind_range (see candidate()): collected in the first
+    // pass (count word + (i, j) pairs), decided by the host with its own hypot, handed back as overrides
+    uint32_t *uncertain;         // [0] count, then (i, j) pairs; null in the passes that use overrides
+    const uint32_t *overrides;   // (i, j, keep) triples
+    uint32_t n_overrides;
 };
+constexpr uint32_t MAX_UNCERTAIN = 256;
 
 __device__ __forceinline__ bool candidate(const ExtractArgs &a, uint32_t i, uint32_t j, double &wx, double &wy)
 {
@@ -39,10 +45,29 @@ __device__ __forceinline__ bool candidate(const ExtractArgs &a, uint32_t i, uint
     const double dx = __dsub_rn(wx, a.robot_x), dy = __dsub_rn(wy, a.robot_y);
     if (fabs(dx) > a.max_distance || fabs(dy) > a.max_distance)
         return false;
-    const double distance = hypot(dx, dy);
-    if (distance > a.behind_range && __dadd_rn(__dmul_rn(dx, a.dir_x), __dmul_rn(dy, a.dir_y)) < 0.0)
-        return false;
-    return true;
+    if (!(__dadd_rn(__dmul_rn(dx, a.dir_x), __dmul_rn(dy, a.dir_y)) < 0.0))
+        return true;  // not behind the robot: the distance does not matter (teb_follower.cpp:161)
+    // The reference compares glibc's hypot(dx, dy) with obstacle_behind_ignore_range. Any hypot with an error
+    // below one ulp gives the same answer as the exact comparison of the squares unless the distance is within a
+    // few ulps of the range: decide those on the host, with the host's own hypot.
+    const double s2 = __dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)), r2 = __dmul_rn(a.behind_range, a.behind_range);
+    if (a.behind_range >= 0.0 && fabs(__dsub_rn(s2, r2)) <= __dmul_rn(r2, 0x1p-46))
+    {
+        for (uint32_t k = 0; k < a.n_overrides; ++k)
+            if (a.overrides[3 * k] == i && a.overrides[3 * k + 1] == j)
+                return a.overrides[3 * k + 2] != 0;
+        if (a.uncertain)
+        {
+            const uint32_t at = atomicAdd(a.uncertain, 1u);
+            if (at < MAX_UNCERTAIN)
+            {
+                a.uncertain[1 + 2 * at] = i;
+                a.uncertain[2 + 2 * at] = j;
+            }
+        }
+        return false;  // provisional: the pass is repeated with the host's decisions
+    }
+    return !(a.behind_range < 0.0 || s2 > r2);
 }
 
 __global__ void extract_count_kernel(ExtractArgs a, uint32_t *col_counts)
@@ -316,14 +341,52 @@ pp_status pp_obstacles_extract(pp_handle h, double resolution, double origin_x, 
     a.dir_y = sin(robot_theta);
     a.max_distance = max_follow_range * 1.2;  // teb_follower.cpp:146
     a.behind_range = behind_ignore_range;
-    PP_CUDA(h, pp_reserve(h->d_col_counts, h->col_cap, static_cast<size_t>(h->W) + 1));
+    const size_t unc_at = static_cast<size_t>(h->W) + 2, ovr_at = unc_at + 1 + 2 * MAX_UNCERTAIN;
+    PP_CUDA(h, pp_reserve(h->d_col_counts, h->col_cap, ovr_at + 3 * MAX_UNCERTAIN));
     const uint32_t blocks = (h->W + 127) / 128;
+    a.uncertain = h->d_col_counts + unc_at;
+    a.overrides = nullptr;
+    a.n_overrides = 0;
+    PP_CUDA(h, cudaMemsetAsync(a.uncertain, 0, sizeof(uint32_t), h->stream));
     extract_count_kernel<<<blocks, 128, 0, h->stream>>>(a, h->d_col_counts);
     extract_scan_kernel<<<1, 1024, 0, h->stream>>>(h->d_col_counts, h->W);
     h->launches += 2;
     PP_CUDA(h, cudaGetLastError());
     PP_CUDA(h, cudaMemcpyAsync(h->h_counter, h->d_col_counts + h->W, sizeof(uint32_t), cudaMemcpyDeviceToHost, h->stream));
+    PP_CUDA(h, cudaMemcpyAsync(h->h_counter + 1, a.uncertain, sizeof(uint32_t), cudaMemcpyDeviceToHost, h->stream));
     PP_CUDA(h, cudaStreamSynchronize(h->stream));
+    if (const uint32_t n_unc = h->h_counter[1])
+    {
+        // candidates within rounding of the range: the reference's own expression, with the host libm's hypot
+        PP_REQUIRE(h, n_unc <= MAX_UNCERTAIN, PP_ERR_RANGE, "pp_obstacles_extract: %u candidates lie within rounding of behind_ignore_range", n_unc);
+        std::vector<uint32_t> list(2 * n_unc), ovr(3 * n_unc);
+        PP_CUDA(h, cudaMemcpyAsync(list.data(), a.uncertain + 1, list.size() * sizeof(uint32_t), cudaMemcpyDeviceToHost, h->stream));
+        PP_CUDA(h, cudaStreamSynchronize(h->stream));
+        for (uint32_t k = 0; k < n_unc; ++k)
+        {
+            const uint32_t i = list[2 * k], j = list[2 * k + 1];
+            const double wx = origin_x + (i + 0.5) * resolution, wy = origin_y + (j + 0.5) * resolution;  // Costmap2D::mapToWorld
+            const double dx = wx - robot_x, dy = wy - robot_y;
+            const double distance = hypot(dx, dy);  // teb_follower.cpp:158; behind the robot is already known
+            ovr[3 * k] = i;
+            ovr[3 * k + 1] = j;
+            ovr[3 * k + 2] = distance > behind_ignore_range ? 0u : 1u;
+        }
+        PP_CUDA(h, cudaMemcpyAsync(h->d_col_counts + ovr_at, ovr.data(), ovr.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, h->stream));
+        a.uncertain = nullptr;
+        a.overrides = h->d_col_counts + ovr_at;
+        a.n_overrides = n_unc;
+        extract_count_kernel<<<blocks, 128, 0, h->stream>>>(a, h->d_col_counts);
+        extract_scan_kernel<<<1, 1024, 0, h->stream>>>(h->d_col_counts, h->W);
+        h->launches += 2;
+        PP_CUDA(h, cudaGetLastError());
+        PP_CUDA(h, cudaMemcpyAsync(h->h_counter, h->d_col_counts + h->W, sizeof(uint32_t), cudaMemcpyDeviceToHost, h->stream));
+        PP_CUDA(h, cudaStreamSynchronize(h->stream));  // (ovr is read by the copy above: it completes here)
+        if (getenv("PP_TEB_DEBUG"))
+            fprintf(stderr, "[pp] extract: %u candidates within rounding of the range decided on the host\n", n_unc);
+    }
+    else
+        a.uncertain = nullptr;
     const uint32_t total = h->h_counter[0];
     PP_CUDA(h, pp_reserve(h->d_pts, h->pts_cap, 2 * static_cast<size_t>(std::max(total, 1u))));
     extract_emit_kernel<<<blocks, 128, 0, h->stream>>>(a, h->d_col_counts, h->d_pts, total);

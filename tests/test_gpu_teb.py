@@ -118,3 +118,22 @@ def test_column_pruned_query_equals_unpruned(handle, port, origin):
     for r in (0.9574, 0.01, 30.0):
         got = handle.radius_topk(None, q, r, 10)
         assert_topk_equal(got, port.radius_topk(pts, q, r, 10))
+
+
+def test_extract_candidates_exactly_at_the_behind_range(handle, port):
+    """teb_follower.cpp:158-161 compares glibc's hypot with obstacle_behind_ignore_range. Obstacles at distance
+    5 cells x 1 m = exactly the range, and one ulp either side of it, behind the robot: the kernel hands such
+    candidates to the host's hypot instead of trusting the device's."""
+    cost = np.zeros((41, 41), np.uint8)
+    for (dx, dy) in [(-3, 4), (-4, 3), (-5, 0), (-3, -4), (-4, -3), (0, 5), (3, 4), (-6, 8), (-8, 6), (-10, 0)]:
+        cost[20 + dy, 20 + dx] = 254
+    handle.costmap_upload(cost)
+    pose = (20.5, 20.5, 0.0)  # centre of cell (20, 20) at 1 m resolution, looking along +x
+    for R in (5.0, np.nextafter(5.0, 0.0), np.nextafter(5.0, 10.0), 10.0, np.nextafter(10.0, 0.0), 4.999, 0.0):
+        got = handle.obstacles_extract(1.0, (0.0, 0.0), pose, 100.0, float(R))
+        want = port.extract_obstacles(cost, 1.0, (0.0, 0.0), pose, 100.0, float(R))
+        assert got.shape == want.shape and np.array_equal(got, want), R
+    # the counts really change across the boundary (the case is not vacuous)
+    n_at = len(port.extract_obstacles(cost, 1.0, (0.0, 0.0), pose, 100.0, 5.0))
+    n_below = len(port.extract_obstacles(cost, 1.0, (0.0, 0.0), pose, 100.0, float(np.nextafter(5.0, 0.0))))
+    assert n_at > n_below
