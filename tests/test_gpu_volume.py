@@ -289,3 +289,18 @@ def test_short_reach_is_refused_not_clamped(monkeypatch):
             h.se2_volume_build(72)
         assert ei.value.status == 4  # PP_ERR_RANGE
         h.close()
+
+
+def test_new_entry_points_reject_bad_arguments(handle):
+    from path_planner_b200 import capi
+    cost = make_costmap(160, 96, seed=4)
+    handle.costmap_upload(cost)
+    handle.footprint_from_boundary(RES, *FOOTPRINTS["rect_hole"])
+    with pytest.raises(capi.PPError):
+        handle.se2_volume_build_bins(72, [3, 72])          # bin outside [0, n_theta)
+    with pytest.raises(capi.PPError) as ei:
+        handle.se2_volume_build_sharded(72, 3)              # no communicator
+    assert ei.value.status == 2  # PP_ERR_STATE
+    handle.se2_volume_build_bins(72, [])                    # an empty set is a no-op
+    handle.se2_volume_build_bins(72, [5])
+    assert handle.se2_volume_download(5, 6).any()
