@@ -199,8 +199,9 @@ typedef struct pp_plan_params
  * of at the cell centre / nearest bin: the volume filters, flagged samples are re-checked exactly, and an
  * expansion that survives is confirmed by one batched pp_footprint_cost_batch launch over all its samples.
  * PP_PLAN_VALIDATE_PATH: after a successful search every pose of the path is evaluated exactly at its
- * continuous position in one batched launch; the count of colliding poses is reported by pp_plan_stats
- * (the primitives of the search are still decided by the volume: see DESIGN.md for measured rates). */
+ * continuous position in one batched launch. If a pose collides there (the primitives of the search are
+ * decided by the volume: see DESIGN.md for measured rates), its search node is excluded and the search is
+ * repeated, up to three times; pp_plan_stats reports the repeats and what the last path still holds. */
 #define PP_PLAN_EXACT_ANALYTIC 1u
 #define PP_PLAN_VALIDATE_PATH 2u
 pp_status pp_plan(pp_handle h, const pp_plan_params *params, double resolution, double origin_x, double origin_y,
@@ -218,7 +219,8 @@ typedef struct pp_plan_stats_t
     uint32_t false_collisions_overruled; /* ... of those, found free at the continuous pose */
     uint32_t false_free_caught;          /* ... samples the volume called free that the exact batch rejected */
     uint32_t path_poses_checked;         /* PP_PLAN_VALIDATE_PATH: poses of the path evaluated exactly ... */
-    uint32_t path_poses_in_collision;    /* ... and how many of them collide at their continuous pose */
+    uint32_t path_poses_in_collision;    /* ... and how many of them collide at their continuous pose (last search) */
+    uint32_t replans;                    /* ... searches repeated with the colliding poses' nodes excluded (at most 3) */
 } pp_plan_stats_t;
 pp_status pp_plan_stats(pp_handle h, pp_plan_stats_t *out);
 /* Quantisation statistics: with the log enabled, pp_plan records every footprint question of the search --

@@ -52,7 +52,7 @@ class PlanStats(C.Structure):
     """pp_plan_stats_t"""
     _fields_ = [("lookups", C.c_uint64), ("analytic_attempts", C.c_uint32), ("analytic_confirm_batches", C.c_uint32),
                 ("exact_host_checks", C.c_uint32), ("false_collisions_overruled", C.c_uint32), ("false_free_caught", C.c_uint32),
-                ("path_poses_checked", C.c_uint32), ("path_poses_in_collision", C.c_uint32)]
+                ("path_poses_checked", C.c_uint32), ("path_poses_in_collision", C.c_uint32), ("replans", C.c_uint32)]
 
 
 class LayerParams(C.Structure):

@@ -198,18 +198,20 @@ extern "C" pp_status pp_plan(pp_handle h, const pp_plan_params *params, double r
     }
     std::vector<ppb::Pose> path;
     int iterations = 0;
-    const bool found = search.plan(tb, start, goal, path, iterations);
+    bool found = false;
+    const char *fake_hit = getenv("PP_DEBUG_PLAN_FAKE_HIT");  // test hook: pretend that pose k of the first path collides
+    for (uint32_t attempt = 0;; ++attempt)
     {
+        found = search.plan(tb, start, goal, path, iterations);
         const ppb::PlanStats &ps = search.stats();
-        h->plan_stats.lookups = ps.lookups;
-        h->plan_stats.analytic_attempts = ps.analytic_attempts;
-        h->plan_stats.analytic_confirm_batches = ps.analytic_confirm_batches;
-        h->plan_stats.exact_host_checks = ps.exact_host_checks;
-        h->plan_stats.false_collisions_overruled = ps.false_collisions_overruled;
-        h->plan_stats.false_free_caught = ps.false_free_caught;
-    }
-    if (found && validate)
-    {
+        h->plan_stats.lookups += ps.lookups;
+        h->plan_stats.analytic_attempts += ps.analytic_attempts;
+        h->plan_stats.analytic_confirm_batches += ps.analytic_confirm_batches;
+        h->plan_stats.exact_host_checks += ps.exact_host_checks;
+        h->plan_stats.false_collisions_overruled += ps.false_collisions_overruled;
+        h->plan_stats.false_free_caught += ps.false_free_caught;
+        if (!found || !validate)
+            break;
         // every pose of the path at its continuous position, exactly, in one batched launch
         const std::vector<ppb::Pose> &pc = search.pathCells();
         std::vector<float> poses(3 * pc.size()), costs(pc.size());
@@ -223,9 +225,26 @@ extern "C" pp_status pp_plan(pp_handle h, const pp_plan_params *params, double r
         pp_status vs = pp_footprint_cost_batch(h, poses.data(), static_cast<uint32_t>(pc.size()), costs.data(), flags.data());
         if (vs != PP_OK)
             return vs;
+        if (fake_hit && attempt == 0 && static_cast<size_t>(atoi(fake_hit)) < flags.size())
+            flags[atoi(fake_hit)] = 1;
         h->plan_stats.path_poses_checked = static_cast<uint32_t>(pc.size());
-        for (uint8_t f : flags)
-            h->plan_stats.path_poses_in_collision += f != 0;
+        h->plan_stats.path_poses_in_collision = 0;
+        uint32_t newly_blocked = 0;
+        const std::vector<unsigned int> &nodes = search.pathNodes();
+        for (size_t i = 0; i < flags.size(); ++i)
+            if (flags[i])
+            {
+                ++h->plan_stats.path_poses_in_collision;
+                if (i > 0 && i + 1 < flags.size() && i < nodes.size())  // the goal and start poses themselves cannot be avoided
+                {
+                    search.block(nodes[i]);
+                    ++newly_blocked;
+                }
+            }
+        // a pose that the volume let through but the continuous check rejects: search again without those nodes
+        if (h->plan_stats.path_poses_in_collision == 0 || newly_blocked == 0 || attempt == 3)
+            break;
+        ++h->plan_stats.replans;
     }
     if (paged)
         cudaStreamSynchronize(h->aux);  // a prefetched band may still be on its way: part of the plan's time

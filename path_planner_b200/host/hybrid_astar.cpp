@@ -253,7 +253,7 @@ void HybridAStar::expand(const Tables &tb, Node *n, std::vector<Node *> &out)
         if (mx <= 0 || mx >= _W - 1 || my <= 0 || my >= _H - 1)
             continue;
         Node *nb = node(indexOf(mx, my, mt));
-        if (nb->visited)
+        if (nb->visited || blocked(nb->index))
             continue;
         float cost;
         if (footprint(tb, next.x, next.y, next.theta * _bin, cost))
@@ -308,6 +308,8 @@ HybridAStar::Node *HybridAStar::analyticExpansion(const Tables &tb, Node *n)
             samples.push_back(sy);
             samples.push_back(syaw);
         }
+        if (blocked(indexOf(xi, yi, static_cast<unsigned int>(heading))))
+            return nullptr;  // a pose of an earlier path that failed the exact check
         steps.push_back({indexOf(xi, yi, static_cast<unsigned int>(heading)), {sx, sy, heading}});
     }
     if (exact && !samples.empty())
@@ -346,24 +348,33 @@ HybridAStar::Node *HybridAStar::analyticExpansion(const Tables &tb, Node *n)
 }
 
 // astar_hybrid.cpp:248-263
-bool HybridAStar::backtrace(Node *n, std::vector<Pose> &path) const
+bool HybridAStar::backtrace(Node *n, std::vector<Pose> &path)
 {
     if (!n->parent)
         return false;
     Node *cur = n;
+    _path_nodes.clear();
     while (cur->parent)
     {
         path.push_back(cur->at);
+        _path_nodes.push_back(cur->index);
         cur = cur->parent;
     }
     path.push_back(cur->at);
+    _path_nodes.push_back(cur->index);
     return path.size() > 1;
+}
+
+bool HybridAStar::blocked(unsigned int index) const
+{
+    return !_blocked.empty() && std::find(_blocked.begin(), _blocked.end(), index) != _blocked.end();
 }
 
 bool HybridAStar::plan(const Tables &tb, const Pose &start_world, const Pose &goal_world, std::vector<Pose> &path, int &iterations)
 {
     path.clear();
     _path_cells.clear();
+    _path_nodes.clear();
     _stats = PlanStats();
     iterations = 0;
     // astar_hybrid.cpp:392-433: world -> cells (costmap_2d::worldToMap rejects poses outside the map)

@@ -99,6 +99,10 @@ public:
     bool plan(const Tables &tables, const Pose &start_world, const Pose &goal_world, std::vector<Pose> &path, int &iterations);
     // after plan(): the poses of the path as the search held them (cells, cells, radians), goal -> start
     const std::vector<Pose> &pathCells() const { return _path_cells; }
+    const std::vector<unsigned int> &pathNodes() const { return _path_nodes; }  // node numbers of those poses
+    // search nodes the next plan() must not enter (poses of an earlier path that failed the exact check)
+    void block(unsigned int node_index) { _blocked.push_back(node_index); }
+    void clearBlocked() { _blocked.clear(); }
     const PlanStats &stats() const { return _stats; }
     void setQueryLog(std::vector<Query> *log) { _log = log; }
 
@@ -129,7 +133,8 @@ private:
     float travelCost(const Node *from, const Node *to) const;
     void expand(const Tables &tb, Node *n, std::vector<Node *> &out);
     Node *analyticExpansion(const Tables &tb, Node *n);
-    bool backtrace(Node *n, std::vector<Pose> &path) const;
+    bool backtrace(Node *n, std::vector<Pose> &path);
+    bool blocked(unsigned int index) const;
 
     PlanParams _p;
     unsigned int _W, _H, _n_theta;
@@ -157,6 +162,7 @@ private:
     };
     mutable std::vector<HeadingEntry> _heading_cache;
     std::vector<Pose> _path_cells;
+    std::vector<unsigned int> _path_nodes, _blocked;
     mutable PlanStats _stats;
     std::vector<Query> *_log = nullptr;
 };

@@ -199,3 +199,23 @@ def test_quantisation_of_the_volume_lookup_is_bounded(handle, W, seed, cov, star
         assert false_free < 0.03 and false_coll < 0.03
     print("path poses colliding at their continuous pose: %d of %d" % (got["stats"]["path_poses_in_collision"], got["stats"]["path_poses_checked"]))
     assert got["stats"]["path_poses_checked"] == len(got["path"])
+
+
+def test_path_pose_that_fails_the_exact_check_is_planned_around(handle, monkeypatch):
+    """PP_PLAN_VALIDATE_PATH: a pose of the found path that collides at its continuous position has its search
+    node excluded and the search is repeated. No test scene produces such a pose (0 of 163 .. 937), so the
+    mechanism is driven by a debug knob that declares pose 40 of the first path colliding."""
+    start, goal = (1.5, 1.5, 0.0), (18.0, 3.0, -1.0)
+    cost = scene(400, 5, 0.05, start, goal)
+    handle.costmap_upload(cost)
+    handle.footprint_from_boundary(RES, [0.64, 0.46], True)
+    params = {"motion_type": 2, "validate_path": True}
+    first = handle.plan(RES, (0.0, 0.0), start, goal, params)
+    assert first["ok"] == 1 and first["stats"]["replans"] == 0 and first["stats"]["path_poses_in_collision"] == 0
+    monkeypatch.setenv("PP_DEBUG_PLAN_FAKE_HIT", "40")
+    second = handle.plan(RES, (0.0, 0.0), start, goal, params)
+    monkeypatch.delenv("PP_DEBUG_PLAN_FAKE_HIT")
+    assert second["ok"] == 1 and second["stats"]["replans"] == 1
+    assert second["stats"]["path_poses_in_collision"] == 0          # the second path passes the exact check
+    assert not any(np.array_equal(first["path"][40], p) for p in second["path"])  # and avoids the excluded pose
+    assert np.array_equal(second["path"][0], first["path"][0]) and np.array_equal(second["path"][-1], first["path"][-1])
