@@ -40,7 +40,7 @@ constexpr int HT_LOCAL = PP_HT_LOCAL;  // warp-local relaxations of a band betwe
 constexpr uint32_t ROUND_GRID = 148 * PP_HT_GRID;  // CTAs per relaxation round: they walk the round's work list
 
 constexpr uint32_t INACTIVE = 0xFFFFFFFFu;  // tile key: bit pattern of the smallest pending value, or this
-constexpr int N_COUNTERS = 16;              // [0..3] tiles flagged per round, [4] visits, [5] sweeps, [8..11] min key per round
+constexpr int N_COUNTERS = 16;              // [0..3] tiles flagged per round, [4] visits, [5] sweeps, [6] rounds that had work, [8..11] min key per round
 
 __global__ void heur_init_kernel(float *field, size_t n, uint32_t *flags, size_t n_flags, uint32_t goal_index,
                                  uint32_t goal_tile)
@@ -97,6 +97,8 @@ __global__ void __launch_bounds__(HT_THREADS) heur_round_kernel(float *__restric
         counters[8 + ((round + 2) & 3)] = INACTIVE;  // and hold their smallest key
     }
     const uint32_t n_active = counters[round & 3];
+    if (blockIdx.x == 0 && threadIdx.x == 0 && n_active > 0)
+        counters[6] = round + 1;  // rounds that had work (the host launches them in batches and overshoots)
     const float threshold = __uint_as_float(counters[8 + (round & 3)]) + delta;
     __shared__ float F[HT + 2][HT_PITCH];
     __shared__ float WS[HT][HT];
@@ -411,7 +413,7 @@ pp_status pp_heuristic_build(pp_handle h, uint32_t goal_x, uint32_t goal_y, floa
         done = h->h_counter[round & 3] == 0;
         PP_REQUIRE(h, done || round < max_rounds, PP_ERR_STATE, "pp_heuristic_build: relaxation did not converge");
     }
-    h->heur_rounds = round;
+    h->heur_rounds = h->h_counter[6];  // rounds that had work
     h->heur_tile_visits = h->h_counter[4];
     h->heur_sweeps = h->h_counter[5];
     heur_finalize_kernel<<<148 * 8, 256, 0, h->stream>>>(h->d_field, n);
