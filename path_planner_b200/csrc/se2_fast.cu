@@ -31,10 +31,15 @@
 //
 // Exactness: the host planner evaluates the reference expression for every column, row, point
 // and bin with the same float operations (and the host libm's cosf/sinf), finds the ranges of
-// columns / rows over which all offsets are constant, and lets the fast kernel handle only tiles
-// that lie inside such ranges (up to 2 ranges per axis and bin). All other (tile, bin) pairs go
-// to the exact generic kernel through a work list. Covers are minimum exact set covers found by
-// greedy + branch and bound.
+// columns / rows over which all offsets are constant, and keeps the two longest per axis and bin.
+// A tile inside one range is evaluated with that range's offset set; a tile that the boundary
+// between the two ranges crosses ("mixed") is evaluated once per range and every evaluation stores
+// only its own columns / rows; all other (tile, bin) pairs go to the exact generic kernel through a
+// work list. Covers are minimum exact set covers found by greedy + branch and bound.
+//
+// Stores: a warp's 16 x 128-byte output block goes to a staging buffer and from there to the volume
+// with one bulk-tensor (TMA) store per heading bin that shares the evaluation; the tensor map covers
+// this GPU's own volume only. Volumes of peers (fused exchange) are written with plain stores.
 #include "se2_plan.h"
 
 #include <cuda.h>  // CUtensorMap (types only; the encoder is fetched through cudaGetDriverEntryPoint)
@@ -1349,7 +1354,7 @@ pp_status pp_se2_launch_fast(pp_handle h, uint32_t x0, uint32_t y0, uint32_t x1,
             if (args.chain_prev[k][0] == NO_LINK)  // bins that share an earlier bin's evaluation load nothing
                 sample_sum += pl->list_len[t * 4];
         }
-        if (n_work > 0 && !getenv("PP_SE2_SKIP_GENERIC"))  // (timing experiments only: the result is incomplete without it)
+        if (n_work > 0)
         {
             const bool whole_map = tx_lo == 0 && ty_lo == 0 && tx_hi >= pl->tiles_x && ty_hi >= pl->tiles_y;
             const uint32_t t_lo = bins[bi], t_hi = bins[bi + n - 1];
