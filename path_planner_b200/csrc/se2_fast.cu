@@ -841,6 +841,7 @@ struct Se2Plan
     uint32_t uses = 0;
     // geometry
     bool usable = false;
+    bool tma = false;  // smem_bytes includes the staging blocks of the bulk-tensor stores
     int R = 0, PW = 0, rows = 0, table_words = 0, n_tables = 0;
     int max_abs_offset = 0;  // largest |sample offset| of any bin, point, column or row (exact, from the reference expression)
     size_t smem_bytes = 0;
@@ -1009,7 +1010,11 @@ pp_status build_plan(pp_handle h, int effort)
     pl->PW = 32 + 2 * halo;
     pl->table_words = pl->rows * pl->PW;
     const size_t table_bytes = static_cast<size_t>(pl->table_words) * 4;
-    int slots = static_cast<int>(std::min<size_t>(MAX_TABLES, (SMEM_LIMIT - 1024 - STAGE_BYTES) / table_bytes));
+    // stores through the TMA unit need per-warp staging blocks behind the tables (PP_SE2_NO_TMA: knob for A/B runs;
+    // plain whole-row stores measure within +-3 % of the bulk stores, which way depends on the box)
+    pl->tma = getenv("PP_SE2_NO_TMA") == nullptr && h->W % 16 == 0;
+    const size_t stage_bytes = pl->tma ? STAGE_BYTES : 0;
+    int slots = static_cast<int>(std::min<size_t>(MAX_TABLES, (SMEM_LIMIT - 1024 - stage_bytes) / table_bytes));
     // Every table costs a fixed amount per tile and saves samples per bin: with few bins per launch
     // (a heading-sharded rank of an 8-GPU job builds 9) a short library is the optimum.
     pl->few_bins = wants_few_bins(h);
@@ -1058,7 +1063,7 @@ pp_status build_plan(pp_handle h, int effort)
         pl->n_tables = std::min<int>(slots, static_cast<int>(lib.size()));
         pl->lib.assign(lib.begin(), lib.begin() + pl->n_tables);
     }
-    pl->smem_bytes = table_bytes * pl->n_tables + STAGE_BYTES;
+    pl->smem_bytes = table_bytes * pl->n_tables + stage_bytes;
     auto bricks = brick_points(pl->lib, pl->n_tables);
 
     // 5. covers -> sample lists (byte offsets relative to the thread's base address)
@@ -1255,7 +1260,7 @@ pp_status pp_se2_launch_fast(pp_handle h, uint32_t x0, uint32_t y0, uint32_t x1,
             args.peer_delta[p - 1] = static_cast<long long>(reinterpret_cast<uintptr_t>(targets[p]) - reinterpret_cast<uintptr_t>(targets[0]));
     }
     // bulk-tensor stores unless peers' volumes are written too (those go out as plain stores over NVLink)
-    args.use_tma = args.n_peers == 0 && getenv("PP_SE2_NO_TMA") == nullptr && encode_volume_map(&args.vol_map, h->d_vol, h->W, h->H, h->n_theta);
+    args.use_tma = pl->tma && args.n_peers == 0 && encode_volume_map(&args.vol_map, h->d_vol, h->W, h->H, h->n_theta);
     if (getenv("PP_SE2_DEBUG"))
         fprintf(stderr, "[pp] se2 fast: halo %d tables %d smem %zu tma %d grid %ux%u\n", pl->R, pl->n_tables, pl->smem_bytes, args.use_tma,
                 (x1 + FT_W - 1) / FT_W - x0 / FT_W, (y1 + FT_H - 1) / FT_H - y0 / FT_H);
