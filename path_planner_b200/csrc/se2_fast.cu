@@ -1013,6 +1013,9 @@ pp_status build_plan(pp_handle h, int effort)
     // stores through the TMA unit need per-warp staging blocks behind the tables (PP_SE2_NO_TMA: knob for A/B runs;
     // plain whole-row stores measure within +-3 % of the bulk stores, which way depends on the box)
     pl->tma = getenv("PP_SE2_NO_TMA") == nullptr && h->W % 16 == 0;
+    // a large halo leaves room for few tables: there the staging blocks cost more (as samples) than they save
+    if ((SMEM_LIMIT - 1024 - STAGE_BYTES) / table_bytes < 12)
+        pl->tma = false;
     const size_t stage_bytes = pl->tma ? STAGE_BYTES : 0;
     int slots = static_cast<int>(std::min<size_t>(MAX_TABLES, (SMEM_LIMIT - 1024 - stage_bytes) / table_bytes));
     // Every table costs a fixed amount per tile and saves samples per bin: with few bins per launch
