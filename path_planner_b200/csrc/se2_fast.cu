@@ -61,11 +61,8 @@ namespace
 #ifndef PP_CTAS_PER_SM
 #define PP_CTAS_PER_SM 2
 #endif
-#ifndef PP_FT_H
-#define PP_FT_H 16
-#endif
-constexpr int FT_W = 128, FT_H = PP_FT_H, FT_THREADS = PP_FT_THREADS;
-constexpr int GEN_W = 64;  // width of a work-list tile of the exact generic kernel (se2_volume.cu); same height
+constexpr int FT_W = 128, FT_THREADS = PP_FT_THREADS;  // the tile height (16 or 32 rows) is a template parameter
+constexpr int GEN_W = 64, GEN_H = 16;  // work-list tile of the exact generic kernel (se2_volume.cu)
 constexpr int CTAS_PER_SM = PP_CTAS_PER_SM;
 constexpr int MAX_TABLES = 24;
 constexpr int MAX_T_PER_LAUNCH = 160;
@@ -130,8 +127,7 @@ __device__ __forceinline__ uint32_t bytemax4(uint32_t a, uint32_t b)
 }
 
 constexpr int QPT = PP_QPT;                  // rows per thread and work unit
-constexpr int UNITS_PER_BIN = FT_H / QPT;    // a work unit is QPT rows x 128 columns of one bin of a tile: one warp, lane = word column
-static_assert(UNITS_PER_BIN * QPT == FT_H && QPT % 8 == 0, "tile height must be a multiple of the unit height, that of 8");
+static_assert(QPT == 16, "tile heights 16 and 32 are whole work units (QPT rows x 128 columns of one bin: one warp, lane = word column)");
 
 template <int PW>
 __device__ __forceinline__ void load_pair(const uint8_t *smb, uint32_t d1, uint32_t d2, uint32_t (&u)[QPT], uint32_t (&v)[QPT])
@@ -216,7 +212,7 @@ __device__ __noinline__ void store_mixed(const FastArgs &a, uint32_t cls, uint32
 // once per range and the results are blended per column (row).
 constexpr uint32_t LEAD_MIXED = 0x80;  // s_lead_lc flag: the evaluation covers only its classes' part of a mixed tile
 constexpr uint32_t CLS_MIXED0 = 4;  // s_cls: 0..3 uniform class cx*2+cy; 4 + cx + 3*cy with cx, cy in {0,1,2 = mixed}; 255 generic
-template <int PW>
+template <int PW, int TH>
 __device__ __forceinline__ void run_units(const FastArgs &a, const uint32_t *sm, const uint8_t *s_cls, const uint8_t *s_lead, const uint8_t *s_lead_lc,
                                           uint32_t n_lead, uint32_t *s_next, int lane, int tx0, int ty0, uint32_t *stage)
 {
@@ -226,9 +222,10 @@ __device__ __forceinline__ void run_units(const FastArgs &a, const uint32_t *sm,
     const int gx = tx0 + 4 * out_word;
     const bool in_x = gx < W;
     const size_t plane = static_cast<size_t>(a.W) * a.H;
+    constexpr int UNITS_PER_BIN = TH / QPT;
     const uint32_t n_units = UNITS_PER_BIN * n_lead;
     const uint32_t cell0 = static_cast<uint32_t>(ty0) * a.W + static_cast<uint32_t>(gx);  // < 2^30
-    const bool tile_inside = tx0 + FT_W <= W && ty0 + FT_H <= H;
+    const bool tile_inside = tx0 + FT_W <= W && ty0 + TH <= H;
     // lane roles of the two transpose steps
     const bool odd_lane = lane & 1, upper_lane = lane & 2;
     const uint32_t sel1 = odd_lane ? 0x3715u : 0x6240u;
@@ -404,17 +401,17 @@ __device__ __forceinline__ void run_units(const FastArgs &a, const uint32_t *sm,
 
 // Shared-memory geometry, compile-time (the halo is a template parameter) so that the row offsets of the
 // output loop are immediates.
-template <int HALO_>
+template <int HALO_, int TH>
 struct Geo
 {
     static constexpr int HALO = HALO_;
     static constexpr int PW = 32 + 2 * HALO;  // words per table row
-    static constexpr int ROWS = FT_H + 2 * HALO;
+    static constexpr int ROWS = TH + 2 * HALO;
     static constexpr int CW = ROWS * PW;      // words per table
 };
 constexpr int halo_for(int reach) { return reach < MIN_HALO ? MIN_HALO : reach; }
 
-template <int HALO>
+template <int HALO, int TH>
 __global__ void __launch_bounds__(FT_THREADS, CTAS_PER_SM) se2_fast_kernel(const __grid_constant__ FastArgs a)
 {
     extern __shared__ __align__(128) uint32_t tb[];
@@ -422,14 +419,14 @@ __global__ void __launch_bounds__(FT_THREADS, CTAS_PER_SM) se2_fast_kernel(const
     __shared__ uint8_t s_lead[4 * MAX_T_PER_LAUNCH];     // evaluations of this tile: bin ...
     __shared__ uint8_t s_lead_lc[4 * MAX_T_PER_LAUNCH];  // ... and its class pair (| LEAD_MIXED)
     __shared__ uint32_t s_next, s_nlead;
-    using G = Geo<HALO>;
+    using G = Geo<HALO, TH>;
     const int tid = threadIdx.x;
     const int warp = tid >> 5, lane = tid & 31;
     constexpr int NWARPS = FT_THREADS / 32;
     constexpr int ROW_ITERS = (G::ROWS + NWARPS - 1) / NWARPS;
     constexpr int PW = G::PW, CW = G::CW;
     const uint32_t tile_x = a.tile_x0 + blockIdx.x, tile_y = a.tile_y0 + blockIdx.y;
-    const int tx0 = static_cast<int>(tile_x) * FT_W, ty0 = static_cast<int>(tile_y) * FT_H;
+    const int tx0 = static_cast<int>(tile_x) * FT_W, ty0 = static_cast<int>(tile_y) * TH;
     const int W = static_cast<int>(a.W), H = static_cast<int>(a.H);
 
     // bin classes of this tile (one bin per thread), requested before anything else
@@ -445,7 +442,7 @@ __global__ void __launch_bounds__(FT_THREADS, CTAS_PER_SM) se2_fast_kernel(const
     // before the first use; zeros outside the map (the identity of max: the reference ignores such samples).
     const int x0 = tx0 - HALO;
     uint32_t cell[ROW_ITERS][5];
-    if (x0 >= 0 && x0 + FT_W + 2 * HALO <= W && ty0 >= HALO && ty0 + FT_H + HALO <= H)
+    if (x0 >= 0 && x0 + FT_W + 2 * HALO <= W && ty0 >= HALO && ty0 + TH + HALO <= H)
     {
         // the tile and its halo lie inside the map: no bounds tests
         const uint8_t *p0 = a.cost + static_cast<size_t>(ty0 - HALO + warp) * a.W + (x0 + lane);
@@ -567,26 +564,26 @@ __global__ void __launch_bounds__(FT_THREADS, CTAS_PER_SM) se2_fast_kernel(const
     // output phase: warps fetch (evaluating bin, QPT rows) units until none are left
     // per-warp staging blocks of the bulk stores sit behind the tables, 128-byte aligned
     uint32_t *stage = tb + ((a.n_tables * CW + 31) & ~31) + warp * (QPT * 32);
-    run_units<PW>(a, tb, s_cls, s_lead, s_lead_lc, s_nlead, &s_next, lane, tx0, ty0, stage);
+    run_units<PW, TH>(a, tb, s_cls, s_lead, s_lead_lc, s_nlead, &s_next, lane, tx0, ty0, stage);
 }
 
-// one instantiation per halo
+// one instantiation per halo and tile height
 template <class F>
-auto dispatch_fast(int halo, F f)
+auto dispatch_fast(int halo, int th, F f)
 {
 #define PP_CASE(HL) \
-    if (halo == HL) return f(se2_fast_kernel<HL>);
+    if (halo == HL) return th == 32 ? f(se2_fast_kernel<HL, 32>) : f(se2_fast_kernel<HL, 16>);
     PP_CASE(7) PP_CASE(8) PP_CASE(9) PP_CASE(10) PP_CASE(11) PP_CASE(12) PP_CASE(13) PP_CASE(14)
 #undef PP_CASE
-    return f(se2_fast_kernel<15>);
+    return th == 32 ? f(se2_fast_kernel<15, 32>) : f(se2_fast_kernel<15, 16>);
 }
-cudaError_t set_fast_smem(int halo, size_t bytes)
+cudaError_t set_fast_smem(int halo, int th, size_t bytes)
 {
-    return dispatch_fast(halo, [&](auto kernel) { return cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(bytes)); });
+    return dispatch_fast(halo, th, [&](auto kernel) { return cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(bytes)); });
 }
-void launch_fast(int halo, dim3 grid, size_t smem, cudaStream_t stream, const FastArgs &args)
+void launch_fast(int halo, int th, dim3 grid, size_t smem, cudaStream_t stream, const FastArgs &args)
 {
-    dispatch_fast(halo, [&](auto kernel) { kernel<<<grid, FT_THREADS, smem, stream>>>(args); return cudaSuccess; });
+    dispatch_fast(halo, th, [&](auto kernel) { kernel<<<grid, FT_THREADS, smem, stream>>>(args); return cudaSuccess; });
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -842,7 +839,7 @@ struct Se2Plan
     // geometry
     bool usable = false;
     bool tma = false;  // smem_bytes includes the staging blocks of the bulk-tensor stores
-    int R = 0, PW = 0, rows = 0, table_words = 0, n_tables = 0;
+    int R = 0, PW = 0, TH = 16, rows = 0, table_words = 0, n_tables = 0;  // halo, row pitch (words), tile height, table rows
     int max_abs_offset = 0;  // largest |sample offset| of any bin, point, column or row (exact, from the reference expression)
     size_t smem_bytes = 0;
     Library lib;
@@ -981,7 +978,6 @@ pp_status build_plan(pp_handle h, int effort)
     pl->usable = false;
     const uint32_t nt = h->n_theta;
     pl->tiles_x = (h->W + FT_W - 1) / FT_W;
-    pl->tiles_y = (h->H + FT_H - 1) / FT_H;
 
     // 1. exact offsets and uniform ranges for every bin
     std::vector<AxisClasses> xc(nt), yc(nt);
@@ -1006,8 +1002,15 @@ pp_status build_plan(pp_handle h, int effort)
     // 2. geometry: the staged halo is a template parameter of the kernel, the row pitch follows from it
     const int halo = halo_for(R);
     pl->R = halo;
-    pl->rows = FT_H + 2 * halo;
     pl->PW = 32 + 2 * halo;
+    // Tile height: with 32 rows the halo rows are shared by twice the output rows (table build and staging per cell
+    // -26 %) but a table is 47 % bigger; taken when at least 11 tables still fit twice per SM (measured at halo 9:
+    // 0.497 against 0.518 ms with 16 rows; the box of config 2, halo 14, is better off with 16 rows and more tables).
+    pl->TH = (SMEM_LIMIT - 1024) / (static_cast<size_t>(32 + 2 * halo) * pl->PW * 4) >= 11 ? 32 : 16;
+    if (const char *e = getenv("PP_SE2_TILE_ROWS"))  // tuning knob for experiments
+        pl->TH = atoi(e) == 32 ? 32 : 16;
+    pl->tiles_y = (h->H + pl->TH - 1) / pl->TH;
+    pl->rows = pl->TH + 2 * halo;
     pl->table_words = pl->rows * pl->PW;
     const size_t table_bytes = static_cast<size_t>(pl->table_words) * 4;
     // stores through the TMA unit need per-warp staging blocks behind the tables (PP_SE2_NO_TMA: knob for A/B runs;
@@ -1102,7 +1105,7 @@ pp_status build_plan(pp_handle h, int effort)
     // with host-made list words: checked here once for all launches (the kernel has no bounds tests in that loop).
     for (uint32_t w : pl->lists)
     {
-        const uint32_t first = w / 4, last = first + static_cast<uint32_t>(FT_H - 1) * pl->PW + 31;
+        const uint32_t first = w / 4, last = first + static_cast<uint32_t>(pl->TH - 1) * pl->PW + 31;
         PP_REQUIRE(h, w % 4 == 0 && last < static_cast<uint32_t>(pl->n_tables) * pl->table_words, PP_ERR_STATE,
                    "internal: a sample list addresses word %u of %u table words", last, pl->n_tables * pl->table_words);
     }
@@ -1157,7 +1160,7 @@ pp_status build_plan(pp_handle h, int effort)
         }
         for (uint32_t ty = 0; ty < pl->tiles_y; ++ty)
         {
-            const int lo = static_cast<int>(ty * FT_H), hi = static_cast<int>(std::min(h->H, (ty + 1) * FT_H));
+            const int lo = static_cast<int>(ty * pl->TH), hi = static_cast<int>(std::min<uint32_t>(h->H, (ty + 1) * pl->TH));
             pl->h_yclass[static_cast<size_t>(t) * pl->tiles_y + ty] = tile_class(yc[t], lo, hi, ys, yleft);
         }
         pl->work_off[t] = static_cast<uint32_t>(pl->h_work.size() / 2);
@@ -1165,14 +1168,15 @@ pp_status build_plan(pp_handle h, int effort)
             for (uint32_t tx = 0; tx < pl->tiles_x; ++tx)
                 if (pl->h_xclass[static_cast<size_t>(t) * pl->tiles_x + tx] == 255 ||
                     pl->h_yclass[static_cast<size_t>(t) * pl->tiles_y + ty] == 255)
-                    for (uint32_t half = 0; half < FT_W / GEN_W; ++half)  // in tiles of the generic kernel
-                    {
-                        const uint32_t gtx = tx * (FT_W / GEN_W) + half;
-                        if (gtx * GEN_W >= h->W)
-                            break;
-                        pl->h_work.push_back(gtx | (ty << 16));
-                        pl->h_work.push_back(t);
-                    }
+                    for (uint32_t sy = 0; sy < static_cast<uint32_t>(pl->TH / GEN_H); ++sy)  // in tiles of the generic kernel
+                        for (uint32_t half = 0; half < FT_W / GEN_W; ++half)
+                        {
+                            const uint32_t gtx = tx * (FT_W / GEN_W) + half, gty = ty * (pl->TH / GEN_H) + sy;
+                            if (gtx * GEN_W >= h->W || gty * GEN_H >= h->H)
+                                continue;
+                            pl->h_work.push_back(gtx | (gty << 16));
+                            pl->h_work.push_back(t);
+                        }
     }
     pl->work_off[nt] = static_cast<uint32_t>(pl->h_work.size() / 2);
 
@@ -1186,7 +1190,7 @@ pp_status build_plan(pp_handle h, int effort)
         PP_CUDA(h, cudaMemcpyAsync(pl->d_work, pl->h_work.data(), pl->h_work.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, h->stream));
     }
     PP_CUDA(h, cudaStreamSynchronize(h->stream));
-    PP_CUDA(h, set_fast_smem(pl->R, pl->smem_bytes));
+    PP_CUDA(h, set_fast_smem(pl->R, pl->TH, pl->smem_bytes));
     pl->usable = true;
     return PP_OK;
 }
@@ -1251,7 +1255,7 @@ pp_status pp_se2_launch_fast(pp_handle h, uint32_t x0, uint32_t y0, uint32_t x1,
         return PP_INTERNAL_DECLINED;
 
     const uint32_t tx_lo = x0 / FT_W, tx_hi = (x1 + FT_W - 1) / FT_W;
-    const uint32_t ty_lo = y0 / FT_H, ty_hi = (y1 + FT_H - 1) / FT_H;
+    const uint32_t ty_lo = y0 / pl->TH, ty_hi = (y1 + pl->TH - 1) / pl->TH;
     static thread_local FastArgs args;  // ~28 KB: keep it off the stack
     args.cost = h->d_cost;
     args.vol = h->d_vol;
@@ -1266,7 +1270,7 @@ pp_status pp_se2_launch_fast(pp_handle h, uint32_t x0, uint32_t y0, uint32_t x1,
     args.use_tma = pl->tma && args.n_peers == 0 && encode_volume_map(&args.vol_map, h->d_vol, h->W, h->H, h->n_theta);
     if (getenv("PP_SE2_DEBUG"))
         fprintf(stderr, "[pp] se2 fast: halo %d tables %d smem %zu tma %d grid %ux%u\n", pl->R, pl->n_tables, pl->smem_bytes, args.use_tma,
-                (x1 + FT_W - 1) / FT_W - x0 / FT_W, (y1 + FT_H - 1) / FT_H - y0 / FT_H);
+                (x1 + FT_W - 1) / FT_W - x0 / FT_W, ty_hi - ty_lo);
     args.xclass = pl->d_xclass;
     args.yclass = pl->d_yclass;
     args.W = h->W;
@@ -1358,7 +1362,7 @@ pp_status pp_se2_launch_fast(pp_handle h, uint32_t x0, uint32_t y0, uint32_t x1,
             const uint32_t nw = pl->work_off[t + 1] - pl->work_off[t];
             n_work += nw;
             generic_pairs += nw;
-            fast_pairs += static_cast<uint64_t>(pl->tiles_x) * pl->tiles_y - nw / (FT_W / GEN_W);
+            fast_pairs += static_cast<uint64_t>(pl->tiles_x) * pl->tiles_y - nw / ((FT_W / GEN_W) * (pl->TH / GEN_H));
             if (args.chain_prev[k][0] == NO_LINK)  // bins that share an earlier bin's evaluation load nothing
                 sample_sum += pl->list_len[t * 4];
         }
@@ -1386,7 +1390,7 @@ pp_status pp_se2_launch_fast(pp_handle h, uint32_t x0, uint32_t y0, uint32_t x1,
                         for (uint32_t e = pl->work_off[bins[bi + k]]; e < pl->work_off[bins[bi + k] + 1]; ++e)
                         {
                             const uint32_t tile = pl->h_work[2 * e], wx = tile & 0xFFFFu, wy = tile >> 16;
-                            if (wx / (FT_W / GEN_W) >= tx_lo && wx / (FT_W / GEN_W) < tx_hi && wy >= ty_lo && wy < ty_hi)
+                            if (wx / (FT_W / GEN_W) >= tx_lo && wx / (FT_W / GEN_W) < tx_hi && wy / (pl->TH / GEN_H) >= ty_lo && wy / (pl->TH / GEN_H) < ty_hi)
                             {
                                 pl->region_work.push_back(tile);
                                 pl->region_work.push_back(pl->h_work[2 * e + 1]);
@@ -1409,7 +1413,7 @@ pp_status pp_se2_launch_fast(pp_handle h, uint32_t x0, uint32_t y0, uint32_t x1,
                 }
             }
         }
-        launch_fast(pl->R, grid, pl->smem_bytes, h->stream, args);
+        launch_fast(pl->R, pl->TH, grid, pl->smem_bytes, h->stream, args);
         h->launches++;
         PP_CUDA(h, cudaGetLastError());
         if (forked)

@@ -19,10 +19,7 @@
 namespace
 {
 constexpr int GT_W = 64;        // tile width  (outputs)
-#ifndef PP_FT_H
-#define PP_FT_H 16
-#endif
-constexpr int GT_H = PP_FT_H;   // tile height (outputs); must equal the fast path's tile height (shared work list)
+constexpr int GT_H = 16;        // tile height (outputs); the work list of the tiled fast path is in these 64 x 16 tiles
 constexpr int GT_THREADS = 256;
 constexpr int GT_ROWS_PER_THREAD = GT_H / (GT_THREADS / GT_W);  // 8
 constexpr int GT_PCHUNK = 256;  // footprint points tabulated per pass
