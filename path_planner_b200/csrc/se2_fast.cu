@@ -839,6 +839,7 @@ struct Se2Plan
     // geometry
     bool usable = false;
     bool tma = false;  // smem_bytes includes the staging blocks of the bulk-tensor stores
+    bool tall_ok = false;  // the build covers enough tiles for 32-row tiles (part of the plan's key)
     int R = 0, PW = 0, TH = 16, rows = 0, table_words = 0, n_tables = 0;  // halo, row pitch (words), tile height, table rows
     int max_abs_offset = 0;  // largest |sample offset| of any bin, point, column or row (exact, from the reference expression)
     size_t smem_bytes = 0;
@@ -953,10 +954,16 @@ AxisClasses classify_axis(bool is_x, uint32_t n, float sample_off, const std::ve
 }
 
 constexpr uint32_t FEW_BINS = 12;
+// 32-row tiles only where a build has enough of them (about seven waves of CTA slots): the whole map, or a wide band
+bool wants_tall_tiles(pp_handle h)
+{
+    const uint32_t rows = h->band_y1 > h->band_y0 ? std::min(h->band_y1, h->H) - std::min(h->band_y0, h->H) : h->H;
+    return static_cast<uint64_t>((h->W + FT_W - 1) / FT_W) * ((rows + 31) / 32) >= 2000;
+}
 bool wants_few_bins(pp_handle h) { return h->few_bins_override >= 0 ? h->few_bins_override != 0 : h->bins.size() <= FEW_BINS; }
 bool plan_matches(const Se2Plan *p, pp_handle h)
 {
-    return p && p->few_bins == wants_few_bins(h) && p->W == h->W && p->H == h->H && p->n_theta == h->n_theta && p->ox == h->ox && p->oy == h->oy &&
+    return p && p->few_bins == wants_few_bins(h) && p->tall_ok == wants_tall_tiles(h) && p->W == h->W && p->H == h->H && p->n_theta == h->n_theta && p->ox == h->ox && p->oy == h->oy &&
            p->ot == h->ot && p->fp == h->fp;
 }
 
@@ -1006,7 +1013,10 @@ pp_status build_plan(pp_handle h, int effort)
     // Tile height: with 32 rows the halo rows are shared by twice the output rows (table build and staging per cell
     // -26 %) but a table is 47 % bigger; taken when at least 11 tables still fit twice per SM (measured at halo 9:
     // 0.497 against 0.518 ms with 16 rows; the box of config 2, halo 14, is better off with 16 rows and more tables).
-    pl->TH = (SMEM_LIMIT - 1024) / (static_cast<size_t>(32 + 2 * halo) * pl->PW * 4) >= 11 ? 32 : 16;
+    // A build that covers few tiles (a row band of an 8-GPU job) keeps 16 rows: twice as many tiles fill the last wave
+    // of CTA slots better (measured at 8 GPUs: 0.089 against 0.096 ms per band).
+    pl->tall_ok = wants_tall_tiles(h);
+    pl->TH = pl->tall_ok && (SMEM_LIMIT - 1024) / (static_cast<size_t>(32 + 2 * halo) * pl->PW * 4) >= 11 ? 32 : 16;
     if (const char *e = getenv("PP_SE2_TILE_ROWS"))  // tuning knob for experiments
         pl->TH = atoi(e) == 32 ? 32 : 16;
     pl->tiles_y = (h->H + pl->TH - 1) / pl->TH;

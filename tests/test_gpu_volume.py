@@ -304,3 +304,24 @@ def test_new_entry_points_reject_bad_arguments(handle):
     handle.se2_volume_build_bins(72, [])                    # an empty set is a no-op
     handle.se2_volume_build_bins(72, [5])
     assert handle.se2_volume_download(5, 6).any()
+
+
+@pytest.mark.parametrize("shape", [(96, 80), (200, 150), (256, 64), (400, 400)])
+@pytest.mark.parametrize("fname", ["rect_hole", "circle_hole", "rect_solid"])
+def test_32_row_tiles_match_the_port(handle, port, monkeypatch, shape, fname):
+    """Large builds use 128 x 32 tiles (the planner picks them from ~2000 tiles on); forced here on small, ragged maps
+    so that partial tiles, mixed tiles at the first columns / rows and the dirty-region refresh run with them too."""
+    monkeypatch.setenv("PP_SE2_TILE_ROWS", "32")
+    W, H = shape
+    cost = make_costmap(W, H, seed=W + H, coverage=0.1)
+    b, hole = FOOTPRINTS[fname]
+    pts = port.footprint_points(RES, b, hole)
+    handle.costmap_upload(cost)
+    handle.footprint_from_boundary(RES, b, hole)
+    handle.se2_volume_build(72)
+    assert np.array_equal(handle.se2_volume_download(), port.se2_volume(cost, pts, 72))
+    c2 = cost.copy()
+    c2[H // 3:H // 3 + 9, W // 2:W // 2 + 13] = 254
+    handle.costmap_update_rect(W // 2, H // 3, np.ascontiguousarray(c2[H // 3:H // 3 + 9, W // 2:W // 2 + 13]))
+    handle.se2_volume_refresh()
+    assert np.array_equal(handle.se2_volume_download(), port.se2_volume(c2, pts, 72))
