@@ -66,6 +66,8 @@ pp_status pp_create(pp_handle *out, int device)
         delete h;
         return PP_ERR_CUDA;
     }
+    if (cudaDeviceGetAttribute(&h->sm_count, cudaDevAttrMultiProcessorCount, device) != cudaSuccess || h->sm_count < 1)
+        h->sm_count = 148;
     *out = h;
     return PP_OK;
 }

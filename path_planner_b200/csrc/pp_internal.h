@@ -12,6 +12,7 @@ struct Se2Plan;  // se2_plan.h
 struct pp_ctx
 {
     int device = 0;
+    int sm_count = 148;
     cudaStream_t stream = nullptr;
     cudaStream_t aux = nullptr;  // side stream: the exact work-list kernel runs beside the tiled kernel
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;

@@ -93,7 +93,8 @@ struct FastArgs
     int n_peers;              // fused exchange: every output word is also stored to these
     const uint8_t *xclass;  // [n_theta][tiles_x]: 0/1 = column range class, 255 = not uniform
     const uint8_t *yclass;  // [n_theta][tiles_y]
-    uint32_t W, H, tiles_x, tiles_y, tile_x0, tile_y0;
+    uint32_t W, H, tiles_x, tiles_y;
+    const uint32_t *tile_order;  // CTA b works on tile tile_order[b] = tile_x | tile_y << 16, the tiles with the most evaluations first
     int32_t n_tables;  // the halo (and with it the row pitch) is a template parameter of the kernel
     // table k >= 1: word i = bytemax(T[rec_a[k] + i], T_b[rec_d[k] + i]) with T_b = T + rec_b[k]; rec_d is the
     // shift dv * pitch + du inside table b (reads that leave table b give 0: they only feed entries whose
@@ -112,6 +113,9 @@ struct FastArgs
     uint16_t chain_prev[MAX_T_PER_LAUNCH][4];
     uint16_t chain_next[MAX_T_PER_LAUNCH][4];
     alignas(16) uint32_t lists[MAX_LIST_WORDS];  // byte offsets into shared memory, relative to the thread's base
+#ifdef PP_SE2_TIMELINE
+    unsigned long long *timeline;  // dev build: per CTA {start, staged, built, end (ns, %globaltimer), SM id}
+#endif
 };
 static_assert(MAX_T_PER_LAUNCH <= 255, "chain links keep the bin in 8 bits");
 static_assert(MAX_TABLES <= 32, "rec_sync is a 32-bit mask");
@@ -226,10 +230,10 @@ __device__ __forceinline__ void run_units(const FastArgs &a, const uint32_t *sm,
     const uint32_t n_units = UNITS_PER_BIN * n_lead;
     const uint32_t cell0 = static_cast<uint32_t>(ty0) * a.W + static_cast<uint32_t>(gx);  // < 2^30
     const bool tile_inside = tx0 + FT_W <= W && ty0 + TH <= H;
-    // lane roles of the two transpose steps
+    // lane roles of the two transpose steps (selectors of the byte permutes; two rows travel in one shuffle)
     const bool odd_lane = lane & 1, upper_lane = lane & 2;
-    const uint32_t sel1 = odd_lane ? 0x3715u : 0x6240u;
-    const uint32_t sel2 = upper_lane ? 0x3276u : 0x5410u;
+    const uint32_t give1 = odd_lane ? 0x6420u : 0x7531u, keep1a = odd_lane ? 0x3514u : 0x5240u, keep1b = odd_lane ? 0x3716u : 0x7260u;
+    const uint32_t give2 = upper_lane ? 0x5410u : 0x7632u, keep2a = upper_lane ? 0x3254u : 0x5410u, keep2b = upper_lane ? 0x3276u : 0x7610u;
     while (true)
     {
         uint32_t unit = 0;
@@ -301,15 +305,18 @@ __device__ __forceinline__ void run_units(const FastArgs &a, const uint32_t *sm,
         // (odd = (., b1, ., b3), even = (., b0, ., b2), b_i = the lane's cell q + 32 i); they are merged first.
         // Step 1 (lane ^ 1): even lanes collect (b0, b2) of both lanes, odd lanes (b1, b3).
         // Step 2 (lane ^ 2): lower lanes collect bytes 0..1 of both, upper lanes bytes 2..3.
+        // A lane gives away half of its bytes in each step, so the halves of two rows share one shuffle
+        // (shuffles go through the shared-memory pipe, the one this kernel is bound by).
         uint32_t res[QPT];
 #pragma unroll
-        for (int j = 0; j < QPT; ++j)
+        for (int j = 0; j < QPT; j += 2)
         {
-            const uint32_t m = __byte_perm(even[j], odd[j], 0x7351);
-            const uint32_t got = __shfl_xor_sync(0xffffffffu, m, 1);
-            const uint32_t p = __byte_perm(m, got, sel1);
-            const uint32_t got2 = __shfl_xor_sync(0xffffffffu, p, 2);
-            res[j] = __byte_perm(p, got2, sel2);
+            const uint32_t m0 = __byte_perm(even[j], odd[j], 0x7351), m1 = __byte_perm(even[j + 1], odd[j + 1], 0x7351);
+            const uint32_t got = __shfl_xor_sync(0xffffffffu, __byte_perm(m0, m1, give1), 1);
+            const uint32_t p0 = __byte_perm(m0, got, keep1a), p1 = __byte_perm(m1, got, keep1b);
+            const uint32_t got2 = __shfl_xor_sync(0xffffffffu, __byte_perm(p0, p1, give2), 2);
+            res[j] = __byte_perm(p0, got2, keep2a);
+            res[j + 1] = __byte_perm(p1, got2, keep2b);
         }
         if (lcm & LEAD_MIXED)
         {
@@ -425,7 +432,12 @@ __global__ void __launch_bounds__(FT_THREADS, CTAS_PER_SM) se2_fast_kernel(const
     constexpr int NWARPS = FT_THREADS / 32;
     constexpr int ROW_ITERS = (G::ROWS + NWARPS - 1) / NWARPS;
     constexpr int PW = G::PW, CW = G::CW;
-    const uint32_t tile_x = a.tile_x0 + blockIdx.x, tile_y = a.tile_y0 + blockIdx.y;
+#ifdef PP_SE2_TIMELINE
+    unsigned long long tl0 = 0, tl1 = 0, tl2 = 0;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tl0));
+#endif
+    const uint32_t tile_xy = __ldg(a.tile_order + blockIdx.x);
+    const uint32_t tile_x = tile_xy & 0xFFFFu, tile_y = tile_xy >> 16;
     const int tx0 = static_cast<int>(tile_x) * FT_W, ty0 = static_cast<int>(tile_y) * TH;
     const int W = static_cast<int>(a.W), H = static_cast<int>(a.H);
 
@@ -494,6 +506,9 @@ __global__ void __launch_bounds__(FT_THREADS, CTAS_PER_SM) se2_fast_kernel(const
         }
     }
     const int any_fast = __syncthreads_or(my_cls != 255u);
+#ifdef PP_SE2_TIMELINE
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tl1));
+#endif
     if (!any_fast)
         return;  // every bin of this tile belongs to the generic work list
 
@@ -560,11 +575,26 @@ __global__ void __launch_bounds__(FT_THREADS, CTAS_PER_SM) se2_fast_kernel(const
         }
     }
     __syncthreads();  // also orders s_lead / s_nlead when no table beyond the costmap is built
+#ifdef PP_SE2_TIMELINE
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tl2));
+#endif
 
     // output phase: warps fetch (evaluating bin, QPT rows) units until none are left
     // per-warp staging blocks of the bulk stores sit behind the tables, 128-byte aligned
     uint32_t *stage = tb + ((a.n_tables * CW + 31) & ~31) + warp * (QPT * 32);
     run_units<PW, TH>(a, tb, s_cls, s_lead, s_lead_lc, s_nlead, &s_next, lane, tx0, ty0, stage);
+#ifdef PP_SE2_TIMELINE
+    __syncthreads();
+    if (tid == 0 && a.timeline)
+    {
+        unsigned long long tl3;
+        uint32_t smid;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tl3));
+        asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+        unsigned long long *o = a.timeline + 5ull * blockIdx.x;
+        o[0] = tl0, o[1] = tl1, o[2] = tl2, o[3] = tl3, o[4] = smid;
+    }
+#endif
 }
 
 // one instantiation per halo and tile height
@@ -865,8 +895,13 @@ struct Se2Plan
     uint32_t *d_region_work = nullptr;
     size_t region_cap = 0;
     uint64_t region_key[6] = {~0ull, 0, 0, 0, 0, 0};
+    // dispatch order of the tiles of the last region (cached the same way)
+    uint32_t *d_tile_order = nullptr;
+    size_t order_cap = 0;
+    uint64_t order_key[5] = {~0ull, 0, 0, 0, 0};
     ~Se2Plan()
     {
+        cudaFree(d_tile_order);
         cudaFree(d_region_work);
         cudaFree(d_xclass);
         cudaFree(d_yclass);
@@ -1287,8 +1322,6 @@ pp_status pp_se2_launch_fast(pp_handle h, uint32_t x0, uint32_t y0, uint32_t x1,
     args.H = h->H;
     args.tiles_x = pl->tiles_x;
     args.tiles_y = pl->tiles_y;
-    args.tile_x0 = tx_lo;
-    args.tile_y0 = ty_lo;
     args.n_tables = pl->n_tables;
     {
         const std::vector<int> lvl = library_levels(pl->lib);
@@ -1303,8 +1336,49 @@ pp_status pp_se2_launch_fast(pp_handle h, uint32_t x0, uint32_t y0, uint32_t x1,
                 args.rec_sync |= 1u << k;
         }
     }
-    const dim3 grid(tx_hi - tx_lo, ty_hi - ty_lo, 1);
-    const uint64_t n_tiles = static_cast<uint64_t>(grid.x) * grid.y;
+    const uint32_t n_tiles = (tx_hi - tx_lo) * (ty_hi - ty_lo);  // one CTA per tile
+    // Dispatch order: CTAs start in index order, so the tiles with the most work go first (a tile that a range
+    // boundary crosses evaluates such a bin once per class pair and stores through masks -- with the boundaries
+    // near x = 0 that is the left-hand tile column, twice as long as the others) and none of them ends the launch.
+    {
+        const uint64_t key[5] = {tx_lo, tx_hi, ty_lo, ty_hi, 1};  // weighed over all bins: one order per region
+        if (std::memcmp(key, pl->order_key, sizeof(key)) != 0)
+        {
+            std::vector<uint32_t> weight(n_tiles, 0), order(n_tiles);
+            for (uint32_t t = 0; t < pl->n_theta; ++t)
+                for (uint32_t ty = ty_lo; ty < ty_hi; ++ty)
+                {
+                    const uint32_t cy = pl->h_yclass[static_cast<size_t>(t) * pl->tiles_y + ty];
+                    for (uint32_t tx = tx_lo; tx < tx_hi; ++tx)
+                    {
+                        const uint32_t cx = pl->h_xclass[static_cast<size_t>(t) * pl->tiles_x + tx];
+                        if (cx > 2 || cy > 2)
+                            continue;  // generic work list
+                        const uint32_t pairs = (cx == 2 ? 2u : 1u) * (cy == 2 ? 2u : 1u);
+                        weight[(ty - ty_lo) * (tx_hi - tx_lo) + (tx - tx_lo)] += (cx == 2 || cy == 2) ? 2u * pairs : 1u;
+                    }
+                }
+            for (uint32_t i = 0; i < n_tiles; ++i)
+                order[i] = i;
+            std::stable_sort(order.begin(), order.end(), [&](uint32_t p, uint32_t q) { return weight[p] > weight[q]; });
+            for (uint32_t i = 0; i < n_tiles; ++i)
+                order[i] = (tx_lo + order[i] % (tx_hi - tx_lo)) | (ty_lo + order[i] / (tx_hi - tx_lo)) << 16;
+            PP_CUDA(h, pp_reserve(pl->d_tile_order, pl->order_cap, order.size()));
+            PP_CUDA(h, cudaMemcpyAsync(pl->d_tile_order, order.data(), order.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, h->stream));
+            PP_CUDA(h, cudaStreamSynchronize(h->stream));  // `order` is pageable and goes out of scope
+            std::memcpy(pl->order_key, key, sizeof(key));
+            if (std::getenv("PP_SE2_DEBUG"))
+            {
+                std::map<uint32_t, uint32_t> hist;
+                for (uint32_t wv : weight)
+                    hist[wv]++;
+                for (auto &kv : hist)
+                    std::fprintf(stderr, "[pp_se2] tile weight %u: %u tiles\n", kv.first, kv.second);
+            }
+        }
+    }
+    args.tile_order = pl->d_tile_order;
+    const dim3 grid(n_tiles, 1, 1);
     double sample_sum = 0.0;
     uint64_t fast_pairs = 0, generic_pairs = 0;
 
@@ -1423,9 +1497,40 @@ pp_status pp_se2_launch_fast(pp_handle h, uint32_t x0, uint32_t y0, uint32_t x1,
                 }
             }
         }
+#ifdef PP_SE2_TIMELINE
+        static unsigned long long *d_tl = nullptr;
+        static size_t tl_cap = 0;
+        const char *tl_path = std::getenv("PP_SE2_TIMELINE_FILE");
+        args.timeline = nullptr;
+        if (tl_path)
+        {
+            if (tl_cap < grid.x)
+            {
+                cudaFree(d_tl);
+                cudaMalloc(&d_tl, 5ull * grid.x * sizeof(unsigned long long));
+                tl_cap = grid.x;
+            }
+            cudaMemsetAsync(d_tl, 0, 5ull * grid.x * sizeof(unsigned long long), h->stream);
+            args.timeline = d_tl;
+        }
+#endif
         launch_fast(pl->R, pl->TH, grid, pl->smem_bytes, h->stream, args);
         h->launches++;
         PP_CUDA(h, cudaGetLastError());
+#ifdef PP_SE2_TIMELINE
+        if (tl_path)
+        {
+            std::vector<unsigned long long> tl(5ull * grid.x);
+            cudaStreamSynchronize(h->stream);
+            cudaMemcpy(tl.data(), d_tl, tl.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost);
+            if (FILE *f = std::fopen(tl_path, "w"))  // the last launch wins
+            {
+                for (uint32_t b = 0; b < grid.x; ++b)
+                    std::fprintf(f, "%u %llu %llu %llu %llu %llu\n", b, tl[5 * b], tl[5 * b + 1], tl[5 * b + 2], tl[5 * b + 3], tl[5 * b + 4]);
+                std::fclose(f);
+            }
+        }
+#endif
         if (forked)
         {
             pp_status s = pp_se2_join_aux(h);
@@ -1434,7 +1539,6 @@ pp_status pp_se2_launch_fast(pp_handle h, uint32_t x0, uint32_t y0, uint32_t x1,
         }
         bi += n;
     }
-    (void)n_tiles;
     h->stat_fast_tiles = fast_pairs;
     h->stat_samples_per_cell = sample_sum / std::max<size_t>(1, h->bins.size());
     return PP_OK;
