@@ -366,20 +366,22 @@ __device__ __forceinline__ void run_units(const FastArgs &a, const uint32_t *sm,
             continue;
         }
         const uint32_t unit_off = static_cast<uint32_t>(row0) * a.W;
+        const int rows_ok = H - gy;  // rows of the unit inside the map
         uint8_t *out = a.vol + plane * a.bin[t] + unit_off;  // warp-uniform
         while (true)
         {
             if (tile_inside && a.n_peers == 0)
             {
+                uint8_t *dst = out + cell0;  // one 64-bit add per row instead of a product and an add
 #pragma unroll
-                for (int j = 0; j < QPT; ++j)
-                    *reinterpret_cast<uint32_t *>(out + cell0 + static_cast<uint32_t>(j) * a.W) = res[j];
+                for (int j = 0; j < QPT; ++j, dst += a.W)
+                    *reinterpret_cast<uint32_t *>(dst) = res[j];
             }
             else if (in_x)
             {
 #pragma unroll
                 for (int j = 0; j < QPT; ++j)
-                    if (gy + j < H)
+                    if (j < rows_ok)
                     {
                         uint8_t *dst = out + cell0 + static_cast<uint32_t>(j) * a.W;
                         *reinterpret_cast<uint32_t *>(dst) = res[j];
