@@ -225,7 +225,7 @@ __device__ __forceinline__ void run_units(const FastArgs &a, const uint32_t *sm,
     const int out_word = (lane >> 2) + 8 * (lane & 3);
     const int gx = tx0 + 4 * out_word;
     const bool in_x = gx < W;
-    const size_t plane = static_cast<size_t>(a.W) * a.H;
+    const uint32_t plane = a.W * a.H;  // cells of one bin (maps are at most 32768 x 32768)
     constexpr int UNITS_PER_BIN = TH / QPT;
     const uint32_t n_units = UNITS_PER_BIN * n_lead;
     const uint32_t cell0 = static_cast<uint32_t>(ty0) * a.W + static_cast<uint32_t>(gx);  // < 2^30
@@ -365,14 +365,14 @@ __device__ __forceinline__ void run_units(const FastArgs &a, const uint32_t *sm,
             }
             continue;
         }
-        const uint32_t unit_off = static_cast<uint32_t>(row0) * a.W;
+        const uint32_t lane_off = cell0 + static_cast<uint32_t>(row0) * a.W;  // this lane's word of the unit's first row, < 2^31
         const int rows_ok = H - gy;  // rows of the unit inside the map
-        uint8_t *out = a.vol + plane * a.bin[t] + unit_off;  // warp-uniform
+        uint8_t *out = a.vol + (static_cast<uint64_t>(plane) * a.bin[t] + lane_off);
         while (true)
         {
             if (tile_inside && a.n_peers == 0)
             {
-                uint8_t *dst = out + cell0;  // one 64-bit add per row instead of a product and an add
+                uint8_t *dst = out;  // one 64-bit add per row instead of a product and an add
 #pragma unroll
                 for (int j = 0; j < QPT; ++j, dst += a.W)
                     *reinterpret_cast<uint32_t *>(dst) = res[j];
@@ -383,7 +383,7 @@ __device__ __forceinline__ void run_units(const FastArgs &a, const uint32_t *sm,
                 for (int j = 0; j < QPT; ++j)
                     if (j < rows_ok)
                     {
-                        uint8_t *dst = out + cell0 + static_cast<uint32_t>(j) * a.W;
+                        uint8_t *dst = out + static_cast<uint32_t>(j) * a.W;
                         *reinterpret_cast<uint32_t *>(dst) = res[j];
                         for (int p = 0; p < a.n_peers; ++p)  // peer volumes over NVLink
                             *reinterpret_cast<uint32_t *>(dst + a.peer_delta[p]) = res[j];
@@ -400,7 +400,7 @@ __device__ __forceinline__ void run_units(const FastArgs &a, const uint32_t *sm,
             }
             if (t2 == NO_LINK)
                 break;
-            out = a.vol + plane * a.bin[t2] + unit_off;
+            out = a.vol + (static_cast<uint64_t>(plane) * a.bin[t2] + lane_off);
         }
     }
     // the staging buffer must outlive the bulk stores that read it
@@ -1366,8 +1366,8 @@ pp_status pp_se2_launch_fast(pp_handle h, uint32_t x0, uint32_t y0, uint32_t x1,
             for (uint32_t i = 0; i < n_tiles; ++i)
                 order[i] = (tx_lo + order[i] % (tx_hi - tx_lo)) | (ty_lo + order[i] / (tx_hi - tx_lo)) << 16;
             PP_CUDA(h, pp_reserve(pl->d_tile_order, pl->order_cap, order.size()));
+            // (pageable source: the call returns once the data has been staged, `order` may go out of scope)
             PP_CUDA(h, cudaMemcpyAsync(pl->d_tile_order, order.data(), order.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, h->stream));
-            PP_CUDA(h, cudaStreamSynchronize(h->stream));  // `order` is pageable and goes out of scope
             std::memcpy(pl->order_key, key, sizeof(key));
             if (std::getenv("PP_SE2_DEBUG"))
             {

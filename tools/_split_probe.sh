@@ -1,4 +1,3 @@
-python -m pytest tests/test_gpu_volume.py -x -q 2>&1 | tail -3
-BANDS=512,1024,2048,4096 python tools/band_probe.py 10
-python tools/k1_probe.py box 10
-python tools/k1_probe.py solid 10
+for t in 8 9 10 11 12 13; do echo "tables $t"; PP_SE2_MAX_TABLES=$t BANDS=512 python tools/band_probe.py 20; done
+echo no tma; PP_SE2_NO_TMA=1 BANDS=512 python tools/band_probe.py 20
+echo rows32; PP_SE2_TILE_ROWS=32 BANDS=512 python tools/band_probe.py 20
