@@ -1360,6 +1360,16 @@ pp_status pp_se2_launch_fast(pp_handle h, uint32_t x0, uint32_t y0, uint32_t x1,
                         weight[(ty - ty_lo) * (tx_hi - tx_lo) + (tx - tx_lo)] += (cx == 2 || cy == 2) ? 2u * pairs : 1u;
                     }
                 }
+            // tiles whose halo leaves the map stage through the bounds-tested path: ahead of the interior ones as well
+            for (uint32_t ty = ty_lo; ty < ty_hi; ++ty)
+                for (uint32_t tx = tx_lo; tx < tx_hi; ++tx)
+                {
+                    const long long cx0 = static_cast<long long>(tx) * FT_W - pl->R, cy0 = static_cast<long long>(ty) * pl->TH - pl->R;
+                    const bool inside = cx0 >= 0 && cy0 >= 0 && cx0 + FT_W + 2 * pl->R <= static_cast<long long>(pl->W) &&
+                                        cy0 + pl->TH + 2 * pl->R <= static_cast<long long>(pl->H);
+                    uint32_t &wv = weight[(ty - ty_lo) * (tx_hi - tx_lo) + (tx - tx_lo)];
+                    wv = 2u * wv + (inside ? 0u : 1u);
+                }
             for (uint32_t i = 0; i < n_tiles; ++i)
                 order[i] = i;
             std::stable_sort(order.begin(), order.end(), [&](uint32_t p, uint32_t q) { return weight[p] > weight[q]; });
