@@ -367,6 +367,21 @@ pp_status pp_occupancy_update_rect(pp_handle h, uint32_t x0, uint32_t y0, uint32
 pp_status pp_occupancy_download(pp_handle h, int8_t *occ_out);
 pp_status pp_costmap_from_occupancy(pp_handle h, const pp_layer_params *params);
 
+/* The follower's costmap is a rolling window (src/path_follower/config/params.yaml:12-24: rolling_window true,
+ * width = height = 10 m at 0.05 m, StaticLayer + InflationLayer): costmap_2d moves the window's origin with the
+ * robot (Costmap2D::updateOrigin), the static layer copies the part of the map under it into the master grid
+ * (cells beyond the map keep the default value, NO_INFORMATION with track_unknown_space) and the inflation layer
+ * sees the window's own cells only. pp_costmap_window_from_occupancy does that in one launch: the costmap of `h`
+ * becomes the win_w x win_h window whose cell (0, 0) lies over cell (origin_x, origin_y) of the occupancy grid
+ * held by `src` (the same handle or another one on the same device; the origin may be negative or beyond the
+ * grid). pp_obstacles_extract, pp_radius_topk and the SE2 volume of `h` then work on the window. Same
+ * nearest-obstacle inflation as above (parity with costmap_2d itself unpinned). pp_window_origin_cell gives the
+ * origin along one axis as costmap_2d computes it from the robot's position, the window's size in metres, the
+ * resolution and the map's origin. */
+pp_status pp_costmap_window_from_occupancy(pp_handle h, pp_handle src, int32_t origin_x, int32_t origin_y, uint32_t win_w,
+                                           uint32_t win_h, const pp_layer_params *params);
+int32_t pp_window_origin_cell(double robot, double window_size_m, double resolution, double map_origin);
+
 #ifdef __cplusplus
 }
 #endif

@@ -251,6 +251,27 @@ class Port:
     def costmap_from_occupancy(self, occ, params, how="nearest"):
         return self.inflate(self.static_layer(occ, params), params, how)
 
+    def costmap_window_from_occupancy(self, occ, origin_x, origin_y, win_w, win_h, params, how="nearest"):
+        """The follower's rolling window (path_follower/config/params.yaml:12-24): the part of the map under the
+        window, unknown beyond the map (costmap_2d leaves the master grid's default there, which is what the static
+        layer makes of an unknown cell), inflated from the window's own cells only."""
+        occ = np.asarray(occ, np.int8)
+        H, W = occ.shape
+        win = np.full((win_h, win_w), np.int8(params.unknown_cost_value), np.int8)
+        x0, y0 = max(0, origin_x), max(0, origin_y)
+        x1, y1 = min(W, origin_x + win_w), min(H, origin_y + win_h)
+        if x1 > x0 and y1 > y0:
+            win[y0 - origin_y:y1 - origin_y, x0 - origin_x:x1 - origin_x] = occ[y0:y1, x0:x1]
+        return self.costmap_from_occupancy(win, params, how)
+
+    @staticmethod
+    def window_origin_cell(robot, window_size_m, resolution, map_origin):
+        """Costmap2D::updateOrigin (window grid starting at 0, whole cells, truncation toward zero) followed by the
+        static layer's worldToMap of the centre of the window's first cell."""
+        cell_o = int((robot - window_size_m / 2.0) / resolution)
+        grid_o = 0.0 + cell_o * resolution
+        return int(np.floor((grid_o + 0.5 * resolution - map_origin) / resolution))
+
     # ---- obstacle edges (oracle/teb_edges.c) ----
     def robot_model(self, numbers):
         """-> (vertices[nv,2] (empty for a circle), inscribed radius, circumscribed radius)"""

@@ -23,6 +23,7 @@ SYMBOLS = [
     "pp_se2_volume_ipc_export", "pp_se2_volume_ipc_open", "pp_se2_volume_set_push", "pp_se2_volume_set_rows",
     "pp_occupancy_from_image", "pp_occupancy_upload", "pp_occupancy_update_rect", "pp_occupancy_download",
     "pp_costmap_from_occupancy", "pp_robot_model_set", "pp_obstacle_edges",
+    "pp_costmap_window_from_occupancy", "pp_window_origin_cell",
 ]
 
 _vp = C.c_void_p
@@ -147,6 +148,9 @@ def load():
     L.pp_occupancy_update_rect.argtypes = [_vp, _u32, _u32, _u32, _u32, _vp, C.c_size_t]
     L.pp_occupancy_download.argtypes = [_vp, _vp]
     L.pp_costmap_from_occupancy.argtypes = [_vp, C.POINTER(LayerParams)]
+    L.pp_costmap_window_from_occupancy.argtypes = [_vp, _vp, C.c_int32, C.c_int32, _u32, _u32, C.POINTER(LayerParams)]
+    L.pp_window_origin_cell.argtypes = [C.c_double, C.c_double, C.c_double, C.c_double]
+    L.pp_window_origin_cell.restype = C.c_int32
     L.pp_robot_model_set.argtypes = [_vp, _vp, _u32, C.POINTER(C.c_double), C.POINTER(C.c_double)]
     L.pp_obstacle_edges.argtypes = [_vp, _vp, _u32, _u32, C.POINTER(ObstacleEdgeParams), _vp, _vp]
     _lib = L
@@ -272,6 +276,12 @@ class Handle:
         p = params if params is not None else LayerParams.make()
         self._ck(self.L.pp_costmap_from_occupancy(self.h, C.byref(p)))
         self.H, self.W = self.occ_H, self.occ_W
+
+    def costmap_window_from_occupancy(self, src, origin_x, origin_y, win_w, win_h, params=None):
+        """Rolling window: this handle's costmap becomes the win_w x win_h window over `src`'s occupancy grid."""
+        p = params if params is not None else LayerParams.make()
+        self._ck(self.L.pp_costmap_window_from_occupancy(self.h, src.h, int(origin_x), int(origin_y), int(win_w), int(win_h), C.byref(p)))
+        self.H, self.W = int(win_h), int(win_w)
 
     # footprint
     def footprint_from_boundary(self, resolution, boundary, hole):

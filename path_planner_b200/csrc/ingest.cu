@@ -31,7 +31,9 @@ struct IngestArgs
     const int8_t *occ;
     uint8_t *cost;
     const uint8_t *infl;  // cost by squared distance, 0..R*R
-    uint32_t W, H;
+    uint32_t W, H;          // the costmap that is written
+    uint32_t occ_W, occ_H;  // the occupancy grid it is cut from: costmap cell (x, y) is occupancy cell (x + ox, y + oy)
+    int ox, oy;             // (0, 0 and equal sizes for the whole map; a rolling window otherwise)
     uint32_t rx0, ry0, rx1, ry1;  // cells to write, half-open
     uint32_t tile_x0, tile_y0;    // tile index of block (0, 0)
     int R;
@@ -77,7 +79,11 @@ __global__ void __launch_bounds__(IT_THREADS) ingest_kernel(const IngestArgs a)
             const int r = i / cols, c = i - r * cols;
             const int x = x_base + c, y = y_base + r;
             inside[b] = i < cols * rows && x >= 0 && y >= 0 && x < static_cast<int>(a.W) && y < static_cast<int>(a.H);
-            raw[b] = inside[b] ? __ldg(a.occ + static_cast<size_t>(y) * a.W + x) : static_cast<int8_t>(0);
+            // a window cell beyond the occupancy grid keeps the master grid's default value, which is what
+            // the static layer makes of an unknown cell
+            const int xs = x + a.ox, ys = y + a.oy;
+            const bool in_occ = xs >= 0 && ys >= 0 && xs < static_cast<int>(a.occ_W) && ys < static_cast<int>(a.occ_H);
+            raw[b] = inside[b] && in_occ ? __ldg(a.occ + static_cast<size_t>(ys) * a.occ_W + xs) : static_cast<int8_t>(a.unknown);
         }
 #pragma unroll
         for (int b = 0; b < BATCH; ++b)
@@ -86,7 +92,7 @@ __global__ void __launch_bounds__(IT_THREADS) ingest_kernel(const IngestArgs a)
             if (i >= cols * rows)
                 break;
             const int r = i / cols, c = i - r * cols;
-            // cells outside the grid hold no obstacle
+            // cells outside the costmap hold no obstacle (a window is inflated from its own cells only)
             const uint8_t v = inside[b] ? interpret(static_cast<uint8_t>(raw[b]), a) : FREE_SPACE;
             s_stat[r * PITCH + c] = v;
             any_lethal |= (v == LETHAL);
@@ -287,29 +293,29 @@ pp_status pp_occupancy_download(pp_handle h, int8_t *occ_out)
     return PP_OK;
 }
 
-pp_status pp_costmap_from_occupancy(pp_handle h, const pp_layer_params *params)
+namespace
 {
-    if (!h)
-        return PP_ERR_INVALID;
-    PP_REQUIRE(h, params, PP_ERR_INVALID, "pp_costmap_from_occupancy: null params");
-    PP_REQUIRE(h, h->d_occ, PP_ERR_STATE, "pp_costmap_from_occupancy: no occupancy grid yet");
-    pp_layer_params p = *params;
+// Checks the layer parameters, fills the handle's cost-by-squared-distance table when they changed; returns the
+// clamped parameters, the inflation radius in cells and whether the table is new.
+pp_status prepare_layers(pp_handle h, const pp_layer_params *params, const char *who, pp_layer_params &p, int &R, bool &params_changed)
+{
+    PP_REQUIRE(h, params, PP_ERR_INVALID, "%s: null params", who);
+    p = *params;
     PP_REQUIRE(h, p.resolution > 0.0 && p.inflation_radius >= 0.0 && p.inscribed_radius >= 0.0, PP_ERR_INVALID,
-               "pp_costmap_from_occupancy: resolution must be > 0, radii >= 0");
+               "%s: resolution must be > 0, radii >= 0", who);
     p.lethal_threshold = std::max(std::min(p.lethal_threshold, 100), 0);  // as StaticLayer clamps it
     // Costmap2D::cellDistance
     const double cells = std::max(0.0, std::ceil(p.inflation_radius / p.resolution));
-    PP_REQUIRE(h, cells <= MAX_R, PP_ERR_RANGE, "pp_costmap_from_occupancy: inflation radius of %.0f cells exceeds %d",
-               cells, MAX_R);
-    const int R = static_cast<int>(cells);
+    PP_REQUIRE(h, cells <= MAX_R, PP_ERR_RANGE, "%s: inflation radius of %.0f cells exceeds %d", who, cells, MAX_R);
+    R = static_cast<int>(cells);
     PP_CUDA(h, cudaSetDevice(h->device));
 
     const pp_layer_params &q = h->layer;
-    const bool params_changed = !h->layer_valid || q.track_unknown_space != p.track_unknown_space ||
-                                q.lethal_threshold != p.lethal_threshold || q.unknown_cost_value != p.unknown_cost_value ||
-                                q.trinary_costmap != p.trinary_costmap || q.inflate_unknown != p.inflate_unknown ||
-                                q.resolution != p.resolution || q.inscribed_radius != p.inscribed_radius ||
-                                q.inflation_radius != p.inflation_radius || q.cost_scaling_factor != p.cost_scaling_factor;
+    params_changed = !h->layer_valid || q.track_unknown_space != p.track_unknown_space ||
+                     q.lethal_threshold != p.lethal_threshold || q.unknown_cost_value != p.unknown_cost_value ||
+                     q.trinary_costmap != p.trinary_costmap || q.inflate_unknown != p.inflate_unknown ||
+                     q.resolution != p.resolution || q.inscribed_radius != p.inscribed_radius ||
+                     q.inflation_radius != p.inflation_radius || q.cost_scaling_factor != p.cost_scaling_factor;
     if (params_changed)
     {
         // cached_costs_[i][j] = computeCost(hypot(i, j)) re-indexed by i*i + j*j
@@ -322,7 +328,7 @@ pp_status pp_costmap_from_occupancy(pp_handle h, const pp_layer_params *params)
                     continue;
                 const int c = compute_cost(std::hypot(static_cast<double>(i), static_cast<double>(j)), p);
                 PP_REQUIRE(h, tab[d2] < 0 || tab[d2] == c, PP_ERR_RANGE,
-                           "pp_costmap_from_occupancy: inflation cost is not a function of the squared distance at (%d,%d)", i, j);
+                           "%s: inflation cost is not a function of the squared distance at (%d,%d)", who, i, j);
                 tab[d2] = c;
             }
         std::vector<uint8_t> bytes(tab.size());
@@ -334,21 +340,54 @@ pp_status pp_costmap_from_occupancy(pp_handle h, const pp_layer_params *params)
         h->layer = p;
         h->layer_valid = true;
     }
+    return PP_OK;
+}
+
+// the handle's costmap becomes a W x H grid that is about to be written in full
+pp_status resize_costmap(pp_handle h, uint32_t W, uint32_t H)
+{
+    if (W != h->W || H != h->H)
+        pp_se2_plan_free(h);
+    PP_CUDA(h, pp_reserve(h->d_cost, h->cost_cap, static_cast<size_t>(W) * H));
+    h->W = W;
+    h->H = H;
+    h->dirty = false;  // like a full upload: the volume is to be rebuilt
+    h->vol_valid = false;
+    return PP_OK;
+}
+
+void fill_layer_args(IngestArgs &a, const pp_layer_params &p, int R)
+{
+    a.R = R;
+    a.unknown = static_cast<uint8_t>(p.unknown_cost_value);
+    a.lethal_threshold = static_cast<uint8_t>(p.lethal_threshold);
+    a.track_unknown = p.track_unknown_space, a.trinary = p.trinary_costmap, a.inflate_unknown = p.inflate_unknown;
+}
+}  // namespace
+
+pp_status pp_costmap_from_occupancy(pp_handle h, const pp_layer_params *params)
+{
+    if (!h)
+        return PP_ERR_INVALID;
+    PP_REQUIRE(h, h->d_occ, PP_ERR_STATE, "pp_costmap_from_occupancy: no occupancy grid yet");
+    pp_layer_params p;
+    int R = 0;
+    bool params_changed = false;
+    pp_status st = prepare_layers(h, params, "pp_costmap_from_occupancy", p, R, params_changed);
+    if (st != PP_OK)
+        return st;
 
     const uint32_t W = h->occ_W, H = h->occ_H;
-    const bool full = params_changed || h->occ_all || !h->d_cost || h->W != W || h->H != H;
+    const bool full = params_changed || h->occ_all || !h->d_cost || h->W != W || h->H != H || h->cost_is_window;
     if (!full && !h->occ_dirty)
         return PP_OK;
     IngestArgs a{};
     if (full)
     {
-        if (W != h->W || H != h->H)
-            pp_se2_plan_free(h);
-        PP_CUDA(h, pp_reserve(h->d_cost, h->cost_cap, static_cast<size_t>(W) * H));
-        h->W = W;
-        h->H = H;
-        h->dirty = false;  // like a full upload: the volume is to be rebuilt
-        h->vol_valid = false;
+        st = resize_costmap(h, W, H);
+        if (st != PP_OK)
+            return st;
+        h->cost_is_window = false;
         a.rx0 = 0, a.ry0 = 0, a.rx1 = W, a.ry1 = H;
     }
     else
@@ -373,11 +412,10 @@ pp_status pp_costmap_from_occupancy(pp_handle h, const pp_layer_params *params)
     a.occ = h->d_occ;
     a.cost = h->d_cost;
     a.infl = h->d_infl;
-    a.W = W, a.H = H, a.R = R;
+    a.W = a.occ_W = W, a.H = a.occ_H = H;
+    a.ox = a.oy = 0;
     a.tile_x0 = a.rx0 / IT_W, a.tile_y0 = a.ry0 / IT_H;
-    a.unknown = static_cast<uint8_t>(p.unknown_cost_value);
-    a.lethal_threshold = static_cast<uint8_t>(p.lethal_threshold);
-    a.track_unknown = p.track_unknown_space, a.trinary = p.trinary_costmap, a.inflate_unknown = p.inflate_unknown;
+    fill_layer_args(a, p, R);
     const dim3 grid((a.rx1 + IT_W - 1) / IT_W - a.tile_x0, (a.ry1 + IT_H - 1) / IT_H - a.tile_y0);
     ingest_kernel<<<grid, IT_THREADS, 0, h->stream>>>(a);
     PP_CUDA(h, cudaGetLastError());
@@ -385,4 +423,57 @@ pp_status pp_costmap_from_occupancy(pp_handle h, const pp_layer_params *params)
     h->occ_dirty = false;
     h->occ_all = false;
     return PP_OK;
+}
+
+// The follower's rolling window (path_follower/config/params.yaml:12-24): see include/pp_b200.h
+pp_status pp_costmap_window_from_occupancy(pp_handle h, pp_handle src, int32_t origin_x, int32_t origin_y, uint32_t win_w, uint32_t win_h,
+                                           const pp_layer_params *params)
+{
+    if (!h)
+        return PP_ERR_INVALID;
+    PP_REQUIRE(h, src && src->d_occ, PP_ERR_STATE, "pp_costmap_window_from_occupancy: the source handle holds no occupancy grid");
+    PP_REQUIRE(h, src->device == h->device, PP_ERR_INVALID, "pp_costmap_window_from_occupancy: handles on devices %d and %d", h->device,
+               src->device);
+    PP_REQUIRE(h, win_w > 0 && win_h > 0 && win_w <= 32768 && win_h <= 32768, PP_ERR_RANGE,
+               "pp_costmap_window_from_occupancy: window of %ux%u cells", win_w, win_h);
+    PP_REQUIRE(h, origin_x > -(1 << 30) && origin_x < (1 << 30) && origin_y > -(1 << 30) && origin_y < (1 << 30), PP_ERR_RANGE,
+               "pp_costmap_window_from_occupancy: origin (%d, %d)", origin_x, origin_y);
+    pp_layer_params p;
+    int R = 0;
+    bool params_changed = false;
+    pp_status st = prepare_layers(h, params, "pp_costmap_window_from_occupancy", p, R, params_changed);
+    if (st != PP_OK)
+        return st;
+    if (src != h)
+        PP_CUDA(h, cudaStreamSynchronize(src->stream));  // the grid's uploads run on the source handle's stream
+    st = resize_costmap(h, win_w, win_h);
+    if (st != PP_OK)
+        return st;
+    h->cost_is_window = true;  // pp_costmap_from_occupancy on this handle starts over
+    IngestArgs a{};
+    a.occ = src->d_occ;
+    a.cost = h->d_cost;
+    a.infl = h->d_infl;
+    a.W = win_w, a.H = win_h;
+    a.occ_W = src->occ_W, a.occ_H = src->occ_H;
+    a.ox = origin_x, a.oy = origin_y;
+    a.rx0 = 0, a.ry0 = 0, a.rx1 = win_w, a.ry1 = win_h;
+    a.tile_x0 = a.tile_y0 = 0;
+    fill_layer_args(a, p, R);
+    const dim3 grid((win_w + IT_W - 1) / IT_W, (win_h + IT_H - 1) / IT_H);
+    ingest_kernel<<<grid, IT_THREADS, 0, h->stream>>>(a);
+    PP_CUDA(h, cudaGetLastError());
+    h->launches++;
+    return PP_OK;
+}
+
+// Costmap2D::updateOrigin (the window's own grid starts at 0 and moves in whole cells, truncating toward zero)
+// followed by StaticLayer::updateCosts' worldToMap of the window's first cell centre
+int32_t pp_window_origin_cell(double robot, double window_size_m, double resolution, double map_origin)
+{
+    const double wanted = robot - window_size_m / 2.0;
+    const int cell_o = static_cast<int>(wanted / resolution);
+    const double grid_o = 0.0 + cell_o * resolution;
+    const double centre = grid_o + (0 + 0.5) * resolution;
+    return static_cast<int32_t>(std::floor((centre - map_origin) / resolution));
 }

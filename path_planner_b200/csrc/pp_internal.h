@@ -96,6 +96,7 @@ struct pp_ctx
     size_t occ_cap = 0;
     uint32_t occ_W = 0, occ_H = 0;
     bool occ_dirty = false, occ_all = false;  // a rectangle / the whole grid changed since the last costmap
+    bool cost_is_window = false;              // the costmap is a rolling window, not the occupancy grid's own
     uint32_t occ_x0 = 0, occ_y0 = 0, occ_x1 = 0, occ_y1 = 0;  // half-open
     uint8_t *d_img = nullptr;  // map image as uploaded
     size_t img_cap = 0;

@@ -159,3 +159,71 @@ def test_errors(handle):
         handle.costmap_from_occupancy(LayerParams.make(resolution=0.0))
     with pytest.raises(PPError):
         handle.occupancy_update_rect(60, 60, np.zeros((8, 8), np.int8))  # sticks out
+
+
+# ---- the follower's rolling window (path_follower/config/params.yaml:12-24) ---------------------------
+
+@pytest.mark.parametrize("origin,win,kw", [
+    ((37, 21), (200, 200), {}),                                 # inside the map: the follower's 10 m x 10 m at 0.05
+    ((-60, 150), (200, 200), {}),                               # sticks out to the left: unknown beyond the map
+    ((310, 260), (200, 200), {"track_unknown_space": 0}),       # over the far corner, unknown taken as free
+    ((-500, -500), (64, 48), {}),                               # entirely off the map
+    ((100, 90), (131, 77), {"inflate_unknown": 1}),             # ragged size
+    ((-10, -10), (420, 380), {"inflation_radius": 0.8}),        # larger than the map
+])
+def test_rolling_window_matches_oracle(handle, port, origin, win, kw):
+    from path_planner_b200 import capi
+    lp, olp = both(**kw)
+    occ = random_occupancy(400, 350, 61)
+    src = capi.Handle(0)  # the global map's handle
+    try:
+        src.occupancy_upload(occ)
+        handle.costmap_window_from_occupancy(src, origin[0], origin[1], win[0], win[1], lp)
+        got = handle.costmap_download()
+        assert got.shape == (win[1], win[0])
+        assert np.array_equal(got, port.costmap_window_from_occupancy(occ, origin[0], origin[1], win[0], win[1], olp))
+    finally:
+        src.close()
+
+
+def test_rolling_window_follows_the_robot_and_feeds_the_obstacle_search(handle, port):
+    """A window moved along a path on ONE handle that also holds the map; every window equals the oracle's, a window
+    far from the edges equals the crop of the whole-map costmap away from its rim, and the obstacle extraction of
+    the follower (K3a) runs on the window."""
+    lp, olp = both()
+    occ = random_occupancy(600, 500, 62, p_lethal=0.004)
+    handle.occupancy_upload(occ)
+    handle.costmap_from_occupancy(lp)
+    whole = handle.costmap_download()
+    R = 10  # ceil(0.5 / 0.05)
+    for robot in [(5.0, 5.0), (12.37, 9.81), (24.99, 20.02), (0.3, 24.0)]:
+        ox = handle.L.pp_window_origin_cell(robot[0], 10.0, 0.05, 0.0)
+        oy = handle.L.pp_window_origin_cell(robot[1], 10.0, 0.05, 0.0)
+        assert (ox, oy) == (port.window_origin_cell(robot[0], 10.0, 0.05, 0.0), port.window_origin_cell(robot[1], 10.0, 0.05, 0.0))
+        handle.costmap_window_from_occupancy(handle, ox, oy, 200, 200, lp)
+        got = handle.costmap_download()
+        assert np.array_equal(got, port.costmap_window_from_occupancy(occ, ox, oy, 200, 200, olp))
+        if ox >= 0 and oy >= 0 and ox + 200 <= 600 and oy + 200 <= 500:
+            assert np.array_equal(got[R:-R, R:-R], whole[oy + R:oy + 200 - R, ox + R:ox + 200 - R])
+        # the window's world origin is (ox, oy) cells from the map's; the robot sits in its middle
+        origin_w = (ox * 0.05, oy * 0.05)
+        pose = (robot[0], robot[1], 0.4)
+        pts = handle.obstacles_extract(0.05, origin_w, pose, 4.5, 1.5)
+        want = port.extract_obstacles(got, 0.05, origin_w, pose, 4.5, 1.5)
+        assert np.array_equal(pts, want)
+    # back to the whole map on the same handle
+    handle.costmap_from_occupancy(lp)
+    assert np.array_equal(handle.costmap_download(), whole)
+
+
+def test_rolling_window_errors(handle):
+    from path_planner_b200 import capi
+    lp, _ = both()
+    with pytest.raises(PPError) as e:
+        handle.costmap_window_from_occupancy(handle, 0, 0, 200, 200, lp)  # no occupancy grid
+    assert e.value.status == 2
+    handle.occupancy_upload(np.zeros((64, 64), np.int8))
+    with pytest.raises(PPError):
+        handle.costmap_window_from_occupancy(handle, 0, 0, 0, 200, lp)
+    with pytest.raises(PPError):
+        handle.costmap_window_from_occupancy(handle, 0, 0, 40000, 10, lp)

@@ -101,3 +101,28 @@ def test_nearest_bounds_propagation(port, seed, W, H, kw):
     assert (near >= static)[static != 255].all()
     # obstacles and cells out of reach are left alone
     assert np.array_equal(near[static == 254], static[static == 254])
+
+
+def test_rolling_window_of_the_oracle(port):
+    """The follower's window (path_follower/config/params.yaml:12-24): away from its rim a window inside the map is
+    the crop of the whole-map costmap, beyond the map it is NO_INFORMATION (or free without track_unknown_space),
+    and obstacles outside the window do not inflate into it."""
+    lp = oracle.layer_params()
+    occ = random_occupancy(300, 260, 71, p_lethal=0.005)
+    whole = port.costmap_from_occupancy(occ, lp, "nearest")
+    R = 10
+    win = port.costmap_window_from_occupancy(occ, 40, 30, 200, 200, lp)
+    assert np.array_equal(win[R:-R, R:-R], whole[30 + R:230 - R, 40 + R:240 - R])
+    out = port.costmap_window_from_occupancy(occ, -50, 100, 120, 80, lp)
+    assert (out[:, :50 - R] == 255).all()
+    free = port.costmap_window_from_occupancy(occ, -50, 100, 120, 80, oracle.layer_params(track_unknown_space=0))
+    assert (free[:, :50 - R] == 0).all()
+    one = np.zeros((100, 100), np.int8)
+    one[50, 49] = 100  # just left of a window that starts at x = 50
+    assert (port.costmap_window_from_occupancy(one, 50, 0, 50, 100, lp) == 0).all()
+    assert port.costmap_window_from_occupancy(one, 49, 0, 50, 100, lp)[50, 0] == 254
+    # Costmap2D::updateOrigin truncates toward zero on the window's own grid
+    assert port.window_origin_cell(5.0, 10.0, 0.05, 0.0) == 0
+    assert port.window_origin_cell(12.37, 10.0, 0.05, 0.0) == 147
+    assert port.window_origin_cell(0.3, 10.0, 0.05, 0.0) == -94 + 0  # int(-4.7 / 0.05) = -94
+    assert port.window_origin_cell(12.37, 10.0, 0.05, -10.0) == 347
