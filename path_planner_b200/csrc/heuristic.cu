@@ -42,6 +42,19 @@ constexpr uint32_t ROUND_GRID = 148 * PP_HT_GRID;  // CTAs per relaxation round:
 constexpr uint32_t INACTIVE = 0xFFFFFFFFu;  // tile key: bit pattern of the smallest pending value, or this
 constexpr int N_COUNTERS = 16;              // [0..3] tiles flagged per round, [4] visits, [5] sweeps, [6] rounds that had work, [8..11] min key per round
 
+#ifdef PP_HEUR_TIMELINE
+// dev build: per tile visit {round, tile, kernel entry, after the dependency wait, work list read, tile staged,
+// converged, published (ns, %globaltimer), sweeps}
+__device__ unsigned long long heur_tl[9 * (1 << 17)];
+__device__ unsigned int heur_tl_n;
+__device__ __forceinline__ unsigned long long gtime()
+{
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+#endif
+
 __global__ void heur_init_kernel(float *field, size_t n, uint32_t *flags, size_t n_flags, uint32_t goal_index,
                                  uint32_t goal_tile)
 {
@@ -83,8 +96,14 @@ __global__ void __launch_bounds__(HT_THREADS) heur_round_kernel(float *__restric
     // Programmatic dependent launch: the CTAs of round r+1 may be scheduled while round r drains (most
     // CTAs of a round find no work and leave at once); they park here until round r has completed and its
     // writes are visible. Without the launch attribute both instructions do nothing.
+#ifdef PP_HEUR_TIMELINE
+    const unsigned long long tl_entry = gtime();
+#endif
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     asm volatile("griddepcontrol.wait;" ::: "memory");
+#ifdef PP_HEUR_TIMELINE
+    const unsigned long long tl_wait = gtime();
+#endif
     const uint32_t nT = tiles_x * tiles_y;
     uint32_t *cur = flags + (round & 1) * nT;
     uint32_t *nxt = flags + ((round + 1) & 1) * nT;
@@ -135,6 +154,9 @@ __global__ void __launch_bounds__(HT_THREADS) heur_round_kernel(float *__restric
     }
     __syncthreads();
     const uint32_t n_mine = s_n_mine;
+#ifdef PP_HEUR_TIMELINE
+    const unsigned long long tl_list = gtime();
+#endif
     // Pass 2: relax the collected tiles, one after the other
     for (uint32_t m = 0; m < n_mine; ++m)
     {
@@ -192,6 +214,9 @@ __global__ void __launch_bounds__(HT_THREADS) heur_round_kernel(float *__restric
         WD[r][c] = cv[j] < 256u ? s_travel[256 + cv[j]] : INF;
     }
     __syncthreads();
+#ifdef PP_HEUR_TIMELINE
+    const unsigned long long tl_staged = gtime();
+#endif
 
     // A warp owns a band of 4 consecutive tile rows, lane = column, and keeps its 4 x 32 values and their
     // travel weights in registers. Left / right neighbours come from the neighbouring lanes by shuffle
@@ -265,6 +290,9 @@ __global__ void __launch_bounds__(HT_THREADS) heur_round_kernel(float *__restric
         changed = __syncthreads_or(local);
         ++iters;
     } while (changed);
+#ifdef PP_HEUR_TIMELINE
+    const unsigned long long tl_conv = gtime();
+#endif
 
     // write back what changed and note which borders moved
     if (tid == 0)
@@ -310,6 +338,18 @@ __global__ void __launch_bounds__(HT_THREADS) heur_round_kernel(float *__restric
             atomicMin(&counters[8 + ((round + 1) & 3)], k);
         }
     }
+#ifdef PP_HEUR_TIMELINE
+    __syncthreads();
+    if (tid == 0)
+    {
+        const unsigned int slot = atomicAdd(&heur_tl_n, 1u);
+        if (slot < (1u << 17))
+        {
+            unsigned long long *o = heur_tl + 9ull * slot;
+            o[0] = round, o[1] = tile, o[2] = tl_entry, o[3] = tl_wait, o[4] = tl_list, o[5] = tl_staged, o[6] = tl_conv, o[7] = gtime(), o[8] = iters;
+        }
+    }
+#endif
     }  // pass 2
     }  // batches of the work list
 }
@@ -413,6 +453,28 @@ pp_status pp_heuristic_build(pp_handle h, uint32_t goal_x, uint32_t goal_y, floa
         done = h->h_counter[round & 3] == 0;
         PP_REQUIRE(h, done || round < max_rounds, PP_ERR_STATE, "pp_heuristic_build: relaxation did not converge");
     }
+#ifdef PP_HEUR_TIMELINE
+    if (const char *path = getenv("PP_HEUR_TIMELINE_FILE"))
+    {
+        unsigned int n_tl = 0;
+        cudaMemcpyFromSymbol(&n_tl, heur_tl_n, sizeof(n_tl));
+        n_tl = std::min(n_tl, 1u << 17);
+        std::vector<unsigned long long> tl(9ull * n_tl);
+        cudaMemcpyFromSymbol(tl.data(), heur_tl, tl.size() * sizeof(unsigned long long));
+        if (FILE *f = fopen(path, "w"))
+        {
+            for (unsigned int i = 0; i < n_tl; ++i)
+            {
+                for (int k = 0; k < 9; ++k)
+                    fprintf(f, "%llu ", tl[9ull * i + k]);
+                fprintf(f, "\n");
+            }
+            fclose(f);
+        }
+        n_tl = 0;
+        cudaMemcpyToSymbol(heur_tl_n, &n_tl, sizeof(n_tl));
+    }
+#endif
     h->heur_rounds = h->h_counter[6];  // rounds that had work
     h->heur_tile_visits = h->h_counter[4];
     h->heur_sweeps = h->h_counter[5];
