@@ -898,12 +898,14 @@ struct Se2Plan
     size_t region_cap = 0;
     uint64_t region_key[6] = {~0ull, 0, 0, 0, 0, 0};
     // dispatch order of the tiles of the last region (cached the same way)
-    uint32_t *d_tile_order = nullptr;
-    size_t order_cap = 0;
-    uint64_t order_key[5] = {~0ull, 0, 0, 0, 0};
+    // [0]: the whole map (kept for the life of the plan), [1]: the last other region (a row band, a dirty rectangle)
+    uint32_t *d_tile_order[2] = {nullptr, nullptr};
+    size_t order_cap[2] = {0, 0};
+    uint64_t order_key[2][5] = {{~0ull, 0, 0, 0, 0}, {~0ull, 0, 0, 0, 0}};
     ~Se2Plan()
     {
-        cudaFree(d_tile_order);
+        cudaFree(d_tile_order[0]);
+        cudaFree(d_tile_order[1]);
         cudaFree(d_region_work);
         cudaFree(d_xclass);
         cudaFree(d_yclass);
@@ -1339,12 +1341,13 @@ pp_status pp_se2_launch_fast(pp_handle h, uint32_t x0, uint32_t y0, uint32_t x1,
         }
     }
     const uint32_t n_tiles = (tx_hi - tx_lo) * (ty_hi - ty_lo);  // one CTA per tile
+    const int oc = (tx_lo == 0 && ty_lo == 0 && tx_hi >= pl->tiles_x && ty_hi >= pl->tiles_y) ? 0 : 1;  // which cached order
     // Dispatch order: CTAs start in index order, so the tiles with the most work go first (a tile that a range
     // boundary crosses evaluates such a bin once per class pair and stores through masks -- with the boundaries
     // near x = 0 that is the left-hand tile column, twice as long as the others) and none of them ends the launch.
     {
         const uint64_t key[5] = {tx_lo, tx_hi, ty_lo, ty_hi, 1};  // weighed over all bins: one order per region
-        if (std::memcmp(key, pl->order_key, sizeof(key)) != 0)
+        if (std::memcmp(key, pl->order_key[oc], sizeof(key)) != 0)
         {
             std::vector<uint32_t> weight(n_tiles, 0), order(n_tiles);
             for (uint32_t t = 0; t < pl->n_theta; ++t)
@@ -1375,10 +1378,10 @@ pp_status pp_se2_launch_fast(pp_handle h, uint32_t x0, uint32_t y0, uint32_t x1,
             std::stable_sort(order.begin(), order.end(), [&](uint32_t p, uint32_t q) { return weight[p] > weight[q]; });
             for (uint32_t i = 0; i < n_tiles; ++i)
                 order[i] = (tx_lo + order[i] % (tx_hi - tx_lo)) | (ty_lo + order[i] / (tx_hi - tx_lo)) << 16;
-            PP_CUDA(h, pp_reserve(pl->d_tile_order, pl->order_cap, order.size()));
+            PP_CUDA(h, pp_reserve(pl->d_tile_order[oc], pl->order_cap[oc], order.size()));
             // (pageable source: the call returns once the data has been staged, `order` may go out of scope)
-            PP_CUDA(h, cudaMemcpyAsync(pl->d_tile_order, order.data(), order.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, h->stream));
-            std::memcpy(pl->order_key, key, sizeof(key));
+            PP_CUDA(h, cudaMemcpyAsync(pl->d_tile_order[oc], order.data(), order.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, h->stream));
+            std::memcpy(pl->order_key[oc], key, sizeof(key));
             if (std::getenv("PP_SE2_DEBUG"))
             {
                 std::map<uint32_t, uint32_t> hist;
@@ -1389,7 +1392,7 @@ pp_status pp_se2_launch_fast(pp_handle h, uint32_t x0, uint32_t y0, uint32_t x1,
             }
         }
     }
-    args.tile_order = pl->d_tile_order;
+    args.tile_order = pl->d_tile_order[oc];
     const dim3 grid(n_tiles, 1, 1);
     double sample_sum = 0.0;
     uint64_t fast_pairs = 0, generic_pairs = 0;
