@@ -24,7 +24,11 @@
 namespace
 {
 constexpr int HT = 32;            // tile edge
-constexpr int HT_THREADS = 256;   // 4 cells per thread
+#ifndef PP_HT_BR
+#define PP_HT_BR 4
+#endif
+constexpr int BR = PP_HT_BR;                 // rows of a warp's band = cells per thread
+constexpr int HT_THREADS = 32 * (HT / BR);   // one warp per band, lane = column
 constexpr int HT_PITCH = HT + 2 + 1;
 #ifndef PP_HT_CHECK
 #define PP_HT_CHECK 32
@@ -115,6 +119,10 @@ __global__ void __launch_bounds__(HT_THREADS) heur_round_kernel(float *__restric
         counters[(round + 2) & 3] = 0;               // will count the tiles listed during round+1
         counters[8 + ((round + 2) & 3)] = INACTIVE;  // and hold their smallest key
     }
+    // The first list entry of this thread is requested together with the entry count it depends on (entries past
+    // the count are stale tiles of earlier rounds: loaded, never used): one round trip less at the head of a round.
+    const uint32_t first_entry = blockIdx.x + threadIdx.x * gridDim.x;
+    const uint32_t first_tile = first_entry < nT ? list_cur[first_entry] : 0u;
     const uint32_t n_active = counters[round & 3];
     if (blockIdx.x == 0 && threadIdx.x == 0 && n_active > 0)
         counters[6] = round + 1;  // rounds that had work (the host launches them in batches and overshoots)
@@ -140,7 +148,7 @@ __global__ void __launch_bounds__(HT_THREADS) heur_round_kernel(float *__restric
     const uint32_t entry = base + threadIdx.x * gridDim.x;
     if (entry < n_active)
     {
-        const uint32_t tile = list_cur[entry];
+        const uint32_t tile = base == blockIdx.x ? first_tile : list_cur[entry];
         const uint32_t key = cur[tile];
         if (__uint_as_float(key) > threshold)
         {
@@ -224,10 +232,10 @@ __global__ void __launch_bounds__(HT_THREADS) heur_round_kernel(float *__restric
     // the band from shared memory, re-read after every block-wide vote. Between two votes a warp relaxes
     // its band HT_LOCAL times on its own (Jacobi inside the band); stale values across bands are
     // harmless: values only decrease, towards the same fixed point.
-    const int lane = tid & 31, band = (tid >> 5) * 4, c = lane + 1;
-    float v[4], ws[4], wd[4], edge_l[4], edge_r[4], init[4];
+    const int lane = tid & 31, band = (tid >> 5) * BR, c = lane + 1;
+    float v[BR], ws[BR], wd[BR], edge_l[BR], edge_r[BR], init[BR];
 #pragma unroll
-    for (int k = 0; k < 4; ++k)
+    for (int k = 0; k < BR; ++k)
     {
         const int r = band + k + 1;
         v[k] = init[k] = F[r][c];
@@ -247,14 +255,14 @@ __global__ void __launch_bounds__(HT_THREADS) heur_round_kernel(float *__restric
         for (int d = 0; d < 3; ++d)
         {
             up[d] = F[band][c - 1 + d];
-            dn[d] = F[band + 5][c - 1 + d];
+            dn[d] = F[band + BR + 1][c - 1 + d];
         }
 #pragma unroll 1
         for (int it = 0; it < HT_LOCAL; ++it)
         {
-            float l[4], r[4];
+            float l[BR], r[BR];
 #pragma unroll
-            for (int k = 0; k < 4; ++k)
+            for (int k = 0; k < BR; ++k)
             {
                 l[k] = __shfl_up_sync(0xffffffffu, v[k], 1);
                 r[k] = __shfl_down_sync(0xffffffffu, v[k], 1);
@@ -263,18 +271,18 @@ __global__ void __launch_bounds__(HT_THREADS) heur_round_kernel(float *__restric
                 if (lane == 31)
                     r[k] = edge_r[k];
             }
-            float nv[4];
+            float nv[BR];
 #pragma unroll
-            for (int k = 0; k < 4; ++k)
+            for (int k = 0; k < BR; ++k)
             {
                 const float a0 = k == 0 ? up[0] : l[k - 1], a1 = k == 0 ? up[1] : v[k - 1], a2 = k == 0 ? up[2] : r[k - 1];
-                const float b0 = k == 3 ? dn[0] : l[k + 1], b1 = k == 3 ? dn[1] : v[k + 1], b2 = k == 3 ? dn[2] : r[k + 1];
+                const float b0 = k == BR - 1 ? dn[0] : l[k + 1], b1 = k == BR - 1 ? dn[1] : v[k + 1], b2 = k == BR - 1 ? dn[2] : r[k + 1];
                 const float ms = fminf(fminf(a1, b1), fminf(l[k], r[k]));
                 const float md = fminf(fminf(a0, b2), fminf(a2, b0));
                 nv[k] = fminf(__fadd_rn(ms, ws[k]), __fadd_rn(md, wd[k]));
             }
 #pragma unroll
-            for (int k = 0; k < 4; ++k)
+            for (int k = 0; k < BR; ++k)
                 if (nv[k] < v[k])
                 {
                     v[k] = nv[k];
@@ -284,7 +292,7 @@ __global__ void __launch_bounds__(HT_THREADS) heur_round_kernel(float *__restric
         if (local)
         {
 #pragma unroll
-            for (int k = 0; k < 4; ++k)
+            for (int k = 0; k < BR; ++k)
                 F[band + k + 1][c] = v[k];
         }
         changed = __syncthreads_or(local);
@@ -303,7 +311,7 @@ __global__ void __launch_bounds__(HT_THREADS) heur_round_kernel(float *__restric
         atomicAdd(&counters[5], iters);   // in-tile relaxation sweeps
     }
 #pragma unroll
-    for (int k = 0; k < 4; ++k)
+    for (int k = 0; k < BR; ++k)
     {
         const int r = band + k, c = lane;
         const float val = v[k];
