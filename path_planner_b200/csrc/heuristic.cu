@@ -131,6 +131,7 @@ __global__ void __launch_bounds__(HT_THREADS) heur_round_kernel(float *__restric
     __shared__ float WS[HT][HT];
     __shared__ float WD[HT][HT];
     __shared__ uint32_t edge_min[8];  // smallest new value on each border / corner (bit pattern), INACTIVE if unchanged
+    __shared__ uint32_t s_moved[3];   // bands that changed in a vote of the in-tile relaxation, three votes in rotation
     __shared__ float s_travel[512];
     for (int i = threadIdx.x; i < 512; i += HT_THREADS)
         s_travel[i] = travel[i];
@@ -177,6 +178,8 @@ __global__ void __launch_bounds__(HT_THREADS) heur_round_kernel(float *__restric
     const float INF = __int_as_float(0x7f800000);
     if (tid < 8)
         edge_min[tid] = INACTIVE;
+    if (tid < 3)
+        s_moved[tid] = 0;
     // A tile visit is a chain of latencies, not of bandwidth (a round with a single tile takes as long as
     // one with hundreds): every global load of the visit -- 34 x 34 field values, 32 x 32 costs -- is
     // issued before the first one is used, and the travel weights come from the shared-memory copy.
@@ -246,58 +249,74 @@ __global__ void __launch_bounds__(HT_THREADS) heur_round_kernel(float *__restric
     }
     uint32_t iters = 0;
 
-    int changed;
+    // A band whose own values and whose neighbour bands did not change in the last vote is a fixed point of its
+    // local relaxation with unchanged inputs: its warp sits the next vote out (same result, fewer instructions on
+    // the schedulers the still-moving bands share). s_moved[n % 3] collects the bands that changed in vote n.
+    const uint32_t my_bit = 1u << (tid >> 5);
+    const uint32_t near_bits = my_bit | my_bit << 1 | my_bit >> 1;
+    uint32_t moved = 0xFFFFFFFFu;  // first vote: every band
+    uint32_t slot = 0;
     do
     {
         int local = 0;
-        float up[3], dn[3];  // the rows just outside the band: columns c-1, c, c+1
-#pragma unroll
-        for (int d = 0; d < 3; ++d)
+        if (moved & near_bits)
         {
-            up[d] = F[band][c - 1 + d];
-            dn[d] = F[band + BR + 1][c - 1 + d];
-        }
+            float up[3], dn[3];  // the rows just outside the band: columns c-1, c, c+1
+#pragma unroll
+            for (int d = 0; d < 3; ++d)
+            {
+                up[d] = F[band][c - 1 + d];
+                dn[d] = F[band + BR + 1][c - 1 + d];
+            }
 #pragma unroll 1
-        for (int it = 0; it < HT_LOCAL; ++it)
-        {
-            float l[BR], r[BR];
-#pragma unroll
-            for (int k = 0; k < BR; ++k)
+            for (int it = 0; it < HT_LOCAL; ++it)
             {
-                l[k] = __shfl_up_sync(0xffffffffu, v[k], 1);
-                r[k] = __shfl_down_sync(0xffffffffu, v[k], 1);
-                if (lane == 0)
-                    l[k] = edge_l[k];
-                if (lane == 31)
-                    r[k] = edge_r[k];
-            }
-            float nv[BR];
+                float l[BR], r[BR];
 #pragma unroll
-            for (int k = 0; k < BR; ++k)
-            {
-                const float a0 = k == 0 ? up[0] : l[k - 1], a1 = k == 0 ? up[1] : v[k - 1], a2 = k == 0 ? up[2] : r[k - 1];
-                const float b0 = k == BR - 1 ? dn[0] : l[k + 1], b1 = k == BR - 1 ? dn[1] : v[k + 1], b2 = k == BR - 1 ? dn[2] : r[k + 1];
-                const float ms = fminf(fminf(a1, b1), fminf(l[k], r[k]));
-                const float md = fminf(fminf(a0, b2), fminf(a2, b0));
-                nv[k] = fminf(__fadd_rn(ms, ws[k]), __fadd_rn(md, wd[k]));
-            }
-#pragma unroll
-            for (int k = 0; k < BR; ++k)
-                if (nv[k] < v[k])
+                for (int k = 0; k < BR; ++k)
                 {
-                    v[k] = nv[k];
-                    local = 1;
+                    l[k] = __shfl_up_sync(0xffffffffu, v[k], 1);
+                    r[k] = __shfl_down_sync(0xffffffffu, v[k], 1);
+                    if (lane == 0)
+                        l[k] = edge_l[k];
+                    if (lane == 31)
+                        r[k] = edge_r[k];
                 }
-        }
-        if (local)
-        {
+                float nv[BR];
 #pragma unroll
-            for (int k = 0; k < BR; ++k)
-                F[band + k + 1][c] = v[k];
+                for (int k = 0; k < BR; ++k)
+                {
+                    const float a0 = k == 0 ? up[0] : l[k - 1], a1 = k == 0 ? up[1] : v[k - 1], a2 = k == 0 ? up[2] : r[k - 1];
+                    const float b0 = k == BR - 1 ? dn[0] : l[k + 1], b1 = k == BR - 1 ? dn[1] : v[k + 1], b2 = k == BR - 1 ? dn[2] : r[k + 1];
+                    const float ms = fminf(fminf(a1, b1), fminf(l[k], r[k]));
+                    const float md = fminf(fminf(a0, b2), fminf(a2, b0));
+                    nv[k] = fminf(__fadd_rn(ms, ws[k]), __fadd_rn(md, wd[k]));
+                }
+#pragma unroll
+                for (int k = 0; k < BR; ++k)
+                    if (nv[k] < v[k])
+                    {
+                        v[k] = nv[k];
+                        local = 1;
+                    }
+            }
+            if (local)
+            {
+#pragma unroll
+                for (int k = 0; k < BR; ++k)
+                    F[band + k + 1][c] = v[k];
+            }
+            if (__any_sync(0xffffffffu, local) && lane == 0)
+                atomicOr(&s_moved[slot], my_bit);
         }
-        changed = __syncthreads_or(local);
+        const uint32_t next_slot = slot == 2 ? 0 : slot + 1;
+        if (tid == 0)
+            s_moved[next_slot] = 0;  // last read after the vote before the previous one
+        __syncthreads();
+        moved = s_moved[slot];
+        slot = next_slot;
         ++iters;
-    } while (changed);
+    } while (moved);
 #ifdef PP_HEUR_TIMELINE
     const unsigned long long tl_conv = gtime();
 #endif
