@@ -292,13 +292,17 @@ __global__ void __launch_bounds__(HT_THREADS) heur_round_kernel(float *__restric
                     const float md = fminf(fminf(a0, b2), fminf(a2, b0));
                     nv[k] = fminf(__fadd_rn(ms, ws[k]), __fadd_rn(md, wd[k]));
                 }
+                int step = 0;
 #pragma unroll
                 for (int k = 0; k < BR; ++k)
                     if (nv[k] < v[k])
                     {
                         v[k] = nv[k];
-                        local = 1;
+                        step = 1;
                     }
+                local |= step;
+                if (!__any_sync(0xffffffffu, step))
+                    break;  // the band is a fixed point of its inputs: the remaining steps would change nothing
             }
             if (local)
             {
