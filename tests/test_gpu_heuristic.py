@@ -78,6 +78,28 @@ def test_repeated_builds_with_goals_in_many_tiles(handle, port):
             assert handle.heuristic_stats()["rounds"] >= 8  # rounds that had work
 
 
+def test_serpentine_corridor_and_cost_gradients(handle, port):
+    """Maps on which the bands of a tile start and stop moving many times during one visit (the in-tile relaxation
+    lets bands that have stopped sit votes out): a serpentine corridor of walls with 3-cell gaps, and a field of
+    steep random costs without obstacles."""
+    W, H = 257, 203
+    cost = np.zeros((H, W), np.uint8)
+    for i, x in enumerate(range(6, W - 6, 7)):
+        cost[:, x] = 254
+        gap = 2 if i % 2 == 0 else H - 5
+        cost[gap:gap + 3, x] = 0
+    handle.costmap_upload(cost)
+    for goal in [(2, 2), (W - 3, H // 2), (130, 100)]:
+        field = handle.heuristic_build(goal[0], goal[1], 2.0)
+        assert np.array_equal(field, port.heuristic_fixed_point(cost, goal, 2.0)), goal
+    rng = np.random.default_rng(9)
+    steep = rng.integers(0, 253, size=(H, W)).astype(np.uint8)
+    handle.costmap_upload(steep)
+    for pen in (2.0, 7.5):
+        field = handle.heuristic_build(100, 60, pen)
+        assert np.array_equal(field, port.heuristic_fixed_point(steep, (100, 60), pen)), pen
+
+
 def test_tiny_maps(handle, port):
     for shape in [(1, 1), (2, 5), (3, 3)]:
         cost = np.zeros(shape[::-1], np.uint8)
