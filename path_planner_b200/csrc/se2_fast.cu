@@ -45,6 +45,7 @@
 #include <cuda.h>  // CUtensorMap (types only; the encoder is fetched through cudaGetDriverEntryPoint)
 
 #include <algorithm>
+#include <atomic>
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
@@ -868,6 +869,7 @@ struct Se2Plan
     // how hard the cover search tried (0 quick, 1 thorough) and how often the plan has been used
     int effort = 0;
     uint32_t uses = 0;
+    uint64_t serial = 0;  // distinguishes plans: the launcher keeps the assembled bin lists of the last (plan, bin set)
     // geometry
     bool usable = false;
     bool tma = false;  // smem_bytes includes the staging blocks of the bulk-tensor stores
@@ -1009,6 +1011,8 @@ bool plan_matches(const Se2Plan *p, pp_handle h)
 pp_status build_plan(pp_handle h, int effort)
 {
     Se2Plan *pl = new Se2Plan();
+    static std::atomic<uint64_t> plan_serial{0};
+    pl->serial = ++plan_serial;
     h->plan = pl;
     pl->effort = effort;
     // branch-and-bound nodes per offset set: a one-off build (pp_plan) should not wait for the last
@@ -1306,6 +1310,10 @@ pp_status pp_se2_launch_fast(pp_handle h, uint32_t x0, uint32_t y0, uint32_t x1,
     const uint32_t tx_lo = x0 / FT_W, tx_hi = (x1 + FT_W - 1) / FT_W;
     const uint32_t ty_lo = y0 / pl->TH, ty_hi = (y1 + pl->TH - 1) / pl->TH;
     static thread_local FastArgs args;  // ~28 KB: keep it off the stack
+    // Assembling the per-bin part of `args` (sample lists, chains) costs tens of microseconds of host time; a rebuild
+    // with the same plan and the same bins, all in one launch, reuses what is already in `args`.
+    static thread_local uint64_t listed_serial = 0;
+    static thread_local std::vector<uint32_t> listed_bins;
     args.cost = h->d_cost;
     args.vol = h->d_vol;
     {
@@ -1316,7 +1324,18 @@ pp_status pp_se2_launch_fast(pp_handle h, uint32_t x0, uint32_t y0, uint32_t x1,
             args.peer_delta[p - 1] = static_cast<long long>(reinterpret_cast<uintptr_t>(targets[p]) - reinterpret_cast<uintptr_t>(targets[0]));
     }
     // bulk-tensor stores unless peers' volumes are written too (those go out as plain stores over NVLink)
-    args.use_tma = pl->tma && args.n_peers == 0 && encode_volume_map(&args.vol_map, h->d_vol, h->W, h->H, h->n_theta);
+    {
+        static thread_local const void *map_vol = nullptr;  // the tensor map in `args` describes this volume
+        static thread_local uint32_t map_dims[3] = {0, 0, 0};
+        const bool want = pl->tma && args.n_peers == 0;
+        if (want && (map_vol != h->d_vol || map_dims[0] != h->W || map_dims[1] != h->H || map_dims[2] != h->n_theta))
+        {
+            const bool ok = encode_volume_map(&args.vol_map, h->d_vol, h->W, h->H, h->n_theta);
+            map_vol = ok ? h->d_vol : nullptr;
+            map_dims[0] = h->W, map_dims[1] = h->H, map_dims[2] = h->n_theta;
+        }
+        args.use_tma = want && map_vol == h->d_vol;
+    }
     if (getenv("PP_SE2_DEBUG"))
         fprintf(stderr, "[pp] se2 fast: halo %d tables %d smem %zu tma %d grid %ux%u\n", pl->R, pl->n_tables, pl->smem_bytes, args.use_tma,
                 (x1 + FT_W - 1) / FT_W - x0 / FT_W, ty_hi - ty_lo);
@@ -1401,53 +1420,66 @@ pp_status pp_se2_launch_fast(pp_handle h, uint32_t x0, uint32_t y0, uint32_t x1,
     size_t bi = 0;
     while (bi < bins.size())
     {
-        // as many bins as fit in the parameter block
-        uint32_t n = 0, words = 0;
-        std::map<uint32_t, uint32_t> stored;           // offset-set id -> where its list sits in args.lists
-        std::map<uint32_t, uint32_t> last_with;        // offset-set id -> last (bin, class) link that has it
-        while (bi + n < bins.size() && n < MAX_T_PER_LAUNCH)
+        uint32_t n = 0;
+        const bool reuse = bi == 0 && listed_serial == pl->serial && listed_bins == bins;
+        if (reuse)
+            n = static_cast<uint32_t>(bins.size());
+        else
         {
-            const uint32_t t = bins[bi + n];
-            uint32_t need = 0;
-            for (int c = 0; c < 4; ++c)
-                if (!stored.count(pl->list_id[t * 4 + c]))
-                    need += (pl->list_len[t * 4 + c] + 3u) & ~3u;
-            if (words + need > MAX_LIST_WORDS)
-                break;
-            args.xsplit[n] = pl->xsplit[t];
-            args.ysplit[n] = pl->ysplit[t];
-            args.split_left[n] = pl->split_left[t];
-            for (int c = 0; c < 4; ++c)
+            listed_serial = 0;
+            // as many bins as fit in the parameter block
+            uint32_t words = 0;
+            std::map<uint32_t, uint32_t> stored;           // offset-set id -> where its list sits in args.lists
+            std::map<uint32_t, uint32_t> last_with;        // offset-set id -> last (bin, class) link that has it
+            while (bi + n < bins.size() && n < MAX_T_PER_LAUNCH)
             {
-                const uint32_t len = pl->list_len[t * 4 + c], id = pl->list_id[t * 4 + c];
-                args.list_len[n][c] = static_cast<uint16_t>(len);
-                args.chain_prev[n][c] = args.chain_next[n][c] = static_cast<uint16_t>(NO_LINK);
-                if (id == Se2Plan::NO_ID)
+                const uint32_t t = bins[bi + n];
+                uint32_t need = 0;
+                for (int c = 0; c < 4; ++c)
+                    if (!stored.count(pl->list_id[t * 4 + c]))
+                        need += (pl->list_len[t * 4 + c] + 3u) & ~3u;
+                if (words + need > MAX_LIST_WORDS)
+                    break;
+                args.xsplit[n] = pl->xsplit[t];
+                args.ysplit[n] = pl->ysplit[t];
+                args.split_left[n] = pl->split_left[t];
+                for (int c = 0; c < 4; ++c)
                 {
-                    args.list_off[n][c] = 0;
-                    continue;
+                    const uint32_t len = pl->list_len[t * 4 + c], id = pl->list_id[t * 4 + c];
+                    args.list_len[n][c] = static_cast<uint16_t>(len);
+                    args.chain_prev[n][c] = args.chain_next[n][c] = static_cast<uint16_t>(NO_LINK);
+                    if (id == Se2Plan::NO_ID)
+                    {
+                        args.list_off[n][c] = 0;
+                        continue;
+                    }
+                    auto st = stored.find(id);
+                    if (st == stored.end())
+                    {
+                        st = stored.emplace(id, words).first;
+                        std::memcpy(args.lists + words, pl->lists.data() + pl->list_off[t * 4 + c], len * sizeof(uint32_t));
+                        words += (len + 3u) & ~3u;  // keep every list 16-byte aligned
+                    }
+                    args.list_off[n][c] = static_cast<uint16_t>(st->second);
+                    const uint32_t me = n | static_cast<uint32_t>(c) << 8;
+                    auto lw = last_with.find(id);
+                    if (lw != last_with.end())
+                    {
+                        args.chain_prev[n][c] = static_cast<uint16_t>(lw->second);
+                        args.chain_next[lw->second & 0xFFu][lw->second >> 8] = static_cast<uint16_t>(me);
+                        lw->second = me;
+                    }
+                    else
+                        last_with.emplace(id, me);
                 }
-                auto st = stored.find(id);
-                if (st == stored.end())
-                {
-                    st = stored.emplace(id, words).first;
-                    std::memcpy(args.lists + words, pl->lists.data() + pl->list_off[t * 4 + c], len * sizeof(uint32_t));
-                    words += (len + 3u) & ~3u;  // keep every list 16-byte aligned
-                }
-                args.list_off[n][c] = static_cast<uint16_t>(st->second);
-                const uint32_t me = n | static_cast<uint32_t>(c) << 8;
-                auto lw = last_with.find(id);
-                if (lw != last_with.end())
-                {
-                    args.chain_prev[n][c] = static_cast<uint16_t>(lw->second);
-                    args.chain_next[lw->second & 0xFFu][lw->second >> 8] = static_cast<uint16_t>(me);
-                    lw->second = me;
-                }
-                else
-                    last_with.emplace(id, me);
+                args.bin[n] = static_cast<uint16_t>(t);
+                ++n;
             }
-            args.bin[n] = static_cast<uint16_t>(t);
-            ++n;
+            if (bi == 0 && n == bins.size())
+            {
+                listed_serial = pl->serial;
+                listed_bins = bins;
+            }
         }
         PP_REQUIRE(h, n > 0, PP_ERR_RANGE, "a single heading bin needs more than %d sample words", MAX_LIST_WORDS);
         args.n_t = n;
