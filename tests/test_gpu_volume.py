@@ -309,7 +309,7 @@ def test_new_entry_points_reject_bad_arguments(handle):
 @pytest.mark.parametrize("shape", [(96, 80), (200, 150), (256, 64), (400, 400)])
 @pytest.mark.parametrize("fname", ["rect_hole", "circle_hole", "rect_solid"])
 def test_32_row_tiles_match_the_port(handle, port, monkeypatch, shape, fname):
-    """Large builds use 128 x 32 tiles (the planner picks them from ~2000 tiles on); forced here on small, ragged maps
+    """Large builds use 128 x 32 tiles (the planner picks them from ~1000 tiles on); forced here on small, ragged maps
     so that partial tiles, mixed tiles at the first columns / rows and the dirty-region refresh run with them too."""
     monkeypatch.setenv("PP_SE2_TILE_ROWS", "32")
     W, H = shape
