@@ -58,3 +58,16 @@ def test_create_fails_loudly_without_gpu():
         pytest.skip("a GPU is present")
     with pytest.raises(capi.PPError):
         capi.Handle(0)
+
+
+def test_window_origin_is_host_arithmetic():
+    """pp_window_origin_cell is plain host arithmetic (Costmap2D::updateOrigin + the static layer's worldToMap): it
+    runs without a GPU and equals the oracle's restatement."""
+    import numpy as np
+    import oracle
+    L = capi.load()
+    rng = np.random.default_rng(3)
+    cases = [(5.0, 10.0, 0.05, 0.0), (12.37, 10.0, 0.05, 0.0), (0.3, 10.0, 0.05, 0.0), (12.37, 10.0, 0.05, -10.0), (-3.21, 6.0, 0.1, -50.0)]
+    cases += [(float(rng.uniform(-40, 40)), 10.0, 0.05, float(rng.uniform(-20, 0))) for _ in range(200)]
+    for robot, size, res, origin in cases:
+        assert L.pp_window_origin_cell(robot, size, res, origin) == oracle.Port.window_origin_cell(robot, size, res, origin), (robot, size, res, origin)
